@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""Headline benchmark: animated + skinned instances per second (BASELINE.json `metric`).
+
+Workload "config3" (BASELINE.json configs[2]) PER GPU:
+  100 000 instances of the bundled 58-bone player skeleton, each blending two clips (the bundled
+  crouch-walk clip + a seeded 17-frame synthetic "run" variant -- the reference ships one clip) with
+  weights (w, 1-w), then 4-weight linear-blend skinning of a 16 380-vertex synthetic player mesh
+  (robot.mesh_bind.json is a missing blob) to positions + normals + tangents (36 B / vertex) into a
+  device ring of 25 000 instance slots (14.7 GB; the consumer -- a renderer -- would drain it).
+A "step" = one pcl_batch_tick (phase advance + sample + blend + hierarchy + palette) + the LBS launches
+that skin all instances (4 ring chunks).  Instances shard across GPUs with no collective (weak scaling).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--instances M]
+  torchrun ... bench.py --gpus N ...        (one rank per GPU; rank 0 prints ONE JSON line)
+
+`value`  : device-resident steps, timed with CUDA events on the library's compute stream, max over ranks.
+`e2e`    : same step through the C ABI with HOST buffers: per-step host->device upload of every
+           instance's phases and weights, and device->host download of every instance's AnimationResult
+           (58 4x4 matrices) into pinned memory; skinned streams stay on the device like the
+           reference's vertex-shader output does.
+`roofline`: the LBS kernel (dominant), algorithmic bytes / measured launch time vs the measured HBM peak.
+`cpu_baseline` / --impl reference: the reference's own Skeleton code (oracle/_ref) + the mesh.vert
+           restatement on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+V_PLAYER = 16380
+RING_SLOTS = 25000
+DT = 1.0 / 60.0
+CLIP_LEN = 0.76666998863220215
+
+
+def measured_hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_workload(n_inst):
+    from piccolo_b200 import assets as A
+    sk, cl, am, mk = A.load_player()
+    run = A.make_variant_clip(cl, 17, seed=1234)
+    mesh = A.make_player_mesh(sk, V=V_PLAYER, seed=42)
+    i = np.arange(n_inst, dtype=np.float64)
+    w = np.modf(i * 0.7548776662)[0].astype(np.float32)
+    weight = np.stack([w, np.float32(1) - w], 1)
+    phase = np.stack([np.modf(i * 0.6180339887)[0], np.modf(i * 0.6180339887 + 0.5)[0]], 1).astype(np.float32)
+    return sk, cl, run, am, mk, mesh, phase, weight
+
+
+def lbs_algorithmic_bytes(count, V, J, out_bytes):
+    # B_lbs = N*(V*O + (J+1)*P) + V*(36+32); P = 48 B (compact 3x4 palette is what is read)
+    return count * (V * out_bytes + (J + 1) * 48) + V * 68
+
+
+def run_ours(args):
+    import torch
+    from piccolo_b200 import capi
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    dist = None
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    N = args.instances
+    sk, cl, run, am, mk, mesh, phase, weight = build_workload(N)
+    ctx = capi.Context(local)
+    skel = ctx.upload_skeleton(sk)
+    c0, c1 = ctx.upload_clip(skel, cl, am), ctx.upload_clip(skel, run, am)
+    mh = ctx.upload_mesh(mesh, sk.J)
+    b = ctx.batch(skel, N, 2)
+    # every rank animates its own shard: offset the phases so shards differ
+    phase = np.modf(phase.astype(np.float64) + 0.37 * rank)[0].astype(np.float32)
+    b.set(clip_ids=np.tile(np.int32([c0, c1]), (N, 1)), phase=phase, weight=weight, clip_len=np.tile(np.float32([CLIP_LEN, 17.0 / 30.0]), (N, 1)))
+    ring = min(RING_SLOTS, N)
+    sb = ctx.skinbuf(mh, mesh.V, ring, capi.PCL_SKIN_POS_NRM_TAN)
+    chunks = [(f, min(ring, N - f)) for f in range(0, N, ring)]
+    if args.lbs_variant is not None:
+        ctx.set_option("lbs_variant", args.lbs_variant)
+
+    def skin_all():
+        for f, n in chunks:
+            b.skin(mh, sb, first=f, count=n, slot_first=0)
+
+    def step_device():
+        b.tick(DT, capi.PCL_ADVANCE_ALL)
+        skin_all()
+
+    host_pal = ctx.pinned((N, sk.J, 16), np.float32)
+    h_phase, h_weight = phase.copy(), weight.copy()
+
+    def step_e2e():
+        b.set(phase=h_phase, weight=h_weight)  # H2D of this step's inputs
+        b.pose()
+        b.download_palette(out=host_pal, asynchronous=True)  # D2H of AnimationResult, overlaps the skinning
+        skin_all()
+        ctx.sync()
+
+    # ---- device-resident timing -------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_device()
+    ctx.sync()
+    l0 = ctx.launch_count()
+    barrier()
+    with ClockSampler(local) as clk:
+        ctx.timer_begin()
+        for _ in range(args.steps):
+            step_device()
+        ms = ctx.timer_end()
+    barrier()
+    launches = ctx.launch_count() - l0
+    ms = max_over_ranks(ms)
+    clocks = clk.summary()
+
+    # ---- the dominant kernel alone (roofline) ---------------------------------------------------
+    ctx.timer_begin()
+    for _ in range(args.steps):
+        skin_all()
+    lbs_ms = ctx.timer_end() / (args.steps * len(chunks))
+    ctx.timer_begin()
+    for _ in range(args.steps):
+        b.pose()
+    pose_ms = ctx.timer_end() / args.steps
+    peak, peak_src = measured_hbm_peak()
+    per_launch = np.mean([lbs_algorithmic_bytes(n, mesh.V, sk.J, 36) for _, n in chunks])
+    achieved = per_launch / (lbs_ms * 1e-3) / 1e9
+    pose_bytes = N * (2 * 12 + 60 * 48)
+    roofline = {"bound": "hbm", "kernel": "lbs_kernel<NT=1>", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": int(per_launch), "launch_ms": round(lbs_ms, 4),
+                "frac_of_nominal_8000": round(achieved / 8000.0, 4),
+                "pose_kernel": {"launch_ms": round(pose_ms, 4), "achieved": round(pose_bytes / (pose_ms * 1e-3) / 1e9, 1),
+                                "frac": round(pose_bytes / (pose_ms * 1e-3) / 1e9 / peak, 4),
+                                "joints_per_s": round(N * sk.J / (pose_ms * 1e-3), 0)}}
+
+    # ---- end to end through the C ABI with host buffers -------------------------------------------
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    ctx.timer_begin()
+    for _ in range(args.steps):
+        step_e2e()
+    e2e_ms = ctx.timer_end()
+    e2e_wall = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max_over_ranks(max(e2e_ms, e2e_wall))  # host-side work counts too
+    barrier()
+
+    total = N * world
+    out = {
+        "metric": "animated+skinned instances/sec", "value": round(total * args.steps / (ms * 1e-3), 1), "unit": "instances/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "config3: %d instances/GPU x 58-bone player skeleton, 2-clip blend (bundled clip + seeded 17-frame variant), "
+                               "4-weight LBS of a %d-vertex synthetic player mesh to POS+NRM+TAN" % (N, mesh.V),
+                   "instances_per_gpu": N, "joints": sk.J, "vertices": mesh.V, "clips_per_instance": 2,
+                   "ring_slots": ring, "palette_layout": "3x4 fp32, 48 B/slot, pitch 60 slots", "lbs_variant": args.lbs_variant,
+                   "l2": "per-step traffic (%.1f GB written) exceeds the 126 MB L2; no flush needed" % (N * mesh.V * 36 / 1e9),
+                   "parallelism": "instances sharded, no collective"},
+        "clocks": clocks, "gpu_launches": int(launches),
+        "e2e": {"value": round(total * args.steps / (e2e_ms * 1e-3), 1), "unit": "instances/s",
+                "h2d_bytes_per_step": int(h_phase.nbytes + h_weight.nbytes), "d2h_bytes_per_step": int(host_pal.nbytes),
+                "ms_per_step": round(e2e_ms / args.steps, 4)},
+        "roofline": roofline,
+        "joints_per_s": round(total * sk.J * args.steps / (ms * 1e-3), 0),
+        "skinned_vertices_per_s": round(total * mesh.V * args.steps / (ms * 1e-3), 0),
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(sk, cl, am, mk, mesh, budget_s=args.cpu_budget)
+    sb.close(), b.close(), ctx.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# the reference's CPU implementation of the path, on the host cores
+# ------------------------------------------------------------------------------------------------
+def _ref_session(sk, cl, am, mk, td):
+    from oracle import pyoracle as O
+    urls = O.write_player_json(td, sk, cl, am, mk)
+    ref = O.RefLib(td)
+    return ref, ref.open(urls["skeleton"], urls["clip"], urls["map"], urls["mask"], CLIP_LEN)
+
+
+def cpu_reference_rate(sk, cl, am, mk, mesh, budget_s, threads):
+    """instances/s of (full AnimationComponent::tick + mesh.vert restatement), all `threads` host threads.
+    Returns (rate, description).  Uses oracle/_ref when present (kind 'reference'), else the C port."""
+    from oracle import pyoracle as O
+    if O.RefLib.available():
+        with tempfile.TemporaryDirectory() as td:
+            ref, h = _ref_session(sk, cl, am, mk, td)
+            # calibrate, then size both legs for ~budget/2 seconds each
+            r_pose = ref.bench_pose(h, threads, 200, True)
+            per_thread = max(200, int(r_pose * (budget_s / 2) / threads))
+            r_pose = ref.bench_pose(h, threads, per_thread, True)
+            mats, _ = ref.pose(h, np.linspace(0, 1, 64, dtype=np.float32))
+            pal = np.concatenate([np.tile(np.eye(4, dtype=np.float32).reshape(1, 1, 16), (64, 1, 1)), mats], 1)
+            r_lbs = ref.bench_lbs(mesh, pal[: 2 * threads], threads)
+            n_lbs = max(2 * threads, int(r_lbs * (budget_s / 2)))
+            pal_n = pal[np.arange(n_lbs) % 64]
+            r_lbs = ref.bench_lbs(mesh, pal_n, threads)
+        rate = 1.0 / (1.0 / r_pose + 1.0 / r_lbs)
+        return rate, "reference", ("oracle/_ref: %d full ticks (getBlendStateWithClipData+applyAnimation+outputAnimationResult; the reference plays "
+                                   "clip 0 only, skeleton.cpp:46) at %.0f/s + mesh.vert restatement of %d instances x %d vertices at %.1f/s"
+                                   % (per_thread * threads, r_pose, n_lbs, mesh.V, r_lbs))
+    orc = O.Oracle()
+    sv, cv = orc.skeleton(sk), orc.clip(cl, am)
+    n = 20000
+    ph = np.random.default_rng(0).uniform(0, 1, n).astype(np.float32)
+    t0 = time.perf_counter()
+    mats = orc.pose_batch(sv, [cv], np.zeros((n, 1), np.int32), ph, n_threads=threads)
+    r_pose = n / (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    k = 8
+    for i in range(k):
+        orc.lbs(mesh, orc.palette_slots(mats[i]))
+    r_lbs = k / (time.perf_counter() - t0)
+    rate = 1.0 / (1.0 / r_pose + 1.0 / r_lbs)
+    return rate, "port", "oracle/oracle.c: %d poses on %d threads + %d single-thread LBS passes" % (n, threads, k)
+
+
+def cpu_baseline(sk, cl, am, mk, mesh, budget_s=16.0):
+    threads = os.cpu_count() or 1
+    rate, kind, sample = cpu_reference_rate(sk, cl, am, mk, mesh, budget_s, threads)
+    return {"value": round(rate, 2), "unit": "instances/s", "cores": threads, "kind": kind, "sample": sample}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sk, cl, run, am, mk, mesh, phase, weight = build_workload(1024)
+    threads = os.cpu_count() or 1
+    budget = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    rates, kind, sample = [], "port", ""
+    t_all = time.perf_counter()
+    for s in range(args.warmup + args.steps):
+        r, kind, sample = cpu_reference_rate(sk, cl, am, mk, mesh, budget, threads)
+        if s >= args.warmup:
+            rates.append(r)
+    wall = time.perf_counter() - t_all
+    v = float(np.mean(rates))
+    out = {"impl": "reference", "metric": "animated+skinned instances/sec", "value": round(v, 2), "unit": "instances/s",
+           "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": round(wall * 1e3 / max(1, args.steps + args.warmup), 2), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": "config3 on the host cores: each step = a bounded sample of the same workload (%s)" % sample},
+           "cpu_baseline": {"value": round(v, 2), "unit": "instances/s", "cores": threads, "kind": kind, "sample": sample},
+           "e2e": {"value": round(v, 2), "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--instances", type=int, default=100000, help="instances per GPU")
+    ap.add_argument("--lbs-variant", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=16.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

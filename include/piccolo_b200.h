@@ -1,0 +1,184 @@
+/*
+ * piccolo_b200 -- C ABI of the B200-native batch skeletal-animation + skinning engine.
+ *
+ * Drop-in scope: Piccolo's runtime animation path
+ *   AnimationComponent::tick -> AnimationManager::getBlendStateWithClipData -> Skeleton::applyAnimation
+ *   -> Node/Bone local->model update -> Skeleton::outputAnimationResult -> mesh.vert 4-weight LBS.
+ * The host-side C++ mirror of the reference classes (piccolo_b200/host/) and any foreign binding sit on
+ * top of exactly these entry points.  Plain pointers and sizes only; no torch / STL types.
+ *
+ * Conventions
+ *   - every function returns PCL_OK (0) or a negative pcl_status; pcl_last_error() gives the text.
+ *   - the caller owns every host array; the library owns all device memory it allocates.
+ *   - one context per CUDA device.  Calls on one context are NOT thread-safe; distinct contexts are
+ *     independent (one per GPU / per rank).  Work is enqueued on the context's streams and is
+ *     asynchronous unless stated; pcl_sync() waits for it.
+ *   - there is no CPU fallback: without a CUDA device pcl_create fails with PCL_ERR_NO_DEVICE.
+ *   - quaternions are (w,x,y,z) like Piccolo::Quaternion (core/math/quaternion.h:19); matrices are
+ *     row-major, column-vector convention, translation in [r][3] (core/math/matrix4.h:98-119).
+ *
+ * file:line citations are relative to /root/reference/engine/source/runtime unless they start with
+ * "engine/".
+ */
+#ifndef PICCOLO_B200_H
+#define PICCOLO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum pcl_status
+{
+    PCL_OK              = 0,
+    PCL_ERR_INVALID     = -1, /* bad argument / malformed asset                                        */
+    PCL_ERR_CUDA        = -2, /* a CUDA runtime call failed (text in pcl_last_error)                   */
+    PCL_ERR_UNSUPPORTED = -3, /* well-formed input this engine does not handle (see each function)     */
+    PCL_ERR_OOM         = -4,
+    PCL_ERR_NO_DEVICE   = -5
+} pcl_status;
+
+typedef struct pcl_ctx     pcl_ctx;     /* one per device                                  */
+typedef struct pcl_batch   pcl_batch;   /* N animated instances of one skeleton            */
+typedef struct pcl_skinbuf pcl_skinbuf; /* device ring of skinned vertex streams           */
+typedef int32_t            pcl_skel;    /* handles are small integers scoped to a context  */
+typedef int32_t            pcl_clip;
+typedef int32_t            pcl_mask;
+typedef int32_t            pcl_mesh;
+
+/* pcl_batch_advance / pcl_batch_tick */
+#define PCL_ADVANCE_FIRST_ONLY 1 /* reference behaviour: only blend_ratio[0] moves (animation_component.cpp:19-21) */
+#define PCL_ADVANCE_ALL 2        /* every clip slot advances with its own clip length                               */
+/* pcl_skinbuf_create / pcl_batch_skin */
+#define PCL_SKIN_POS 1           /* positions only (shadow / pick shader variants)                                  */
+#define PCL_SKIN_POS_NRM_TAN 7   /* positions + normals + tangents (engine/shader/glsl/mesh.vert)                   */
+
+/* ---- lifecycle ------------------------------------------------------------------------------ */
+int         pcl_version(void);
+int         pcl_device_count(void);
+int         pcl_create(int device, pcl_ctx** out);
+int         pcl_destroy(pcl_ctx* ctx);
+const char* pcl_last_error(const pcl_ctx* ctx); /* ctx == NULL: error of the last failed pcl_create */
+int         pcl_sync(pcl_ctx* ctx);
+/* number of this library's kernels launched on the context so far */
+int64_t     pcl_launch_count(const pcl_ctx* ctx);
+/* pinned host memory for the download / set calls (cudaHostAlloc); optional, any host memory works */
+int         pcl_host_alloc(pcl_ctx* ctx, size_t bytes, void** out);
+int         pcl_host_free(pcl_ctx* ctx, void* p);
+/* device timing on the context's compute stream: begin records an event, end waits for all the
+ * context's streams, records, synchronises and returns the elapsed milliseconds */
+int         pcl_timer_begin(pcl_ctx* ctx);
+int         pcl_timer_end(pcl_ctx* ctx, float* ms);
+
+/* ---- assets: repacked once into SoA device buffers --------------------------------------------
+ * pcl_upload_skeleton replaces Skeleton::buildSkeleton (function/animation/skeleton.cpp:17-37) with
+ * find_by_index (function/animation/utilities.cpp:7-27: parent_index == INT_MAX or >= own position
+ * => root) and Bone::initialize (function/animation/node.cpp:220-234: the bind quaternion is
+ * normalised, NaN -> identity).  Arrays follow SkeletonData::bones_map order
+ * (resource/res_type/data/skeleton_data.h:9-35).
+ *   PCL_ERR_UNSUPPORTED when !is_flat || !in_topological_order (the reference silently builds
+ *   nothing, skeleton.cpp:24-28) or when an inverse-bind matrix is not affine (row 3 != 0 0 0 1).
+ *   PCL_ERR_INVALID for J < 1 or a negative parent_index (undefined behaviour in the reference). */
+int pcl_upload_skeleton(pcl_ctx* ctx, int32_t J, const int32_t* index /*[J] RawBone.index*/,
+                        const int32_t* parent_index /*[J]*/, const float* bind_pos /*[3J]*/,
+                        const float* bind_rot_wxyz /*[4J]*/, const float* bind_scl /*[3J]*/,
+                        const float* inv_bind /*[16J] RawBone.tpose_matrix*/, int32_t is_flat,
+                        int32_t in_topological_order, pcl_skel* out);
+int pcl_skeleton_bone_count(pcl_ctx* ctx, pcl_skel skel, int32_t* J);
+/* AnimationResultElement.index per bone = RawBone.index + 1 (skeleton.cpp:127, node.cpp:237-244) */
+int pcl_skeleton_indices(pcl_ctx* ctx, pcl_skel skel, int32_t* out /*[J]*/);
+/* parent position per bone after find_by_index (-1 = root) */
+int pcl_skeleton_parents(pcl_ctx* ctx, pcl_skel skel, int32_t* out /*[J]*/);
+
+/* One AnimationClip (resource/res_type/data/animation_clip.h:18-39) together with the AnimSkelMap it
+ * is played through (resource/res_type/data/animation_skeleton_node_map.h:9-16), i.e. one entry of
+ * BlendStateWithClipData::blend_clip / blend_anim_skel_map (resource/res_type/data/blend_state.h:19-30).
+ * Tracks are ragged: key_counts[3c+0..2] = number of position / rotation / scaling keys of channel c,
+ * stored back to back in pos / rot_wxyz / scl in channel order.  Only channels
+ * n < min(node_count, convert_len) are played (skeleton.cpp:57-59); convert[n] == -1 skips a channel
+ * (skeleton.cpp:69-73).  The key-count clamp that carries over from one channel to the next
+ * (skeleton.cpp:75-87) is reproduced.
+ *   PCL_ERR_INVALID: node_count > C, convert[n] outside {-1} U [0,J), or a played channel with an
+ *   empty track (the reference would index [-1]). */
+int pcl_upload_clip(pcl_ctx* ctx, pcl_skel skel, int32_t total_frame, int32_t node_count, int32_t C,
+                    const int32_t* key_counts /*[3C]*/, const float* pos, const float* rot_wxyz, const float* scl,
+                    int32_t convert_len, const int32_t* convert, pcl_clip* out);
+/* BoneBlendMask::enabled (resource/res_type/data/skeleton_mask.h:9-16); used only when a batch blends
+ * K > 1 clips (the reference forces weight = 1 for its single clip, skeleton.cpp:63-64). */
+int pcl_upload_mask(pcl_ctx* ctx, pcl_skel skel, int32_t J, const int32_t* enabled, pcl_mask* out);
+/* Vertex streams + joint binding of one skinned mesh: MeshData (resource/res_type/data/mesh_data.h:9-53)
+ * as RenderResourceBase::loadMeshData lays it out (function/render/render_resource_base.cpp:96-148).
+ * idx4 holds palette slots (bone position + 1, 0 = empty, function/animation/animation_loader.cpp:40-71);
+ * w4_raw is renormalised here exactly like RenderResource::updateVertexBuffer
+ * (function/render/render_resource.cpp:714-725).  The mesh must be fully expanded (one binding per
+ * vertex, the case in which the reference's per-index binding upload is self-consistent,
+ * render_resource.cpp:705-712).  PCL_ERR_INVALID when an idx4 entry is < 0 or > max_slot. */
+int pcl_upload_mesh(pcl_ctx* ctx, int32_t V, const float* pos /*[3V]*/, const float* nrm /*[3V]*/,
+                    const float* tan /*[3V]*/, const int32_t* idx4 /*[4V]*/, const float* w4_raw /*[4V]*/,
+                    int32_t max_slot, pcl_mesh* out);
+
+/* ---- instances -------------------------------------------------------------------------------
+ * A batch = N independent AnimationComponents sharing one skeleton, each holding K clip slots
+ * (BlendState::clip_count, resource/res_type/data/blend_state.h:32-45): clip id, blend_ratio (phase),
+ * blend_weight, blend_clip_file_length and mask id per slot.  K == 1 is the reference's executed path;
+ * K in 2..4 is this engine's documented blend extension (DESIGN.md "A4").  K > 4: PCL_ERR_UNSUPPORTED. */
+int pcl_batch_create(pcl_ctx* ctx, pcl_skel skel, int64_t N, int32_t K, pcl_batch** out);
+int pcl_batch_destroy(pcl_batch* b);
+/* Host arrays are [count][K]; a NULL array leaves that field unchanged.  Defaults after create:
+ * clip 0, phase 0, weight 1, length 1, mask -1 (= every bone enabled).  Synchronous. */
+int pcl_batch_set(pcl_batch* b, int64_t first, int64_t count, const int32_t* clip_ids, const float* phase,
+                  const float* weight, const float* clip_len, const int32_t* mask_ids);
+int pcl_batch_get_phases(pcl_batch* b, int64_t first, int64_t count, float* phase /*[count][K]*/);
+/* ratio += dt / length; ratio -= floor(ratio)   (animation_component.cpp:19-21), on the device */
+int pcl_batch_advance(pcl_batch* b, float dt, int32_t mode);
+
+/* ---- hot path --------------------------------------------------------------------------------
+ * pcl_batch_pose = Skeleton::applyAnimation + outputAnimationResult for every instance
+ * (skeleton.cpp:39-156): keyframe sampling (lerp / lerp / nlerp shortest path), bind-relative local
+ * pose, level-ordered local->model update, model x inverse-bind.  Product: the device palette
+ * [N][pitch][3] float4 = rows 0..2 of each 4x4 (row 3 is 0 0 0 1), slot 0 = identity, slot i+1 = bone i
+ * (the layout MeshComponent::tick hands to the renderer, function/framework/component/mesh/
+ * mesh_component.cpp:72-79).  pcl_batch_tick = pcl_batch_advance + pcl_batch_pose in one launch
+ * (AnimationComponent::tick, animation_component.cpp:17-25). */
+int pcl_batch_pose(pcl_batch* b);
+int pcl_batch_tick(pcl_batch* b, float dt, int32_t mode);
+/* when enabled, pose/tick also keep the derived (model-space) TRS per bone that LevelDebugger reads
+ * through Skeleton::getBones() (function/framework/level/level_debugger.cpp:110-146) */
+int pcl_batch_keep_derived(pcl_batch* b, int32_t enable);
+
+/* Skinned vertex streams live in a device ring of `capacity` instance slots:
+ *   positions        [capacity][Vp][3] float   (MeshVertex::VulkanMeshVertexPostition,
+ *   normal+tangent   [capacity][Vp][6] float    ...VaryingEnableBlending, function/render/render_mesh.h:14-23)
+ * Vp = V rounded up to a multiple of 4 (keeps every instance 16-byte aligned). */
+int pcl_skinbuf_create(pcl_ctx* ctx, pcl_mesh mesh, int64_t capacity, int32_t flags, pcl_skinbuf** out);
+int pcl_skinbuf_destroy(pcl_skinbuf* s);
+/* engine/shader/glsl/mesh.vert:72-111 for instances [first, first+count) of the batch, written to ring
+ * slots [slot_first, slot_first+count).  Reads the palette of the last pcl_batch_pose / _tick. */
+int pcl_batch_skin(pcl_batch* b, pcl_mesh mesh, pcl_skinbuf* out, int64_t first, int64_t count, int64_t slot_first);
+
+/* ---- readback / interop ----------------------------------------------------------------------- */
+/* AnimationResult for instances [first, first+count): [count][J][16] floats, bones_map order, no
+ * identity slot (resource/res_type/components/animation.h:12-29).  Synchronous. */
+int pcl_batch_download_palette(pcl_batch* b, int64_t first, int64_t count, float* host16);
+/* Same, enqueued on the context's copy stream after the last pose; returns at once.  host16 must stay
+ * valid until pcl_sync().  Overlaps with a following pcl_batch_skin. */
+int pcl_batch_download_palette_async(pcl_batch* b, int64_t first, int64_t count, float* host16);
+/* derived TRS [count][J][10] = P.xyz, Q.wxyz, S.xyz (needs pcl_batch_keep_derived) */
+int pcl_batch_download_derived(pcl_batch* b, int64_t first, int64_t count, float* host10);
+/* device pointer + geometry of the compact palette, for consumers living on the GPU */
+int pcl_batch_palette_dev(pcl_batch* b, const void** dptr, int32_t* pitch_slots, int32_t* floats_per_slot);
+int pcl_skinbuf_dev(pcl_skinbuf* s, const void** pos_dev, const void** nt_dev, int32_t* Vp);
+/* tight host copies: pos [count][V][3], nt [count][V][6] (nt may be NULL) */
+int pcl_skinbuf_download(pcl_skinbuf* s, int64_t slot_first, int64_t count, float* host_pos, float* host_nt);
+
+/* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
+/* key: "pose_warps_per_block" (1,2,4,8), "lbs_variant" (0 = coalesced 128-bit stores, 1 = TMA bulk
+ * stores), "lbs_vsplit" (0 = auto), "lbs_inst_tile" (0 = auto, <= 16).  PCL_ERR_INVALID for unknown keys. */
+int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PICCOLO_B200_H */

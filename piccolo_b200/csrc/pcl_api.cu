@@ -1,0 +1,999 @@
+// C ABI of piccolo_b200 (include/piccolo_b200.h): context, asset repacking into SoA device buffers,
+// kernel launches.  No CPU fallback anywhere: every compute entry point launches a CUDA kernel or fails.
+// Citations are relative to /root/reference/engine/source/runtime.
+#include "../../include/piccolo_b200.h"
+#include "pcl_kernels.cuh"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace pcl;
+
+namespace
+{
+    std::string g_create_error;
+
+    struct SkelRec
+    {
+        int32_t              J = 0, pitch = 0, nslot = 0;
+        std::vector<int32_t> index, parent, order;
+        StepRec*             d_steps = nullptr;
+        int32_t*             d_masks = nullptr; // [n_masks][J]
+        int32_t              n_masks = 0, cap_masks = 0;
+    };
+    struct ClipHost
+    {
+        pcl_skel skel;
+        void*    d_blob = nullptr;
+        ClipRec  rec {};
+    };
+    struct MaskHost
+    {
+        pcl_skel skel;
+        int32_t  local;
+    };
+    struct MeshRec
+    {
+        int32_t V = 0, Vp = 0, Vt = 0, max_slot = 0;
+        float * d_pos = nullptr, *d_nrm = nullptr, *d_tan = nullptr;
+        int4*   d_idx = nullptr;
+        float4* d_w   = nullptr;
+    };
+} // namespace
+
+struct pcl_ctx
+{
+    int          device = 0;
+    cudaStream_t compute = nullptr, copy = nullptr;
+    cudaEvent_t  ev_pose = nullptr, ev_copy = nullptr, t0 = nullptr, t1 = nullptr;
+    bool         copy_pending = false;
+    std::string  err;
+    int64_t      launches = 0;
+    std::vector<SkelRec>  skels;
+    std::vector<ClipHost> clips;
+    std::vector<MaskHost> masks;
+    std::vector<MeshRec>  meshes;
+    ClipRec*     d_clips = nullptr;
+    int32_t      cap_clips = 0;
+    int32_t      opt_pose_wpb = 0, opt_lbs_variant = 0, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0;
+    int          max_smem_optin = 0, sm_count = 0;
+};
+
+struct pcl_batch
+{
+    pcl_ctx*  ctx;
+    pcl_skel  skel;
+    long long N;
+    int32_t   K;
+    int32_t * d_clip_ids = nullptr, *d_mask_ids = nullptr;
+    float *   d_phase = nullptr, *d_weight = nullptr, *d_len = nullptr;
+    float4*   d_palette = nullptr;
+    float*    d_derived = nullptr;
+    float4*   d_export  = nullptr;
+    long long export_cap = 0; // instances
+    bool      posed = false;
+};
+
+struct pcl_skinbuf
+{
+    pcl_ctx*  ctx;
+    pcl_mesh  mesh;
+    long long capacity;
+    int32_t   flags, V, Vp;
+    float *   d_pos = nullptr, *d_nt = nullptr;
+};
+
+namespace
+{
+    int fail(pcl_ctx* c, int code, const std::string& msg)
+    {
+        if (c)
+            c->err = msg;
+        else
+            g_create_error = msg;
+        return code;
+    }
+#define PCL_CK(ctx, call)                                                                                               \
+    do                                                                                                                  \
+    {                                                                                                                   \
+        cudaError_t e__ = (call);                                                                                       \
+        if (e__ != cudaSuccess)                                                                                         \
+            return fail(ctx, e__ == cudaErrorMemoryAllocation ? PCL_ERR_OOM : PCL_ERR_CUDA,                             \
+                        std::string(#call) + ": " + cudaGetErrorString(e__));                                           \
+    } while (0)
+
+    template<typename T>
+    int upload(pcl_ctx* c, T** dptr, const std::vector<T>& h)
+    {
+        PCL_CK(c, cudaMalloc((void**)dptr, std::max<size_t>(h.size(), 1) * sizeof(T)));
+        if (!h.empty())
+            PCL_CK(c, cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return PCL_OK;
+    }
+
+    // Slot plan for one processing order: which bones must park their derived TRS in shared memory
+    // (those with a child that is not the very next step) and for how long.
+    int plan_slots(const std::vector<int32_t>& parent, const std::vector<int32_t>& order, std::vector<int32_t>* psrc,
+                   std::vector<int32_t>* store)
+    {
+        const int            J = (int)parent.size();
+        std::vector<int32_t> step_of(J), last_child_step(J, -1), slot_of(J, -1);
+        std::vector<char>    needs(J, 0);
+        for (int s = 0; s < J; s++)
+            step_of[order[s]] = s;
+        for (int b = 0; b < J; b++)
+            if (parent[b] >= 0)
+            {
+                last_child_step[parent[b]] = std::max(last_child_step[parent[b]], step_of[b]);
+                if (step_of[b] != step_of[parent[b]] + 1)
+                    needs[parent[b]] = 1;
+            }
+        std::vector<int32_t> free_list;
+        int                  nslot = 0;
+        psrc->assign(J, -1), store->assign(J, -1);
+        std::vector<std::vector<int32_t>> release(J + 1);
+        for (int s = 0; s < J; s++)
+        {
+            for (int32_t sl : release[s])
+                free_list.push_back(sl);
+            const int b = order[s], p = parent[b];
+            if (p >= 0)
+                (*psrc)[s] = (step_of[p] == s - 1) ? -2 : slot_of[p];
+            if (needs[b])
+            {
+                int sl;
+                if (!free_list.empty())
+                    sl = free_list.back(), free_list.pop_back();
+                else
+                    sl = nslot++;
+                slot_of[b]  = sl;
+                (*store)[s] = sl;
+                release[last_child_step[b] + 1].push_back(sl);
+            }
+        }
+        return nslot;
+    }
+
+    void dfs_order(const std::vector<int32_t>& parent, std::vector<int32_t>* order)
+    {
+        const int                         J = (int)parent.size();
+        std::vector<std::vector<int32_t>> kids(J);
+        std::vector<int32_t>              roots, stack;
+        for (int b = 0; b < J; b++)
+            (parent[b] >= 0 ? kids[parent[b]] : roots).push_back(b);
+        order->clear();
+        for (auto r = roots.rbegin(); r != roots.rend(); ++r)
+            stack.push_back(*r);
+        while (!stack.empty())
+        {
+            int b = stack.back();
+            stack.pop_back();
+            order->push_back(b);
+            for (auto k = kids[b].rbegin(); k != kids[b].rend(); ++k)
+                stack.push_back(*k);
+        }
+    }
+
+    bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size(); }
+} // namespace
+
+extern "C"
+{
+    int pcl_version(void) { return 100; }
+
+    int pcl_device_count(void)
+    {
+        int n = 0;
+        if (cudaGetDeviceCount(&n) != cudaSuccess)
+        {
+            (void)cudaGetLastError();
+            return 0;
+        }
+        return n;
+    }
+
+    int pcl_create(int device, pcl_ctx** out)
+    {
+        if (!out)
+            return fail(nullptr, PCL_ERR_INVALID, "pcl_create: out == NULL");
+        *out  = nullptr;
+        int n = pcl_device_count();
+        if (n <= 0)
+            return fail(nullptr, PCL_ERR_NO_DEVICE, "pcl_create: no CUDA device (this engine has no CPU path)");
+        if (device < 0 || device >= n)
+            return fail(nullptr, PCL_ERR_INVALID, "pcl_create: device index out of range");
+        PCL_CK(nullptr, cudaSetDevice(device));
+        pcl_ctx* c = new pcl_ctx();
+        c->device  = device;
+        cudaDeviceProp prop;
+        PCL_CK(nullptr, cudaGetDeviceProperties(&prop, device));
+        c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+        c->sm_count       = prop.multiProcessorCount;
+        if (prop.major < 10)
+        {
+            delete c;
+            return fail(nullptr, PCL_ERR_UNSUPPORTED, "pcl_create: kernels are built for sm_100a (Blackwell) only");
+        }
+        PCL_CK(nullptr, cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
+        PCL_CK(nullptr, cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
+        PCL_CK(nullptr, cudaEventCreateWithFlags(&c->ev_pose, cudaEventDisableTiming));
+        PCL_CK(nullptr, cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
+        PCL_CK(nullptr, cudaEventCreate(&c->t0));
+        PCL_CK(nullptr, cudaEventCreate(&c->t1));
+        *out = c;
+        return PCL_OK;
+    }
+
+    int pcl_destroy(pcl_ctx* c)
+    {
+        if (!c)
+            return PCL_ERR_INVALID;
+        cudaSetDevice(c->device);
+        cudaDeviceSynchronize();
+        for (auto& s : c->skels)
+            cudaFree(s.d_steps), cudaFree(s.d_masks);
+        for (auto& cl : c->clips)
+            cudaFree(cl.d_blob);
+        for (auto& m : c->meshes)
+            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w);
+        cudaFree(c->d_clips);
+        cudaEventDestroy(c->ev_pose), cudaEventDestroy(c->ev_copy), cudaEventDestroy(c->t0), cudaEventDestroy(c->t1);
+        cudaStreamDestroy(c->compute), cudaStreamDestroy(c->copy);
+        delete c;
+        return PCL_OK;
+    }
+
+    const char* pcl_last_error(const pcl_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+    int pcl_sync(pcl_ctx* c)
+    {
+        if (!c)
+            return PCL_ERR_INVALID;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->copy));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        return PCL_OK;
+    }
+
+    int64_t pcl_launch_count(const pcl_ctx* c) { return c ? c->launches : 0; }
+
+    int pcl_host_alloc(pcl_ctx* c, size_t bytes, void** out)
+    {
+        if (!c || !out)
+            return PCL_ERR_INVALID;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+        return PCL_OK;
+    }
+    int pcl_host_free(pcl_ctx* c, void* p)
+    {
+        if (!c)
+            return PCL_ERR_INVALID;
+        PCL_CK(c, cudaFreeHost(p));
+        return PCL_OK;
+    }
+
+    int pcl_timer_begin(pcl_ctx* c)
+    {
+        if (!c)
+            return PCL_ERR_INVALID;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaEventRecord(c->t0, c->compute));
+        return PCL_OK;
+    }
+    int pcl_timer_end(pcl_ctx* c, float* ms)
+    {
+        if (!c || !ms)
+            return PCL_ERR_INVALID;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy)); // join the copy stream into the timed region
+        PCL_CK(c, cudaStreamWaitEvent(c->compute, c->ev_copy, 0));
+        PCL_CK(c, cudaEventRecord(c->t1, c->compute));
+        PCL_CK(c, cudaEventSynchronize(c->t1));
+        PCL_CK(c, cudaEventElapsedTime(ms, c->t0, c->t1));
+        return PCL_OK;
+    }
+
+    int pcl_set_option(pcl_ctx* c, const char* key, int32_t v)
+    {
+        if (!c || !key)
+            return PCL_ERR_INVALID;
+        std::string k(key);
+        if (k == "pose_warps_per_block" && (v == 0 || v == 1 || v == 2 || v == 4 || v == 8))
+            c->opt_pose_wpb = v;
+        else if (k == "lbs_variant" && (v == 0 || v == 1))
+            c->opt_lbs_variant = v;
+        else if (k == "lbs_vsplit" && v >= 0)
+            c->opt_lbs_vsplit = v;
+        else if (k == "lbs_inst_tile" && v >= 0 && v <= 16)
+            c->opt_lbs_inst_tile = v;
+        else
+            return fail(c, PCL_ERR_INVALID, "pcl_set_option: unknown key or bad value: " + k);
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // assets
+    // ------------------------------------------------------------------------------------------
+    int pcl_upload_skeleton(pcl_ctx* c, int32_t J, const int32_t* index, const int32_t* parent_index, const float* bind_pos,
+                            const float* bind_rot, const float* bind_scl, const float* inv_bind, int32_t is_flat,
+                            int32_t in_topo, pcl_skel* out)
+    {
+        if (!c || !out || J < 1 || !index || !parent_index || !bind_pos || !bind_rot || !bind_scl || !inv_bind)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_skeleton: bad argument");
+        if (!is_flat || !in_topo)
+            return fail(c, PCL_ERR_UNSUPPORTED,
+                        "pcl_upload_skeleton: skeleton must be flat and in topological order (the reference builds nothing "
+                        "otherwise, skeleton.cpp:24-28)");
+        PCL_CK(c, cudaSetDevice(c->device));
+        SkelRec s;
+        s.J = J;
+        s.index.assign(index, index + J);
+        s.parent.resize(J);
+        for (int i = 0; i < J; i++)
+        {
+            int key = parent_index[i];
+            if (key < 0)
+                return fail(c, PCL_ERR_INVALID, "pcl_upload_skeleton: negative parent_index");
+            s.parent[i] = (key == INT_MAX || key >= i) ? -1 : key; // find_by_index, utilities.cpp:7-27
+            const float* m = inv_bind + 16 * (size_t)i;
+            if (!(m[12] == 0.f && m[13] == 0.f && m[14] == 0.f && m[15] == 1.f))
+                return fail(c, PCL_ERR_UNSUPPORTED, "pcl_upload_skeleton: inverse bind matrix is not affine (row 3 != 0 0 0 1)");
+        }
+        // processing order: bones_map order unless that needs many parked parents, then DFS pre-order
+        std::vector<int32_t> order(J), psrc, store;
+        for (int i = 0; i < J; i++)
+            order[i] = i;
+        int nslot = plan_slots(s.parent, order, &psrc, &store);
+        if (nslot > 12)
+        {
+            std::vector<int32_t> o2, p2, s2;
+            dfs_order(s.parent, &o2);
+            int n2 = plan_slots(s.parent, o2, &p2, &s2);
+            if (n2 < nslot)
+                order = o2, psrc = p2, store = s2, nslot = n2;
+        }
+        if ((size_t)pose_smem_floats_per_warp(nslot) * 4 > (size_t)c->max_smem_optin)
+            return fail(c, PCL_ERR_UNSUPPORTED, "pcl_upload_skeleton: hierarchy needs more parked parents than shared memory holds");
+        s.nslot = nslot;
+        s.order = order;
+        s.pitch = (J + 1 + 1) & ~1; // slots per instance, even => every instance starts on a 32-byte sector
+        std::vector<StepRec> steps(J);
+        for (int st = 0; st < J; st++)
+        {
+            const int b  = order[st];
+            StepRec&  r  = steps[st];
+            r.joint = b, r.psrc = psrc[st], r.store = store[st], r.pad = 0;
+            r.bpos = make_float4(bind_pos[3 * b], bind_pos[3 * b + 1], bind_pos[3 * b + 2], 0.f);
+            r.bscl = make_float4(bind_scl[3 * b], bind_scl[3 * b + 1], bind_scl[3 * b + 2], 0.f);
+            // Node::setOrientation, node.cpp:71-85: NaN -> identity, else normalise (factor = 1/length; q*factor)
+            float w = bind_rot[4 * b], x = bind_rot[4 * b + 1], y = bind_rot[4 * b + 2], z = bind_rot[4 * b + 3];
+            if (std::isnan(w) || std::isnan(x) || std::isnan(y) || std::isnan(z))
+                w = 1.f, x = y = z = 0.f;
+            else
+            {
+                float factor = 1.0f / std::sqrt(w * w + x * x + y * y + z * z);
+                w = w * factor, x = x * factor, y = y * factor, z = z * factor;
+            }
+            r.brot = make_float4(w, x, y, z);
+            const float* m = inv_bind + 16 * (size_t)b;
+            r.ib0 = make_float4(m[0], m[1], m[2], m[3]);
+            r.ib1 = make_float4(m[4], m[5], m[6], m[7]);
+            r.ib2 = make_float4(m[8], m[9], m[10], m[11]);
+        }
+        int rc = upload(c, &s.d_steps, steps);
+        if (rc != PCL_OK)
+            return rc;
+        c->skels.push_back(std::move(s));
+        *out = (pcl_skel)c->skels.size() - 1;
+        return PCL_OK;
+    }
+
+    int pcl_skeleton_bone_count(pcl_ctx* c, pcl_skel s, int32_t* J)
+    {
+        if (!valid_skel(c, s) || !J)
+            return fail(c, PCL_ERR_INVALID, "pcl_skeleton_bone_count: bad handle");
+        *J = c->skels[s].J;
+        return PCL_OK;
+    }
+    int pcl_skeleton_indices(pcl_ctx* c, pcl_skel s, int32_t* out)
+    {
+        if (!valid_skel(c, s) || !out)
+            return fail(c, PCL_ERR_INVALID, "pcl_skeleton_indices: bad handle");
+        for (int i = 0; i < c->skels[s].J; i++)
+            out[i] = c->skels[s].index[i] + 1; // getID() + 1, skeleton.cpp:127
+        return PCL_OK;
+    }
+    int pcl_skeleton_parents(pcl_ctx* c, pcl_skel s, int32_t* out)
+    {
+        if (!valid_skel(c, s) || !out)
+            return fail(c, PCL_ERR_INVALID, "pcl_skeleton_parents: bad handle");
+        std::memcpy(out, c->skels[s].parent.data(), sizeof(int32_t) * c->skels[s].J);
+        return PCL_OK;
+    }
+
+    int pcl_upload_clip(pcl_ctx* c, pcl_skel skel, int32_t total_frame, int32_t node_count, int32_t C, const int32_t* key_counts,
+                        const float* pos, const float* rot, const float* scl, int32_t convert_len, const int32_t* convert,
+                        pcl_clip* out)
+    {
+        if (!valid_skel(c, skel) || !out || C < 0 || node_count < 0 || convert_len < 0 || (C > 0 && !key_counts))
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: bad argument");
+        if (node_count > C)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: node_count exceeds the number of channels");
+        PCL_CK(c, cudaSetDevice(c->device));
+        const int J   = c->skels[skel].J;
+        const int NCH = std::min(node_count, convert_len); // skeleton.cpp:57-59
+        // track offsets
+        std::vector<size_t> op(C + 1, 0), orr(C + 1, 0), os(C + 1, 0);
+        int                 F = 1;
+        for (int n = 0; n < C; n++)
+        {
+            const int np = key_counts[3 * n], nr = key_counts[3 * n + 1], ns = key_counts[3 * n + 2];
+            if (np < 0 || nr < 0 || ns < 0)
+                return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: negative key count");
+            op[n + 1] = op[n] + np, orr[n + 1] = orr[n] + nr, os[n + 1] = os[n] + ns;
+            if (n < NCH)
+                F = std::max(F, std::max(np, std::max(nr, ns)));
+        }
+        std::vector<int32_t> first(J, -1), next(std::max(C, 1), -1), hic(std::max(C, 1), 0), last(J, -1);
+        int                  run = INT_MAX;
+        for (int n = 0; n < NCH; n++)
+        {
+            const int bone = convert[n];
+            if (bone == -1)
+                continue; // size_t(-1) == numeric_limits<size_t>::max(): skipped before the clamp, skeleton.cpp:69-73
+            if (bone < 0 || bone >= J)
+                return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: convert[] entry outside [0,J) (undefined behaviour in the reference)");
+            const int shortest = std::min(key_counts[3 * n], std::min(key_counts[3 * n + 1], key_counts[3 * n + 2]));
+            if (shortest < 1)
+                return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: a played channel has an empty track (the reference would index [-1])");
+            run    = std::min(run, shortest - 1); // carry-over clamp, skeleton.cpp:75-87
+            hic[n] = run;
+            if (first[bone] < 0)
+                first[bone] = n;
+            else
+                next[last[bone]] = n;
+            last[bone] = n;
+        }
+        std::vector<float4> keys((size_t)std::max(C, 1) * F * 3, make_float4(0, 0, 0, 0));
+        for (int n = 0; n < NCH; n++)
+        {
+            for (int k = 0; k < key_counts[3 * n] && k < F; k++)
+            {
+                const float* p = pos + 3 * (op[n] + k);
+                keys[((size_t)n * F + k) * 3 + 0] = make_float4(p[0], p[1], p[2], 0.f);
+            }
+            for (int k = 0; k < key_counts[3 * n + 1] && k < F; k++)
+            {
+                const float* q = rot + 4 * (orr[n] + k);
+                keys[((size_t)n * F + k) * 3 + 1] = make_float4(q[0], q[1], q[2], q[3]);
+            }
+            for (int k = 0; k < key_counts[3 * n + 2] && k < F; k++)
+            {
+                const float* s = scl + 3 * (os[n] + k);
+                keys[((size_t)n * F + k) * 3 + 2] = make_float4(s[0], s[1], s[2], 0.f);
+            }
+        }
+        // one device blob: keys | first | next | hi_clamp
+        const size_t kb = keys.size() * sizeof(float4), fb = (size_t)J * 4, nb = next.size() * 4, hb = hic.size() * 4;
+        auto         up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+        const size_t total = up16(kb) + up16(fb) + up16(nb) + up16(hb);
+        ClipHost     ch;
+        ch.skel = skel;
+        PCL_CK(c, cudaMalloc(&ch.d_blob, total));
+        unsigned char* d = (unsigned char*)ch.d_blob;
+        PCL_CK(c, cudaMemcpy(d, keys.data(), kb, cudaMemcpyHostToDevice));
+        PCL_CK(c, cudaMemcpy(d + up16(kb), first.data(), fb, cudaMemcpyHostToDevice));
+        PCL_CK(c, cudaMemcpy(d + up16(kb) + up16(fb), next.data(), nb, cudaMemcpyHostToDevice));
+        PCL_CK(c, cudaMemcpy(d + up16(kb) + up16(fb) + up16(nb), hic.data(), hb, cudaMemcpyHostToDevice));
+        ch.rec.keys           = (const float4*)d;
+        ch.rec.first_chan     = (const int32_t*)(d + up16(kb));
+        ch.rec.next_chan      = (const int32_t*)(d + up16(kb) + up16(fb));
+        ch.rec.hi_clamp       = (const int32_t*)(d + up16(kb) + up16(fb) + up16(nb));
+        ch.rec.F              = F;
+        ch.rec.total_frame_m1 = total_frame - 1;
+        ch.rec.C              = C;
+        c->clips.push_back(ch);
+        const int id = (int)c->clips.size() - 1;
+        if (id >= c->cap_clips)
+        {
+            const int ncap = std::max(16, c->cap_clips * 2);
+            ClipRec*  nd   = nullptr;
+            PCL_CK(c, cudaStreamSynchronize(c->compute));
+            PCL_CK(c, cudaMalloc((void**)&nd, ncap * sizeof(ClipRec)));
+            std::vector<ClipRec> all;
+            for (auto& x : c->clips)
+                all.push_back(x.rec);
+            PCL_CK(c, cudaMemcpy(nd, all.data(), all.size() * sizeof(ClipRec), cudaMemcpyHostToDevice));
+            cudaFree(c->d_clips);
+            c->d_clips = nd, c->cap_clips = ncap;
+        }
+        else
+            PCL_CK(c, cudaMemcpy(c->d_clips + id, &ch.rec, sizeof(ClipRec), cudaMemcpyHostToDevice));
+        *out = id;
+        return PCL_OK;
+    }
+
+    int pcl_upload_mask(pcl_ctx* c, pcl_skel skel, int32_t J, const int32_t* enabled, pcl_mask* out)
+    {
+        if (!valid_skel(c, skel) || !out || !enabled)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_mask: bad argument");
+        SkelRec& s = c->skels[skel];
+        if (J < s.J)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_mask: mask shorter than the skeleton (animation_system.cpp:122 reads enabled[bone])");
+        PCL_CK(c, cudaSetDevice(c->device));
+        if (s.n_masks >= s.cap_masks)
+        {
+            const int ncap = std::max(8, s.cap_masks * 2);
+            int32_t*  nd   = nullptr;
+            PCL_CK(c, cudaStreamSynchronize(c->compute));
+            PCL_CK(c, cudaMalloc((void**)&nd, (size_t)ncap * s.J * 4));
+            if (s.n_masks)
+                PCL_CK(c, cudaMemcpy(nd, s.d_masks, (size_t)s.n_masks * s.J * 4, cudaMemcpyDeviceToDevice));
+            cudaFree(s.d_masks);
+            s.d_masks = nd, s.cap_masks = ncap;
+        }
+        PCL_CK(c, cudaMemcpy(s.d_masks + (size_t)s.n_masks * s.J, enabled, (size_t)s.J * 4, cudaMemcpyHostToDevice));
+        c->masks.push_back(MaskHost {skel, s.n_masks});
+        s.n_masks++;
+        *out = (pcl_mask)c->masks.size() - 1;
+        return PCL_OK;
+    }
+
+    int pcl_upload_mesh(pcl_ctx* c, int32_t V, const float* pos, const float* nrm, const float* tan, const int32_t* idx4,
+                        const float* w4, int32_t max_slot, pcl_mesh* out)
+    {
+        if (!c || !out || V < 1 || !pos || !idx4 || !w4 || max_slot < 0)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_mesh: bad argument");
+        PCL_CK(c, cudaSetDevice(c->device));
+        MeshRec m;
+        m.V = V, m.Vp = (V + 3) & ~3, m.Vt = (V + LBS_VT - 1) / LBS_VT * LBS_VT, m.max_slot = max_slot;
+        std::vector<float>  hp((size_t)m.Vt * 3, 0.f), hn((size_t)m.Vt * 3, 0.f), ht((size_t)m.Vt * 3, 0.f);
+        std::vector<int4>   hi(m.Vt, make_int4(0, 0, 0, 0));
+        std::vector<float4> hw(m.Vt, make_float4(0, 0, 0, 0));
+        std::memcpy(hp.data(), pos, (size_t)V * 12);
+        if (nrm)
+            std::memcpy(hn.data(), nrm, (size_t)V * 12);
+        if (tan)
+            std::memcpy(ht.data(), tan, (size_t)V * 12);
+        for (int v = 0; v < V; v++)
+        {
+            const float* wr = w4 + 4 * (size_t)v;
+            // RenderResource::updateVertexBuffer, function/render/render_resource.cpp:714-725
+            float inv = wr[0] + wr[1] + wr[2] + wr[3];
+            inv       = (inv != 0.0f) ? 1 / inv : 1.0f;
+            int   id[4];
+            float w[4];
+            for (int k = 0; k < 4; k++)
+            {
+                id[k] = idx4[4 * (size_t)v + k];
+                w[k]  = wr[k] * inv;
+                if (id[k] < 0 || id[k] > max_slot)
+                    return fail(c, PCL_ERR_INVALID, "pcl_upload_mesh: joint index outside [0, max_slot]");
+                // mesh.vert:77-102 gate (weight > 0 && index > 0) folded into the data: a gated influence
+                // becomes (slot 0, weight 0) and contributes an exact zero
+                if (!(w[k] > 0.0f && id[k] > 0))
+                    id[k] = 0, w[k] = 0.f;
+            }
+            hi[v] = make_int4(id[0], id[1], id[2], id[3]);
+            hw[v] = make_float4(w[0], w[1], w[2], w[3]);
+        }
+        int rc;
+        if ((rc = upload(c, &m.d_pos, hp)) || (rc = upload(c, &m.d_nrm, hn)) || (rc = upload(c, &m.d_tan, ht)) ||
+            (rc = upload(c, &m.d_idx, hi)) || (rc = upload(c, &m.d_w, hw)))
+            return rc;
+        c->meshes.push_back(m);
+        *out = (pcl_mesh)c->meshes.size() - 1;
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // instances
+    // ------------------------------------------------------------------------------------------
+    int pcl_batch_create(pcl_ctx* c, pcl_skel skel, int64_t N, int32_t K, pcl_batch** out)
+    {
+        if (!valid_skel(c, skel) || !out || N < 1 || K < 1)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_create: bad argument");
+        if (K > 4)
+            return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_create: at most 4 clip slots per instance");
+        PCL_CK(c, cudaSetDevice(c->device));
+        pcl_batch* b = new pcl_batch();
+        b->ctx = c, b->skel = skel, b->N = N, b->K = K;
+        const size_t   n = (size_t)N * K;
+        const SkelRec& s = c->skels[skel];
+        PCL_CK(c, cudaMalloc((void**)&b->d_clip_ids, n * 4));
+        PCL_CK(c, cudaMalloc((void**)&b->d_mask_ids, n * 4));
+        PCL_CK(c, cudaMalloc((void**)&b->d_phase, n * 4));
+        PCL_CK(c, cudaMalloc((void**)&b->d_weight, n * 4));
+        PCL_CK(c, cudaMalloc((void**)&b->d_len, n * 4));
+        PCL_CK(c, cudaMalloc((void**)&b->d_palette, (size_t)N * s.pitch * 48));
+        std::vector<float> ones(n, 1.f);
+        PCL_CK(c, cudaMemset(b->d_clip_ids, 0, n * 4));
+        PCL_CK(c, cudaMemset(b->d_mask_ids, 0xff, n * 4));
+        PCL_CK(c, cudaMemset(b->d_phase, 0, n * 4));
+        PCL_CK(c, cudaMemcpy(b->d_weight, ones.data(), n * 4, cudaMemcpyHostToDevice));
+        PCL_CK(c, cudaMemcpy(b->d_len, ones.data(), n * 4, cudaMemcpyHostToDevice));
+        PCL_CK(c, cudaMemset(b->d_palette, 0, (size_t)N * s.pitch * 48));
+        *out = b;
+        return PCL_OK;
+    }
+
+    int pcl_batch_destroy(pcl_batch* b)
+    {
+        if (!b)
+            return PCL_ERR_INVALID;
+        cudaSetDevice(b->ctx->device);
+        cudaStreamSynchronize(b->ctx->compute), cudaStreamSynchronize(b->ctx->copy);
+        cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len);
+        cudaFree(b->d_palette), cudaFree(b->d_derived), cudaFree(b->d_export);
+        delete b;
+        return PCL_OK;
+    }
+
+    int pcl_batch_set(pcl_batch* b, int64_t first, int64_t count, const int32_t* clip_ids, const float* phase, const float* weight,
+                      const float* clip_len, const int32_t* mask_ids)
+    {
+        if (!b || first < 0 || count < 0 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_set: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        const int K = b->K;
+        std::vector<int32_t> ti;
+        std::vector<float>   tf;
+        auto put_i = [&](int32_t* dst, const int32_t* src, bool is_mask) -> int {
+            ti.resize((size_t)count * K);
+            for (int64_t i = 0; i < count; i++)
+                for (int k = 0; k < K; k++)
+                {
+                    int32_t v = src[i * K + k];
+                    if (is_mask)
+                    {
+                        if (v >= 0)
+                        {
+                            if (v >= (int)c->masks.size() || c->masks[v].skel != b->skel)
+                                return fail(c, PCL_ERR_INVALID, "pcl_batch_set: mask id does not belong to the batch's skeleton");
+                            v = c->masks[v].local;
+                        }
+                        else
+                            v = -1;
+                    }
+                    else if (v < 0 || v >= (int)c->clips.size() || c->clips[v].skel != b->skel)
+                        return fail(c, PCL_ERR_INVALID, "pcl_batch_set: clip id does not belong to the batch's skeleton");
+                    ti[(size_t)k * count + i] = v;
+                }
+            for (int k = 0; k < K; k++)
+                PCL_CK(c, cudaMemcpyAsync(dst + (size_t)k * b->N + first, ti.data() + (size_t)k * count, (size_t)count * 4,
+                                          cudaMemcpyHostToDevice, c->compute));
+            PCL_CK(c, cudaStreamSynchronize(c->compute));
+            return PCL_OK;
+        };
+        auto put_f = [&](float* dst, const float* src) -> int {
+            if (K == 1)
+            {
+                PCL_CK(c, cudaMemcpyAsync(dst + first, src, (size_t)count * 4, cudaMemcpyHostToDevice, c->compute));
+            }
+            else
+            {
+                tf.resize((size_t)count * K);
+                for (int64_t i = 0; i < count; i++)
+                    for (int k = 0; k < K; k++)
+                        tf[(size_t)k * count + i] = src[i * K + k];
+                for (int k = 0; k < K; k++)
+                    PCL_CK(c, cudaMemcpyAsync(dst + (size_t)k * b->N + first, tf.data() + (size_t)k * count, (size_t)count * 4,
+                                              cudaMemcpyHostToDevice, c->compute));
+            }
+            PCL_CK(c, cudaStreamSynchronize(c->compute));
+            return PCL_OK;
+        };
+        int rc;
+        if (clip_ids && (rc = put_i(b->d_clip_ids, clip_ids, false)))
+            return rc;
+        if (mask_ids && (rc = put_i(b->d_mask_ids, mask_ids, true)))
+            return rc;
+        if (phase && (rc = put_f(b->d_phase, phase)))
+            return rc;
+        if (weight && (rc = put_f(b->d_weight, weight)))
+            return rc;
+        if (clip_len && (rc = put_f(b->d_len, clip_len)))
+            return rc;
+        return PCL_OK;
+    }
+
+    int pcl_batch_get_phases(pcl_batch* b, int64_t first, int64_t count, float* phase)
+    {
+        if (!b || !phase || first < 0 || count < 0 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_get_phases: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        std::vector<float> t((size_t)count * b->K);
+        for (int k = 0; k < b->K; k++)
+            PCL_CK(c, cudaMemcpy(t.data() + (size_t)k * count, b->d_phase + (size_t)k * b->N + first, (size_t)count * 4, cudaMemcpyDeviceToHost));
+        for (int64_t i = 0; i < count; i++)
+            for (int k = 0; k < b->K; k++)
+                phase[i * b->K + k] = t[(size_t)k * count + i];
+        return PCL_OK;
+    }
+
+    int pcl_batch_advance(pcl_batch* b, float dt, int32_t mode)
+    {
+        if (!b || (mode != PCL_ADVANCE_FIRST_ONLY && mode != PCL_ADVANCE_ALL))
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_advance: bad mode");
+        pcl_ctx* c = b->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        const long long total = (mode == PCL_ADVANCE_ALL) ? b->N * b->K : b->N; // slot 0 is row 0 of the [K][N] arrays
+        advance_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->compute>>>(b->d_phase, b->d_len, 0, total, dt);
+        c->launches++;
+        PCL_CK(c, cudaGetLastError());
+        return PCL_OK;
+    }
+
+    static int launch_pose(pcl_batch* b, float dt, int32_t advance)
+    {
+        pcl_ctx* c = b->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        const SkelRec& s = c->skels[b->skel];
+        if (c->clips.empty())
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_pose: no clip uploaded");
+        if (c->copy_pending) // an async palette export may still be reading the palette
+        {
+            PCL_CK(c, cudaStreamWaitEvent(c->compute, c->ev_copy, 0));
+            c->copy_pending = false;
+        }
+        PoseParams p {};
+        p.steps = s.d_steps, p.clips = c->d_clips, p.masks = s.d_masks;
+        p.clip_ids = b->d_clip_ids, p.phase = b->d_phase, p.weight = b->d_weight, p.clip_len = b->d_len;
+        p.mask_ids = (b->K > 1 && s.n_masks > 0) ? b->d_mask_ids : nullptr;
+        p.palette = b->d_palette, p.derived = b->d_derived;
+        p.N = b->N, p.J = s.J, p.pitch = s.pitch, p.nslot = s.nslot;
+        p.n_steps_padded = (s.J + POSE_G - 1) / POSE_G * POSE_G;
+        p.dt = dt, p.advance = advance;
+        const long long warps = (b->N + 31) / 32;
+        const size_t    per_warp = pose_smem_floats_per_warp(s.nslot) * 4;
+        int             wpb = c->opt_pose_wpb;
+        if (wpb == 0) // enough blocks for every SM first, then larger blocks
+            wpb = warps >= 8LL * 4 * c->sm_count ? 4 : (warps >= 8LL * 2 * c->sm_count ? 2 : 1);
+        while (wpb > 1 && per_warp * wpb > (size_t)c->max_smem_optin)
+            wpb >>= 1;
+        const size_t   smem = per_warp * wpb;
+        const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
+#define PCL_LAUNCH_POSE(KK)                                                                                          \
+    {                                                                                                                \
+        PCL_CK(c, cudaFuncSetAttribute(pose_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+        pose_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                    \
+    }
+        switch (b->K)
+        {
+            case 1: PCL_LAUNCH_POSE(1) break;
+            case 2: PCL_LAUNCH_POSE(2) break;
+            case 3: PCL_LAUNCH_POSE(3) break;
+            default: PCL_LAUNCH_POSE(4) break;
+        }
+#undef PCL_LAUNCH_POSE
+        c->launches++;
+        PCL_CK(c, cudaGetLastError());
+        PCL_CK(c, cudaEventRecord(c->ev_pose, c->compute));
+        b->posed = true;
+        return PCL_OK;
+    }
+
+    int pcl_batch_pose(pcl_batch* b)
+    {
+        if (!b)
+            return PCL_ERR_INVALID;
+        return launch_pose(b, 0.f, 0);
+    }
+    int pcl_batch_tick(pcl_batch* b, float dt, int32_t mode)
+    {
+        if (!b || (mode != PCL_ADVANCE_FIRST_ONLY && mode != PCL_ADVANCE_ALL))
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_tick: bad mode");
+        return launch_pose(b, dt, mode);
+    }
+
+    int pcl_batch_keep_derived(pcl_batch* b, int32_t enable)
+    {
+        if (!b)
+            return PCL_ERR_INVALID;
+        pcl_ctx* c = b->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        if (enable && !b->d_derived)
+            PCL_CK(c, cudaMalloc((void**)&b->d_derived, (size_t)b->N * c->skels[b->skel].J * 40));
+        if (!enable && b->d_derived)
+        {
+            cudaFree(b->d_derived);
+            b->d_derived = nullptr;
+        }
+        return PCL_OK;
+    }
+
+    int pcl_skinbuf_create(pcl_ctx* c, pcl_mesh mesh, int64_t capacity, int32_t flags, pcl_skinbuf** out)
+    {
+        if (!c || !out || mesh < 0 || mesh >= (int)c->meshes.size() || capacity < 1 || (flags != PCL_SKIN_POS && flags != PCL_SKIN_POS_NRM_TAN))
+            return fail(c, PCL_ERR_INVALID, "pcl_skinbuf_create: bad argument");
+        PCL_CK(c, cudaSetDevice(c->device));
+        pcl_skinbuf* s = new pcl_skinbuf();
+        s->ctx = c, s->mesh = mesh, s->capacity = capacity, s->flags = flags;
+        s->V = c->meshes[mesh].V, s->Vp = c->meshes[mesh].Vp;
+        cudaError_t e = cudaMalloc((void**)&s->d_pos, (size_t)capacity * s->Vp * 12);
+        if (e == cudaSuccess && flags == PCL_SKIN_POS_NRM_TAN)
+            e = cudaMalloc((void**)&s->d_nt, (size_t)capacity * s->Vp * 24);
+        if (e != cudaSuccess)
+        {
+            cudaFree(s->d_pos);
+            delete s;
+            (void)cudaGetLastError();
+            return fail(c, PCL_ERR_OOM, std::string("pcl_skinbuf_create: ") + cudaGetErrorString(e));
+        }
+        *out = s;
+        return PCL_OK;
+    }
+    int pcl_skinbuf_destroy(pcl_skinbuf* s)
+    {
+        if (!s)
+            return PCL_ERR_INVALID;
+        cudaSetDevice(s->ctx->device);
+        cudaStreamSynchronize(s->ctx->compute);
+        cudaFree(s->d_pos), cudaFree(s->d_nt);
+        delete s;
+        return PCL_OK;
+    }
+
+    int pcl_batch_skin(pcl_batch* b, pcl_mesh mesh, pcl_skinbuf* out, int64_t first, int64_t count, int64_t slot_first)
+    {
+        if (!b || !out)
+            return PCL_ERR_INVALID;
+        pcl_ctx* c = b->ctx;
+        if (out->ctx != c || out->mesh != mesh || mesh < 0 || mesh >= (int)c->meshes.size())
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: skin buffer was created for another mesh / context");
+        if (first < 0 || count < 1 || first + count > b->N || slot_first < 0 || slot_first + count > out->capacity)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: range outside the batch or the ring");
+        if (!b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: pcl_batch_pose / pcl_batch_tick has not run");
+        const SkelRec& s = c->skels[b->skel];
+        const MeshRec& m = c->meshes[mesh];
+        if (m.max_slot > s.J)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: mesh references palette slots the skeleton does not have");
+        PCL_CK(c, cudaSetDevice(c->device));
+        LbsParams p {};
+        p.pos = m.d_pos, p.nrm = m.d_nrm, p.tan = m.d_tan, p.idx = m.d_idx, p.w = m.d_w;
+        p.palette = b->d_palette, p.out_pos = out->d_pos, p.out_nt = out->d_nt;
+        p.first = first, p.count = count, p.slot_first = slot_first;
+        p.V = m.V, p.Vp = m.Vp, p.n_vtiles = m.Vt / LBS_VT, p.pitch = s.pitch;
+        int it = c->opt_lbs_inst_tile;
+        if (it == 0)
+            it = (int)std::max<size_t>(1, std::min<size_t>(16, (48 * 1024) / ((size_t)s.pitch * 48)));
+        while (it > 1 && lbs_smem_bytes(it, s.pitch) > (size_t)c->max_smem_optin)
+            it--;
+        const size_t smem = lbs_smem_bytes(it, s.pitch);
+        if (smem > (size_t)c->max_smem_optin)
+            return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: one palette does not fit in shared memory");
+        p.inst_tile = it;
+        const long long tiles = (count + it - 1) / it;
+        int             vs    = c->opt_lbs_vsplit;
+        if (vs == 0)
+            vs = (int)std::max<long long>(1, std::min<long long>(p.n_vtiles, (16LL * c->sm_count + tiles - 1) / tiles));
+        vs       = std::min(vs, p.n_vtiles);
+        p.vsplit = vs;
+        const unsigned grid = (unsigned)(tiles * vs);
+        const bool     nt   = out->flags == PCL_SKIN_POS_NRM_TAN;
+#define PCL_LAUNCH_LBS(NT_, TMA_)                                                                                          \
+    {                                                                                                                      \
+        PCL_CK(c, cudaFuncSetAttribute(lbs_kernel<NT_, TMA_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+        lbs_kernel<NT_, TMA_><<<grid, LBS_THREADS, smem, c->compute>>>(p);                                                 \
+    }
+        if (nt && c->opt_lbs_variant == 0) PCL_LAUNCH_LBS(true, false)
+        else if (nt) PCL_LAUNCH_LBS(true, true)
+        else if (c->opt_lbs_variant == 0) PCL_LAUNCH_LBS(false, false)
+        else PCL_LAUNCH_LBS(false, true)
+#undef PCL_LAUNCH_LBS
+        c->launches++;
+        PCL_CK(c, cudaGetLastError());
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // readback
+    // ------------------------------------------------------------------------------------------
+    static int export_palette(pcl_batch* b, int64_t first, int64_t count, float* host16, bool async)
+    {
+        if (!b || !host16 || first < 0 || count < 1 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_download_palette: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        if (!b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_download_palette: pcl_batch_pose / pcl_batch_tick has not run");
+        PCL_CK(c, cudaSetDevice(c->device));
+        const SkelRec& s = c->skels[b->skel];
+        if (count > b->export_cap)
+        {
+            PCL_CK(c, cudaStreamSynchronize(c->copy));
+            cudaFree(b->d_export);
+            b->d_export = nullptr, b->export_cap = 0;
+            PCL_CK(c, cudaMalloc((void**)&b->d_export, (size_t)count * s.J * 64));
+            b->export_cap = count;
+        }
+        PCL_CK(c, cudaStreamWaitEvent(c->copy, c->ev_pose, 0));
+        const long long total = count * s.J * 4;
+        export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, b->d_export, first, count, s.J, s.pitch);
+        c->launches++;
+        PCL_CK(c, cudaGetLastError());
+        PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy));
+        c->copy_pending = true;
+        PCL_CK(c, cudaMemcpyAsync(host16, b->d_export, (size_t)count * s.J * 64, cudaMemcpyDeviceToHost, c->copy));
+        if (!async)
+            PCL_CK(c, cudaStreamSynchronize(c->copy));
+        return PCL_OK;
+    }
+    int pcl_batch_download_palette(pcl_batch* b, int64_t first, int64_t count, float* host16)
+    {
+        return export_palette(b, first, count, host16, false);
+    }
+    int pcl_batch_download_palette_async(pcl_batch* b, int64_t first, int64_t count, float* host16)
+    {
+        return export_palette(b, first, count, host16, true);
+    }
+
+    int pcl_batch_download_derived(pcl_batch* b, int64_t first, int64_t count, float* host10)
+    {
+        if (!b || !host10 || first < 0 || count < 1 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_download_derived: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        if (!b->d_derived || !b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_download_derived: enable pcl_batch_keep_derived before posing");
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        const int J = c->skels[b->skel].J;
+        PCL_CK(c, cudaMemcpy(host10, b->d_derived + (size_t)first * J * 10, (size_t)count * J * 40, cudaMemcpyDeviceToHost));
+        return PCL_OK;
+    }
+
+    int pcl_batch_palette_dev(pcl_batch* b, const void** dptr, int32_t* pitch_slots, int32_t* floats_per_slot)
+    {
+        if (!b || !dptr)
+            return PCL_ERR_INVALID;
+        *dptr = b->d_palette;
+        if (pitch_slots)
+            *pitch_slots = b->ctx->skels[b->skel].pitch;
+        if (floats_per_slot)
+            *floats_per_slot = 12;
+        return PCL_OK;
+    }
+
+    int pcl_skinbuf_dev(pcl_skinbuf* s, const void** pos_dev, const void** nt_dev, int32_t* Vp)
+    {
+        if (!s)
+            return PCL_ERR_INVALID;
+        if (pos_dev)
+            *pos_dev = s->d_pos;
+        if (nt_dev)
+            *nt_dev = s->d_nt;
+        if (Vp)
+            *Vp = s->Vp;
+        return PCL_OK;
+    }
+
+    int pcl_skinbuf_download(pcl_skinbuf* s, int64_t slot_first, int64_t count, float* host_pos, float* host_nt)
+    {
+        if (!s || slot_first < 0 || count < 1 || slot_first + count > s->capacity)
+            return fail(s ? s->ctx : nullptr, PCL_ERR_INVALID, "pcl_skinbuf_download: range outside the ring");
+        pcl_ctx* c = s->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        if (host_pos)
+            PCL_CK(c, cudaMemcpy2D(host_pos, (size_t)s->V * 12, s->d_pos + (size_t)slot_first * s->Vp * 3, (size_t)s->Vp * 12,
+                                   (size_t)s->V * 12, (size_t)count, cudaMemcpyDeviceToHost));
+        if (host_nt)
+        {
+            if (!s->d_nt)
+                return fail(c, PCL_ERR_INVALID, "pcl_skinbuf_download: the ring was created without normals/tangents");
+            PCL_CK(c, cudaMemcpy2D(host_nt, (size_t)s->V * 24, s->d_nt + (size_t)slot_first * s->Vp * 6, (size_t)s->Vp * 24,
+                                   (size_t)s->V * 24, (size_t)count, cudaMemcpyDeviceToHost));
+        }
+        return PCL_OK;
+    }
+}

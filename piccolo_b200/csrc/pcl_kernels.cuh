@@ -1,0 +1,578 @@
+// Hand-written sm_100a kernels of the animation + skinning hot path.
+//   pose_kernel<K>   K1-K4 fused: keyframe sampling, (blend,) bind-relative local pose, hierarchy, palette
+//   lbs_kernel<..>   K5: 4-weight linear-blend skinning, TMA-staged streams
+//   export_kernel    compact 3x4 palette -> AnimationResult 4x4 (readback path)
+//   advance_kernel   AnimationComponent::tick phase update
+// Citations are relative to /root/reference/engine/source/runtime.
+#pragma once
+#include "pcl_math.cuh"
+
+#include <cstdint>
+
+namespace pcl
+{
+    // -------------------------------------------------------------------------------------------
+    // device-side asset records
+    // -------------------------------------------------------------------------------------------
+    // One record per processing step (= one bone), in dependency order.  Everything in it is uniform
+    // across a warp, so it is fetched with broadcast loads.
+    struct alignas(16) StepRec
+    {
+        int32_t joint; // bone position in bones_map; palette slot = joint + 1
+        int32_t psrc;  // parent's derived TRS: -1 root, -2 result of the previous step (still in registers), >= 0 smem slot
+        int32_t store; // smem slot to keep this bone's derived TRS in for later children, or -1
+        int32_t pad;
+        float4  bpos, brot, bscl;  // bind TRS (brot = normalised (w,x,y,z)), Node::m_initial_*
+        float4  ib0, ib1, ib2;     // inverse bind rows 0..2 (Node::m_inverse_Tpose)
+    };
+
+    // One uploaded clip+map.  keys: [C][F][3] float4 = {pos.xyz_, rot.wxyz, scl.xyz_} per key, tracks
+    // zero-padded to F keys (the clamp below never reads the padding).
+    struct alignas(16) ClipRec
+    {
+        const float4*  keys;
+        const int32_t* first_chan; // [J]  first played channel driving this bone, or -1
+        const int32_t* next_chan;  // [C]  next played channel driving the same bone, or -1
+        const int32_t* hi_clamp;   // [C]  prefix-min over played channels 0..c of (shortest track length - 1):
+                                   //      the data-parallel form of the carry-over clamp at skeleton.cpp:75-87
+        int32_t F;
+        int32_t total_frame_m1;    // total_frame - 1
+        int32_t C;
+        int32_t pad;
+    };
+
+    struct PoseParams
+    {
+        const StepRec* steps;
+        const ClipRec* clips;
+        const int32_t* masks;    // [n_masks][J]
+        const int32_t* clip_ids; // [K][N]
+        float*         phase;    // [K][N]
+        const float*   weight;   // [K][N]
+        const float*   clip_len; // [K][N]
+        const int32_t* mask_ids; // [K][N]  (-1 = all enabled)
+        float4*        palette;  // [N][pitch][3]
+        float*         derived;  // [N][J][10] or nullptr
+        long long      N;
+        int32_t        J, pitch, nslot, n_steps_padded;
+        float          dt;
+        int32_t        advance; // 0, PCL_ADVANCE_FIRST_ONLY, PCL_ADVANCE_ALL
+    };
+
+    constexpr int POSE_G = 4; // bones staged in shared memory between two coalesced palette flushes
+
+    // per-warp dynamic shared memory, in floats
+    __host__ __device__ inline size_t pose_smem_floats_per_warp(int nslot) { return (size_t)nslot * 10 * 32 + 32 * (POSE_G * 12 + 4); }
+
+    struct SlotState // one clip slot of one instance, resident in registers
+    {
+        const float4*  keys;
+        const int32_t* first;
+        const int32_t* next;
+        const int32_t* hic;
+        int32_t        F, lo, hi, mask_off;
+        float          r, w;
+    };
+
+    // skeleton.cpp:75-95 for one channel of one instance
+    __device__ __forceinline__ void sample_channel(const SlotState& st, int chan, float3& P, float3& S, Quat& Q)
+    {
+        int hc = __ldg(st.hic + chan);
+        int h  = max(min(st.hi, hc), 0);
+        int l  = max(min(st.lo, h), 0);
+        const float4* kl = st.keys + ((size_t)chan * st.F + l) * 3;
+        const float4* kh = st.keys + ((size_t)chan * st.F + h) * 3;
+        float4 p0 = __ldg(kl), q0 = __ldg(kl + 1), s0 = __ldg(kl + 2);
+        float4 p1 = __ldg(kh), q1 = __ldg(kh + 1), s1 = __ldg(kh + 2);
+        P = lerp3(make_float3(p0.x, p0.y, p0.z), make_float3(p1.x, p1.y, p1.z), st.r);
+        S = lerp3(make_float3(s0.x, s0.y, s0.z), make_float3(s1.x, s1.y, s1.z), st.r);
+        Q = qnlerp(st.r, Quat {q0.x, q0.y, q0.z, q0.w}, Quat {q1.x, q1.y, q1.z, q1.w});
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // pose kernel: lane = instance, the warp walks the bones in dependency order.
+    //   - clip keys: 128-bit read-only loads (the whole clip is L1/L2 resident, shared by all instances)
+    //   - parent lookups: registers when the parent was the previous step, else a per-warp shared-memory
+    //     slot [slot][component][lane] (conflict-free); slots are recycled once a bone's last child is done
+    //   - palette rows are staged [lane][bone] in shared memory and flushed as coalesced 128-bit stores
+    //     (a run of POSE_G consecutive slots of one instance is contiguous in HBM)
+    // -------------------------------------------------------------------------------------------
+    template<int K>
+    __global__ void __launch_bounds__(256) pose_kernel(const PoseParams par)
+    {
+        extern __shared__ __align__(16) float smem[];
+        const int       lane  = threadIdx.x & 31;
+        const int       wib   = threadIdx.x >> 5;
+        const long long wglob = (long long)blockIdx.x * (blockDim.x >> 5) + wib;
+        const long long inst0 = wglob * 32;
+        if (inst0 >= par.N)
+            return;
+        const long long inst   = min(inst0 + lane, par.N - 1); // idle lanes shadow the last instance, never store
+        const bool      active = (inst0 + lane) < par.N;
+        float*          slots  = smem + (size_t)wib * pose_smem_floats_per_warp(par.nslot);
+        float*          stage  = slots + (size_t)par.nslot * 10 * 32;
+        constexpr int   SROW   = POSE_G * 12 + 4; // floats per staged instance row (+4: conflict-free float4 columns)
+
+        // ---- per-instance clip slot state (A1 + head of A3) -----------------------------------
+        SlotState st[K];
+#pragma unroll
+        for (int k = 0; k < K; k++)
+        {
+            const size_t  o  = (size_t)k * par.N + inst;
+            const ClipRec cr = par.clips[__ldg(par.clip_ids + o)];
+            float         ph = par.phase[o];
+            if (par.advance == 2 || (par.advance == 1 && k == 0))
+            {
+                // AnimationComponent::tick, function/framework/component/animation/animation_component.cpp:19-21
+                ph += par.dt / __ldg(par.clip_len + o);
+                ph -= floorf(ph);
+                if (active)
+                    par.phase[o] = ph;
+            }
+            // skeleton.cpp:52-55 (computed once per clip, before any clamping)
+            float exact = ph * (float)cr.total_frame_m1;
+            st[k].lo    = (int)floorf(exact);
+            st[k].hi    = (int)ceilf(exact);
+            st[k].r     = exact - (float)st[k].lo;
+            st[k].keys = cr.keys, st[k].first = cr.first_chan, st[k].next = cr.next_chan, st[k].hic = cr.hi_clamp;
+            st[k].F = cr.F;
+            st[k].w = (K > 1) ? __ldg(par.weight + o) : 1.0f;
+            int mid = (K > 1 && par.mask_ids) ? __ldg(par.mask_ids + o) : -1;
+            st[k].mask_off = mid < 0 ? -1 : mid * par.J;
+        }
+
+        // slot 0 of the palette is the identity (mesh_component.cpp:72-79)
+        if (active)
+        {
+            float4* p0 = par.palette + (size_t)inst * par.pitch * 3;
+            p0[0] = make_float4(1, 0, 0, 0), p0[1] = make_float4(0, 1, 0, 0), p0[2] = make_float4(0, 0, 1, 0);
+        }
+
+        TRS prev; // derived TRS of the previous step
+        prev.p = make_float3(0, 0, 0), prev.q = Quat {1, 0, 0, 0}, prev.s = make_float3(1, 1, 1);
+
+        for (int s0 = 0; s0 < par.n_steps_padded; s0 += POSE_G)
+        {
+#pragma unroll
+            for (int g = 0; g < POSE_G; g++)
+            {
+                const int s = s0 + g;
+                if (s >= par.J)
+                    break;
+                const StepRec* rec  = par.steps + s;
+                const int4     hdr  = __ldg(reinterpret_cast<const int4*>(rec));
+                const int      bone = hdr.x;
+                const float4   bp = __ldg(&rec->bpos), br = __ldg(&rec->brot), bs = __ldg(&rec->bscl);
+                // resetSkeleton -> Node::resetToInitialPose, skeleton.cpp:45, node.cpp:197-206
+                TRS loc;
+                loc.p = make_float3(bp.x, bp.y, bp.z), loc.q = Quat {br.x, br.y, br.z, br.w}, loc.s = make_float3(bs.x, bs.y, bs.z);
+
+                if (K == 1)
+                {
+                    // the reference's executed path: every played channel of this bone, in channel order
+                    // (skeleton.cpp:57-105); rotate(LOCAL) node.cpp:135-157, scale :182-186, translate(AREN) :107-132
+                    int chan = __ldg(st[0].first + bone);
+                    while (chan >= 0)
+                    {
+                        float3 P, S;
+                        Quat   Q;
+                        sample_channel(st[0], chan, P, S, Q);
+                        loc.q = qmul(loc.q, qnormalise(Q));
+                        loc.s = loc.s * S;
+                        loc.p = loc.p + P;
+                        chan  = __ldg(st[0].next + chan);
+                    }
+                }
+                else
+                {
+                    // documented blend extension; weights as animation_system.cpp:117-149
+                    float wsum = 0.f;
+                    bool  en[K];
+#pragma unroll
+                    for (int k = 0; k < K; k++)
+                    {
+                        en[k] = st[k].mask_off < 0 ? true : (__ldg(par.masks + st[k].mask_off + bone) != 0);
+                        if (en[k])
+                            wsum += st[k].w;
+                    }
+                    TRS  acc;
+                    Quat qref {1, 0, 0, 0};
+                    bool any = false, touched = false;
+                    acc.p = make_float3(0, 0, 0), acc.q = Quat {0, 0, 0, 0}, acc.s = make_float3(0, 0, 0);
+#pragma unroll
+                    for (int k = 0; k < K; k++)
+                    {
+                        float wn   = en[k] ? st[k].w / wsum : 0.f;
+                        int   chan = __ldg(st[k].first + bone);
+                        bool  has  = false;
+                        TRS   d;
+                        d.p = make_float3(0, 0, 0), d.q = Quat {1, 0, 0, 0}, d.s = make_float3(1, 1, 1);
+                        while (chan >= 0)
+                        {
+                            float3 P, S;
+                            Quat   Q;
+                            sample_channel(st[k], chan, P, S, Q);
+                            if (!has)
+                                d.p = P, d.s = S, d.q = Q, has = true;
+                            else
+                                d.p = d.p + P, d.s = d.s * S, d.q = qmul(d.q, Q);
+                            chan = __ldg(st[k].next + chan);
+                        }
+                        touched |= has;
+                        if (fabsf(wsum) >= 0.0001f && wn != 0.f)
+                        {
+                            if (!any)
+                            {
+                                qref  = d.q;
+                                acc.p = wn * d.p, acc.s = wn * d.s, acc.q = qscale(d.q, wn);
+                                any   = true;
+                            }
+                            else
+                            {
+                                float sg = (qdot(d.q, qref) < 0.0f) ? -wn : wn;
+                                acc.p = acc.p + wn * d.p, acc.s = acc.s + wn * d.s;
+                                acc.q = Quat {acc.q.w + d.q.w * sg, acc.q.x + d.q.x * sg, acc.q.y + d.q.y * sg, acc.q.z + d.q.z * sg};
+                            }
+                        }
+                    }
+                    if (any && touched)
+                    {
+                        loc.q = qmul(loc.q, qnormalise(acc.q));
+                        loc.s = loc.s * acc.s;
+                        loc.p = loc.p + acc.p;
+                    }
+                }
+
+                // m_bones[i].update(), skeleton.cpp:110-113 -> Node::updateDerivedTransform node.cpp:32-65
+                TRS der;
+                if (hdr.y == -1)
+                    der = loc;
+                else
+                {
+                    TRS par_trs = prev;
+                    if (hdr.y >= 0)
+                    {
+                        const float* sp = slots + (size_t)hdr.y * 320 + lane;
+                        par_trs.p = make_float3(sp[0], sp[32], sp[64]);
+                        par_trs.q = Quat {sp[96], sp[128], sp[160], sp[192]};
+                        par_trs.s = make_float3(sp[224], sp[256], sp[288]);
+                    }
+                    der = compose(par_trs, loc);
+                }
+                if (hdr.z >= 0)
+                {
+                    float* sp = slots + (size_t)hdr.z * 320 + lane;
+                    sp[0] = der.p.x, sp[32] = der.p.y, sp[64] = der.p.z;
+                    sp[96] = der.q.w, sp[128] = der.q.x, sp[160] = der.q.y, sp[192] = der.q.z;
+                    sp[224] = der.s.x, sp[256] = der.s.y, sp[288] = der.s.z;
+                }
+                prev = der;
+                if (par.derived && active)
+                {
+                    float* o = par.derived + ((size_t)inst * par.J + bone) * 10;
+                    o[0] = der.p.x, o[1] = der.p.y, o[2] = der.p.z, o[3] = der.q.w, o[4] = der.q.x;
+                    o[5] = der.q.y, o[6] = der.q.z, o[7] = der.s.x, o[8] = der.s.y, o[9] = der.s.z;
+                }
+
+                // outputAnimationResult, skeleton.cpp:119-156
+                float4 r0, r1, r2;
+                palette_rows(der, __ldg(&rec->ib0), __ldg(&rec->ib1), __ldg(&rec->ib2), r0, r1, r2);
+                float4* row = reinterpret_cast<float4*>(stage + (size_t)lane * SROW + g * 12);
+                row[0] = r0, row[1] = r1, row[2] = r2;
+            }
+            __syncwarp();
+            // coalesced flush: 32 instances x POSE_G bones x 3 float4
+#pragma unroll
+            for (int it = 0; it < POSE_G * 3; it++)
+            {
+                const int f  = it * 32 + lane;
+                const int il = f / (POSE_G * 3);
+                const int rm = f % (POSE_G * 3);
+                const int g  = rm / 3;
+                const int s  = s0 + g;
+                if (s < par.J && inst0 + il < par.N)
+                {
+                    const int    bone = __ldg(&par.steps[s].joint);
+                    const float4 v    = *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
+                    par.palette[((size_t)(inst0 + il) * par.pitch + bone + 1) * 3 + (rm - g * 3)] = v;
+                }
+            }
+            __syncwarp();
+        }
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // phase update alone (pcl_batch_advance), animation_component.cpp:19-21
+    // -------------------------------------------------------------------------------------------
+    __global__ void advance_kernel(float* phase, const float* clip_len, long long n_first, long long n_total, float dt)
+    {
+        long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n_total)
+            return;
+        (void)n_first;
+        float ph = phase[i];
+        ph += dt / clip_len[i];
+        ph -= floorf(ph);
+        phase[i] = ph;
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // readback helper: compact palette [N][pitch][3] float4 -> AnimationResult [count][J][16]
+    // (Matrix4x4::toMatrix4x4_, core/math/matrix4.h:98-119; row 3 = 0 0 0 1)
+    // -------------------------------------------------------------------------------------------
+    __global__ void export_kernel(const float4* __restrict__ palette, float4* __restrict__ out, long long first,
+                                  long long count, int J, int pitch)
+    {
+        long long t     = (long long)blockIdx.x * blockDim.x + threadIdx.x; // one thread per output float4
+        long long total = count * J * 4;
+        if (t >= total)
+            return;
+        int       r = (int)(t & 3);
+        long long e = t >> 2;
+        long long i = e / J;
+        int       b = (int)(e - i * J);
+        out[t] = (r == 3) ? make_float4(0, 0, 0, 1) : palette[((size_t)(first + i) * pitch + b + 1) * 3 + r];
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // K5: linear-blend skinning, engine/shader/glsl/mesh.vert:72-111
+    // -------------------------------------------------------------------------------------------
+    struct LbsParams
+    {
+        const float*  pos;  // [Vt][3]   Vt = V rounded up to LBS_VT (zero padded)
+        const float*  nrm;  // [Vt][3]
+        const float*  tan;  // [Vt][3]
+        const int4*   idx;  // [Vt]      palette slots, gated to 0 where the shader's test fails
+        const float4* w;    // [Vt]      renormalised weights, 0 where gated
+        const float4* palette;
+        float*        out_pos; // [cap][Vp][3]
+        float*        out_nt;  // [cap][Vp][6]
+        long long     first, count, slot_first;
+        int32_t       V, Vp, n_vtiles, pitch, inst_tile, vsplit;
+    };
+
+    constexpr int LBS_VT      = 256; // vertices per tile = threads per CTA (one vertex per thread)
+    constexpr int LBS_THREADS = 256;
+
+    __host__ __device__ inline size_t lbs_smem_bytes(int inst_tile, int pitch)
+    {
+        return (size_t)inst_tile * pitch * 48      // palette tile
+               + LBS_VT * (36 + 32)                // vertex streams: pos, nrm, tan, idx4, w4
+               + (LBS_THREADS / 32) * 2 * 1152     // per-warp double-buffered output staging
+               + 64;                               // mbarriers
+    }
+
+    __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+    __device__ __forceinline__ void     mbar_init(uint64_t* bar, int count)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    }
+    __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+    {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    }
+    __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+    {
+        asm volatile("{\n"
+                     ".reg .pred p;\n"
+                     "W_%=:\n"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                     "@p bra D_%=;\n"
+                     "bra W_%=;\n"
+                     "D_%=:\n"
+                     "}" ::"r"(smem_u32(bar)),
+                     "r"(parity)
+                     : "memory");
+    }
+    // TMA bulk copy global -> shared (1-D, no tensor map); completes on the mbarrier.  SASS: UBLKCP
+    __device__ __forceinline__ void tma_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+    {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                     "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                     : "memory");
+    }
+    // TMA bulk copy shared -> global
+    __device__ __forceinline__ void tma_store(void* dst, const void* src, uint32_t bytes)
+    {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+    }
+    __device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+    template<int N>
+    __device__ __forceinline__ void tma_wait_read()
+    {
+        asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+    }
+    __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+    // CTA = (instance tile, vertex split).  The instance tile's palettes (one contiguous block of the
+    // compact palette) are brought into shared memory by ONE TMA bulk copy; each vertex tile's five
+    // streams by five more, prefetched one tile ahead (the tile is consumed into registers at once, so a
+    // single shared buffer double-buffers against registers).  thread = vertex, loop over the tile's
+    // instances: palette rows are gathered from shared memory with 128-bit loads (lanes bound to the same
+    // bone broadcast), results are staged per warp and leave either as coalesced 128-bit stores
+    // (STORE_TMA = false) or as TMA bulk stores of the warp's contiguous 384 B + 768 B runs (true).
+    template<bool NT, bool STORE_TMA>
+    __global__ void __launch_bounds__(LBS_THREADS, 2) lbs_kernel(const LbsParams par)
+    {
+        extern __shared__ __align__(128) unsigned char lsm[];
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const int tile  = blockIdx.x / par.vsplit;
+        const int split = blockIdx.x - tile * par.vsplit;
+        const long long i0 = (long long)tile * par.inst_tile; // first instance of this tile, relative to par.first
+        const int       ni = (int)min((long long)par.inst_tile, par.count - i0);
+
+        float4*        pal_s  = reinterpret_cast<float4*>(lsm);
+        unsigned char* vbuf   = lsm + (size_t)par.inst_tile * par.pitch * 48;
+        float*         vpos   = reinterpret_cast<float*>(vbuf);
+        float*         vnrm   = vpos + LBS_VT * 3;
+        float*         vtan   = vnrm + LBS_VT * 3;
+        int4*          vidx   = reinterpret_cast<int4*>(vtan + LBS_VT * 3);
+        float4*        vw     = reinterpret_cast<float4*>(vidx + LBS_VT);
+        float*         ostage = reinterpret_cast<float*>(vbuf + LBS_VT * 68) + (size_t)warp * 2 * 288;
+        uint64_t*      bars   = reinterpret_cast<uint64_t*>(vbuf + LBS_VT * 68 + (LBS_THREADS / 32) * 2 * 1152);
+
+        // vertex tiles of this split
+        const int per   = (par.n_vtiles + par.vsplit - 1) / par.vsplit;
+        const int vt_lo = split * per, vt_hi = min(par.n_vtiles, vt_lo + per);
+        if (vt_lo >= vt_hi)
+            return;
+
+        auto issue_vtile = [&](int vt) {
+            const size_t v0 = (size_t)vt * LBS_VT;
+            mbar_expect_tx(&bars[1], LBS_VT * 68);
+            tma_load(vpos, par.pos + v0 * 3, LBS_VT * 12, &bars[1]);
+            tma_load(vnrm, par.nrm + v0 * 3, LBS_VT * 12, &bars[1]);
+            tma_load(vtan, par.tan + v0 * 3, LBS_VT * 12, &bars[1]);
+            tma_load(vidx, par.idx + v0, LBS_VT * 16, &bars[1]);
+            tma_load(vw, par.w + v0, LBS_VT * 16, &bars[1]);
+        };
+
+        if (tid == 0)
+        {
+            mbar_init(&bars[0], 1);
+            mbar_init(&bars[1], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (tid == 0)
+        {
+            const uint32_t pbytes = (uint32_t)ni * par.pitch * 48;
+            mbar_expect_tx(&bars[0], pbytes);
+            tma_load(pal_s, par.palette + (size_t)(par.first + i0) * par.pitch * 3, pbytes, &bars[0]);
+            issue_vtile(vt_lo);
+        }
+        mbar_wait(&bars[0], 0);
+
+        uint32_t vphase = 0;
+        int      obuf   = 0;
+        for (int vt = vt_lo; vt < vt_hi; vt++)
+        {
+            mbar_wait(&bars[1], vphase);
+            vphase ^= 1;
+            const int    v  = vt * LBS_VT + tid;
+            const float3 p  = make_float3(vpos[tid * 3], vpos[tid * 3 + 1], vpos[tid * 3 + 2]);
+            float3       n  = make_float3(0, 0, 0), t = make_float3(0, 0, 0);
+            if (NT)
+            {
+                n = make_float3(vnrm[tid * 3], vnrm[tid * 3 + 1], vnrm[tid * 3 + 2]);
+                t = make_float3(vtan[tid * 3], vtan[tid * 3 + 1], vtan[tid * 3 + 2]);
+            }
+            const int4   id = vidx[tid];
+            const float4 w  = vw[tid];
+            __syncthreads(); // everyone holds its vertex in registers: the buffer is free again
+            if (tid == 0 && vt + 1 < vt_hi)
+                issue_vtile(vt + 1);
+
+            // influences nobody in the warp uses are skipped (warp-uniform)
+            const bool a1 = __any_sync(0xffffffffu, w.y != 0.f), a2 = __any_sync(0xffffffffu, w.z != 0.f),
+                       a3 = __any_sync(0xffffffffu, w.w != 0.f);
+            const int  o0 = id.x * 3, o1 = id.y * 3, o2 = id.z * 3, o3 = id.w * 3;
+            const int  wv0    = vt * LBS_VT + warp * 32;            // first vertex of this warp
+            const int  nvalid = min(32, par.Vp - wv0);              // vertices (incl. <= 3 pad) this warp stores
+            if (nvalid <= 0)
+                continue;
+
+            for (int i = 0; i < ni; i++)
+            {
+                const float4* P = pal_s + (size_t)i * par.pitch * 3;
+                // vertex_blending_matrix = sum_k joint_matrices[idx_k] * w_k (mesh.vert:77-102); a gated
+                // influence has idx = 0, w = 0 and adds an exact zero
+                float4 m0 = P[o0], m1 = P[o0 + 1], m2 = P[o0 + 2];
+                float4 b0 = make_float4(m0.x * w.x, m0.y * w.x, m0.z * w.x, m0.w * w.x);
+                float4 b1 = make_float4(m1.x * w.x, m1.y * w.x, m1.z * w.x, m1.w * w.x);
+                float4 b2 = make_float4(m2.x * w.x, m2.y * w.x, m2.z * w.x, m2.w * w.x);
+#define PCL_ACC(o, ww)                                                                               \
+    {                                                                                                \
+        m0 = P[o], m1 = P[o + 1], m2 = P[o + 2];                                                     \
+        b0.x += m0.x * ww, b0.y += m0.y * ww, b0.z += m0.z * ww, b0.w += m0.w * ww;                  \
+        b1.x += m1.x * ww, b1.y += m1.y * ww, b1.z += m1.z * ww, b1.w += m1.w * ww;                  \
+        b2.x += m2.x * ww, b2.y += m2.y * ww, b2.z += m2.z * ww, b2.w += m2.w * ww;                  \
+    }
+                if (a1) PCL_ACC(o1, w.y)
+                if (a2) PCL_ACC(o2, w.z)
+                if (a3) PCL_ACC(o3, w.w)
+#undef PCL_ACC
+                // model_position = (B * vec4(p, 1)).xyz (mesh.vert:104)
+                const float px = b0.x * p.x + b0.y * p.y + b0.z * p.z + b0.w;
+                const float py = b1.x * p.x + b1.y * p.y + b1.z * p.z + b1.w;
+                const float pz = b2.x * p.x + b2.y * p.y + b2.z * p.z + b2.w;
+                float*      os = ostage + obuf * 288;
+                if (STORE_TMA)
+                {
+                    if (lane == 0)
+                        tma_wait_read<1>(); // the bulk store issued from this buffer two instances ago has read it
+                    __syncwarp();
+                }
+                os[lane * 3] = px, os[lane * 3 + 1] = py, os[lane * 3 + 2] = pz;
+                if (NT)
+                {
+                    // normalize(mat3(B) * n), normalize(mat3(B) * t) (mesh.vert:106-110)
+                    float nx = b0.x * n.x + b0.y * n.y + b0.z * n.z, ny = b1.x * n.x + b1.y * n.y + b1.z * n.z,
+                          nz = b2.x * n.x + b2.y * n.y + b2.z * n.z;
+                    float tx = b0.x * t.x + b0.y * t.y + b0.z * t.z, ty = b1.x * t.x + b1.y * t.y + b1.z * t.z,
+                          tz = b2.x * t.x + b2.y * t.y + b2.z * t.z;
+                    const float rn = 1.0f / sqrtf(nx * nx + ny * ny + nz * nz);
+                    const float rt = 1.0f / sqrtf(tx * tx + ty * ty + tz * tz);
+                    float2*     on = reinterpret_cast<float2*>(os + 96 + lane * 6);
+                    on[0] = make_float2(nx * rn, ny * rn), on[1] = make_float2(nz * rn, tx * rt), on[2] = make_float2(ty * rt, tz * rt);
+                }
+                const size_t slot = (size_t)(par.slot_first + i0 + i);
+                float*       gp   = par.out_pos + (slot * par.Vp + wv0) * 3;
+                float*       gn   = NT ? par.out_nt + (slot * par.Vp + wv0) * 6 : nullptr;
+                if (STORE_TMA)
+                {
+                    fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0)
+                    {
+                        tma_store(gp, os, nvalid * 12);
+                        if (NT)
+                            tma_store(gn, os + 96, nvalid * 24);
+                        tma_commit();
+                    }
+                }
+                else
+                {
+                    __syncwarp();
+                    const float4* s4 = reinterpret_cast<const float4*>(os);
+                    if (lane * 4 < nvalid * 3)
+                        reinterpret_cast<float4*>(gp)[lane] = s4[lane];
+                    if (NT)
+                    {
+                        if (lane * 4 < nvalid * 6)
+                            reinterpret_cast<float4*>(gn)[lane] = s4[24 + lane];
+                        if ((lane + 32) * 4 < nvalid * 6)
+                            reinterpret_cast<float4*>(gn)[lane + 32] = s4[24 + 32 + lane];
+                    }
+                }
+                obuf ^= 1;
+            }
+        }
+        if (STORE_TMA)
+        {
+            if (lane == 0)
+                tma_wait_read<0>();
+            __syncwarp();
+        }
+    }
+} // namespace pcl

@@ -1,0 +1,393 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the reference-generated goldens.
+
+Tolerances (SURVEY.md section 0.7 / BASELINE.md section 3.5):
+  joint matrices     max|d| <= 1e-5 * max(1, max|M_ref|)   per joint matrix
+  skinned positions  |dp|   <= 1e-4 * max(1, bounding radius of the reference positions)
+  normals/tangents   |dn|   <= 1e-4 (unit vectors)
+  indices / ordering / phases: bit-exact
+"""
+import os
+
+import numpy as np
+import pytest
+
+from piccolo_b200 import assets as A
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+MAT_TOL = 1e-5
+POS_TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from piccolo_b200 import capi
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def player_dev(ctx, player):
+    sk, cl, am, mk = player
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    return skel, clip
+
+
+def assert_mats_close(got, ref, tol=MAT_TOL):
+    got, ref = got.reshape(-1, 16), ref.reshape(-1, 16)
+    scale = np.maximum(1.0, np.abs(ref).max(axis=1))
+    err = np.abs(got.astype(np.float64) - ref.astype(np.float64)).max(axis=1) / scale
+    assert np.all(np.isfinite(got)), "non-finite palette entries"
+    assert err.max() <= tol, "joint-matrix error %.3g > %.1g at flat joint %d" % (err.max(), tol, int(err.argmax()))
+    return float(err.max())
+
+
+def gpu_pose(ctx, skel, clip_ids, phases, weight=None, mask_ids=None, derived=False, tick=None):
+    clip_ids = np.asarray(clip_ids, np.int32)
+    clip_ids = clip_ids.reshape(len(clip_ids), -1)
+    N, K = clip_ids.shape
+    b = ctx.batch(skel, N, K)
+    try:
+        b.set(clip_ids=clip_ids, phase=np.asarray(phases, np.float32).reshape(N, K), weight=weight, mask_ids=mask_ids)
+        if derived:
+            b.keep_derived(True)
+        b.pose()
+        mats = b.download_palette()
+        return (mats, b.download_derived()) if derived else mats
+    finally:
+        b.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# pose: goldens produced by the reference's own Skeleton code
+# ------------------------------------------------------------------------------------------------
+def test_pose_reference_goldens(ctx, player_dev):
+    skel, clip = player_dev
+    g = np.load(os.path.join(GOLDEN, "pose_golden.npz"))
+    ph = g["phases"]
+    mats, der = gpu_pose(ctx, skel, np.full((len(ph), 1), clip), ph, derived=True)
+    assert_mats_close(mats, g["mats"])
+    assert np.array_equal(mats[..., 12:], np.broadcast_to(np.float32([0, 0, 0, 1]), mats[..., 12:].shape))
+    assert np.array_equal(ctx.skeleton_indices(skel), g["index"])  # bit-exact, bones_map order
+    d = np.abs(der[g["derived_phase_idx"]] - g["derived"]).max()
+    assert d <= 1e-5, "derived TRS error %.3g" % d
+    # the root is exactly the identity in the reference
+    assert np.array_equal(mats[:, 0], np.broadcast_to(np.eye(4, dtype=np.float32).reshape(16), (len(ph), 16)))
+
+
+def test_pose_clamp_carry_over(ctx, player):
+    g = np.load(os.path.join(GOLDEN, "clamp_golden.npz"))
+    sk, cl, am, mk = A.load_player()
+    for ch, track, keep in g["cut"]:
+        tr = (cl.pos_keys, cl.rot_keys, cl.scl_keys)[track]
+        tr[ch] = tr[ch][:keep].copy()
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    mats = gpu_pose(ctx, skel, np.full((len(g["phases"]), 1), clip), g["phases"])
+    assert_mats_close(mats, g["mats"])
+
+
+def test_tick_sequence_matches_animation_component(ctx, player_dev):
+    """200 x AnimationComponent::tick: phases bit-exact, palettes within tolerance."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    g = np.load(os.path.join(GOLDEN, "tick_golden.npz"))
+    b = ctx.batch(skel, 3, 1)
+    b.set(clip_ids=np.full((3, 1), clip, np.int32), phase=np.zeros((3, 1), np.float32),
+          clip_len=np.full((3, 1), g["clip_len"], np.float32))
+    want = dict(zip(g["mats_tick_idx"].tolist(), g["mats"]))
+    for t in range(len(g["phases"])):
+        if t % 2:
+            b.tick(float(g["dt"]), capi.PCL_ADVANCE_FIRST_ONLY)  # fused advance + pose
+        else:
+            b.advance(float(g["dt"]), capi.PCL_ADVANCE_FIRST_ONLY)  # separate kernels
+            b.pose()
+        ph = b.phases()
+        assert np.all(ph == g["phases"][t]), "phase diverged at tick %d" % t
+        if t in want:
+            assert_mats_close(b.download_palette()[1], want[t])
+    b.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# pose: against the oracle on seeded inputs
+# ------------------------------------------------------------------------------------------------
+def test_pose_config2_10k_single_clip(ctx, player_dev, oracle, player):
+    skel, clip = player_dev
+    sk, cl, am, mk = player
+    N = 10000
+    ph = np.modf(np.arange(N, dtype=np.float64) * 0.6180339887)[0].astype(np.float32)
+    mats = gpu_pose(ctx, skel, np.full((N, 1), clip), ph)
+    ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((N, 1), np.int32), ph)
+    assert_mats_close(mats, ref)
+
+
+@pytest.mark.parametrize("N", [1, 31, 33, 1000, 4097])
+def test_pose_ragged_batch_sizes(ctx, player_dev, oracle, player, N):
+    skel, clip = player_dev
+    sk, cl, am, mk = player
+    ph = np.random.default_rng(N).uniform(0, 1, N).astype(np.float32)
+    for wpb in (1, 2, 4, 8):
+        ctx.set_option("pose_warps_per_block", wpb)
+        mats = gpu_pose(ctx, skel, np.full((N, 1), clip), ph)
+        ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((N, 1), np.int32), ph)
+        assert_mats_close(mats, ref)
+    ctx.set_option("pose_warps_per_block", 0)
+
+
+def _variants(cl, frames=(17, 23, 29, 31, 37, 41, 47)):
+    return [cl] + [A.make_variant_clip(cl, f, seed=100 + i) for i, f in enumerate(frames)]
+
+
+def test_pose_config4_mixed_clips_random_phases(ctx, oracle, player):
+    sk, cl, am, mk = player
+    clips = _variants(cl)
+    skel = ctx.upload_skeleton(sk)
+    ids = [ctx.upload_clip(skel, c, am) for c in clips]
+    N = 20000
+    rng = np.random.default_rng(7)
+    pick = rng.integers(0, len(clips), N)
+    ph = rng.uniform(0, 1, N).astype(np.float32)
+    mats = gpu_pose(ctx, skel, np.asarray(ids, np.int32)[pick].reshape(N, 1), ph)
+    sv = oracle.skeleton(sk)
+    ref = oracle.pose_batch(sv, [oracle.clip(c, am) for c in clips], pick.reshape(N, 1).astype(np.int32), ph)
+    assert_mats_close(mats, ref)
+
+
+@pytest.mark.parametrize("K", [2, 3, 4])
+def test_pose_blend_extension_vs_oracle(ctx, oracle, player, K):
+    """Multi-clip blend (no executed reference counterpart; oracle = documented semantics A4)."""
+    sk, cl, am, mk = player
+    clips = _variants(cl, frames=(17, 29, 41))
+    skel = ctx.upload_skeleton(sk)
+    ids = np.asarray([ctx.upload_clip(skel, c, am) for c in clips], np.int32)
+    rng = np.random.default_rng(K)
+    masks = np.ones((3, sk.J), np.int32)
+    masks[1, rng.choice(sk.J, 20, replace=False)] = 0
+    masks[2, :] = 0
+    masks[2, :5] = 1
+    mids = [ctx.upload_mask(skel, m) for m in masks]
+    N = 3000
+    pick = np.stack([rng.permutation(len(clips))[:K] for _ in range(N)]).astype(np.int32)
+    ph = rng.uniform(0, 1, (N, K)).astype(np.float32)
+    w = rng.uniform(0.05, 1, (N, K)).astype(np.float32)
+    w[::7, 0] = 0  # zero-weight slots
+    mpick = rng.integers(0, 3, (N, K)).astype(np.int32)
+    mpick[::5] = 0
+    mats = gpu_pose(ctx, skel, ids[pick], ph, weight=w, mask_ids=np.asarray(mids, np.int32)[mpick])
+    sv = oracle.skeleton(sk)
+    ref = oracle.pose_batch(sv, [oracle.clip(c, am) for c in clips], pick, ph, weight=w, masks=masks, mask_ids=mpick)
+    assert_mats_close(mats, ref, tol=2e-5)  # two renormalisations more than the single-clip path
+
+
+def test_pose_multi_channel_per_bone_and_skipped_channels(ctx, oracle, player):
+    """Two channels driving one bone apply in channel order; convert[n] = -1 skips a channel BEFORE the clamp."""
+    sk, cl, am, mk = A.load_player()
+    conv = am.convert.copy()
+    conv[10] = conv[4]  # bone of channel 4 now also driven by channel 10; channel 10's old bone keeps the bind pose
+    conv[20] = -1
+    cl.rot_keys[20] = cl.rot_keys[20][:3].copy()  # would clamp later channels if it were not skipped
+    cl.scl_keys[30] = cl.scl_keys[30][:11].copy()
+    am2 = A.AnimSkelMap(conv)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am2)
+    ph = np.linspace(0, 1, 257, dtype=np.float32)
+    mats = gpu_pose(ctx, skel, np.full((257, 1), clip), ph)
+    ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am2)], np.zeros((257, 1), np.int32), ph)
+    assert_mats_close(mats, ref)
+
+
+def test_pose_config5_synthetic_256_joints(ctx, oracle):
+    sk = A.make_synthetic_skeleton(256)
+    cl, am = A.make_synthetic_clip(sk, 32)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    N = 2000
+    ph = np.random.default_rng(5).uniform(0, 1, N).astype(np.float32)
+    mats, der = gpu_pose(ctx, skel, np.full((N, 1), clip), ph, derived=True)
+    ref, rder = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((N, 1), np.int32), ph, derived=True)
+    assert_mats_close(mats, ref, tol=2e-5)  # depth-8 chains of random rotations, entries O(1)
+    assert np.abs(der - rder).max() <= 2e-5
+
+
+def test_pose_wide_and_deep_hierarchies(ctx, oracle):
+    """Star (every bone a child of the root: many parked parents avoided) and chain (parent always in registers)."""
+    for parent_of in (lambda i: 0, lambda i: i - 1, lambda i: max(0, i - 3)):
+        sk = A.make_synthetic_skeleton(64)
+        sk.parent_index = np.array([A.INT_MAX] + [parent_of(i) for i in range(1, 64)], np.int32)
+        cl, am = A.make_synthetic_clip(sk, 9, seed=3)
+        skel = ctx.upload_skeleton(sk)
+        clip = ctx.upload_clip(skel, cl, am)
+        ph = np.linspace(0, 1, 100, dtype=np.float32)
+        mats = gpu_pose(ctx, skel, np.full((100, 1), clip), ph)
+        ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((100, 1), np.int32), ph)
+        assert_mats_close(mats, ref, tol=5e-5)  # 63-deep chain of random rotations
+        assert np.array_equal(ctx.skeleton_parents(skel), np.array([-1] + [parent_of(i) for i in range(1, 64)]))
+
+
+def test_pose_is_independent_of_batch_composition(ctx, player_dev):
+    """Full-size property (config 3 scale): instance i's palette does not depend on N or its position in the batch."""
+    skel, clip = player_dev
+    N = 100000
+    ph = np.modf(np.arange(N, dtype=np.float64) * 0.7548776662)[0].astype(np.float32)
+    big = ctx.batch(skel, N, 1)
+    big.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph)
+    big.pose()
+    sel = np.random.default_rng(0).choice(N, 2000, replace=False)
+    small = gpu_pose(ctx, skel, np.full((2000, 1), clip), ph[sel])
+    for chunk in range(0, 2000, 500):
+        idx = sel[chunk:chunk + 500]
+        lo, hi = idx.min(), idx.max() + 1
+        blk = big.download_palette(int(lo), int(hi - lo))
+        assert np.array_equal(blk[idx - lo], small[chunk:chunk + 500])  # bit-identical
+    # idempotence: posing twice changes nothing
+    a = big.download_palette(0, 1000)
+    big.pose()
+    assert np.array_equal(a, big.download_palette(0, 1000))
+    big.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# skinning
+# ------------------------------------------------------------------------------------------------
+def _skin(ctx, skel, clip, mesh_h, V, N, ph, flags, variant, vsplit=0, inst_tile=0, K=1):
+    ctx.set_option("lbs_variant", variant)
+    ctx.set_option("lbs_vsplit", vsplit)
+    ctx.set_option("lbs_inst_tile", inst_tile)
+    b = ctx.batch(skel, N, 1)
+    b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph)
+    b.pose()
+    sb = ctx.skinbuf(mesh_h, V, N, flags)
+    b.skin(mesh_h, sb)
+    pos, nt = sb.download()
+    pal = b.download_palette()
+    sb.close(), b.close()
+    ctx.set_option("lbs_variant", 0), ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_inst_tile", 0)
+    return pos, nt, pal
+
+
+def _check_skin(oracle, mesh, pal, pos, nt):
+    for i in range(pal.shape[0]):
+        p16 = oracle.palette_slots(pal[i])
+        rp, rn, rt = oracle.lbs(mesh, p16)
+        radius = max(1.0, float(np.abs(rp).max()))
+        assert np.abs(pos[i] - rp).max() <= POS_TOL * radius
+        if nt is not None:
+            ok = np.isfinite(rn).all(axis=1) & np.isfinite(rt).all(axis=1)
+            assert np.abs(nt[i][ok, :3] - rn[ok]).max() <= 1e-4 and np.abs(nt[i][ok, 3:] - rt[ok]).max() <= 1e-4
+            assert np.all(np.isnan(nt[i][~ok]).any(axis=1))  # normalize(0) stays NaN like the shader
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_lbs_reference_golden(ctx, player_dev, variant):
+    """mesh.vert restated with the reference's Matrix4x4/Vector4 operators (oracle/_ref) on 2048 vertices."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    g = np.load(os.path.join(GOLDEN, "lbs_golden.npz"))
+    V = len(g["pos"])
+    mesh = A.MeshData(g["pos"], g["nrm"], g["tan"], np.zeros((V, 2), np.float32), np.arange(V, dtype=np.int32), g["idx"], g["w"])
+    mh = ctx.upload_mesh(mesh, 58)
+    pos, nt, pal = _skin(ctx, skel, clip, mh, V, 1, np.float32([0.37]), capi.PCL_SKIN_POS_NRM_TAN, variant)
+    assert_mats_close(pal[0], g["palette"][1:])
+    assert np.abs(pos[0] - g["out_pos"]).max() <= POS_TOL * max(1.0, np.abs(g["out_pos"]).max())
+    ok = np.isfinite(g["out_nrm"]).all(axis=1)
+    assert np.abs(nt[0][ok, :3] - g["out_nrm"][ok]).max() <= 1e-4 and np.abs(nt[0][ok, 3:] - g["out_tan"][ok]).max() <= 1e-4
+    assert np.all(pos[0][5] == 0) and np.all(np.isnan(nt[0][5]))  # vertex with zero total weight
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("V,N", [(16380, 37), (1001, 5), (255, 3), (4, 1), (513, 70)])
+def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    mesh = A.make_player_mesh(player[0], V=max(V, 58), seed=42)
+    if V < 58:
+        mesh = A.MeshData(*(a[:V].copy() for a in (mesh.pos, mesh.nrm, mesh.tan, mesh.uv, mesh.index_buffer, mesh.bind_idx, mesh.bind_w)))
+    mh = ctx.upload_mesh(mesh, 58)
+    ph = np.random.default_rng(V).uniform(0, 1, N).astype(np.float32)
+    for flags in (capi.PCL_SKIN_POS_NRM_TAN, capi.PCL_SKIN_POS):
+        for vsplit, it in ((0, 0), (1, 16), (3, 5)):
+            pos, nt, pal = _skin(ctx, skel, clip, mh, V, N, ph, flags, variant, vsplit, it)
+            _check_skin(oracle, mesh, pal, pos, nt)
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_lbs_config5_synthetic(ctx, oracle, variant):
+    from piccolo_b200 import capi
+    sk = A.make_synthetic_skeleton(256)
+    cl, am = A.make_synthetic_clip(sk, 32)
+    mesh = A.make_synthetic_mesh(sk, V=49998)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    mh = ctx.upload_mesh(mesh, 256)
+    N = 9
+    ph = np.linspace(0.05, 0.95, N, dtype=np.float32)
+    pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
+    _check_skin(oracle, mesh, pal, pos, nt)
+
+
+def test_lbs_ring_slots_and_linearity(ctx, player_dev, player):
+    """Ring addressing + a size-independent property: skinning is linear in the vertex position stream."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    mesh = A.make_player_mesh(player[0], V=16380, seed=1)
+    m2 = A.MeshData(mesh.pos * np.float32(2.0), mesh.nrm, mesh.tan, mesh.uv, mesh.index_buffer, mesh.bind_idx, mesh.bind_w)
+    h1, h2 = ctx.upload_mesh(mesh, 58), ctx.upload_mesh(m2, 58)
+    N = 64
+    b = ctx.batch(skel, N, 1)
+    b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=np.linspace(0, 1, N, dtype=np.float32))
+    b.pose()
+    s1, s2 = ctx.skinbuf(h1, 16380, 16, capi.PCL_SKIN_POS), ctx.skinbuf(h2, 16380, 16, capi.PCL_SKIN_POS)
+    b.skin(h1, s1, first=40, count=8, slot_first=4)
+    b.skin(h2, s2, first=40, count=8, slot_first=4)
+    b.skin(h1, s1, first=0, count=4, slot_first=0)
+    p1, _ = s1.download(4, 8)
+    p2, _ = s2.download(4, 8)
+    pal = b.download_palette(40, 8)
+    t = pal[:, :, [3, 7, 11]]  # translations; p(2x) - 2 p(x) = -sum_k w_k t_k : bounded by max |t|
+    assert np.abs(p2 - 2 * p1).max() <= np.abs(t).max() * 1.0001 + 1e-4
+    full = ctx.skinbuf(h1, 16380, N, capi.PCL_SKIN_POS)
+    b.skin(h1, full)
+    pf, _ = full.download()
+    assert np.array_equal(pf[40:48], p1)  # same instances through a different slot / launch shape: bit-identical
+    assert np.array_equal(pf[0:4], s1.download(0, 4)[0])
+    for x in (s1, s2, full, b):
+        x.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# boundary behaviour
+# ------------------------------------------------------------------------------------------------
+def test_upload_errors(ctx, player):
+    from piccolo_b200 import capi
+    sk, cl, am, mk = A.load_player()
+    sk.is_flat = False
+    with pytest.raises(capi.PclError) as e:
+        ctx.upload_skeleton(sk)
+    assert e.value.code == -3  # the reference silently builds nothing; the C ABI says so
+    sk.is_flat = True
+    sk.tpose[3, 12] = 0.5
+    with pytest.raises(capi.PclError):
+        ctx.upload_skeleton(sk)
+    sk, cl, am, mk = A.load_player()
+    skel = ctx.upload_skeleton(sk)
+    bad = A.AnimSkelMap(am.convert.copy())
+    bad.convert[3] = 58
+    with pytest.raises(capi.PclError):
+        ctx.upload_clip(skel, cl, bad)
+    cl.rot_keys[7] = cl.rot_keys[7][:0]
+    with pytest.raises(capi.PclError):
+        ctx.upload_clip(skel, cl, am)
+    mesh = A.make_player_mesh(sk, V=100)
+    mesh.bind_idx[0, 0] = 59
+    with pytest.raises(capi.PclError):
+        ctx.upload_mesh(mesh, 58)
+    with pytest.raises(capi.PclError):
+        ctx.batch(skel, 10, 5)
+    b = ctx.batch(skel, 10, 1)
+    with pytest.raises(capi.PclError):
+        b.download_palette()  # nothing posed yet
+    b.close()
