@@ -173,6 +173,24 @@ int pcl_skinbuf_dev(pcl_skinbuf* s, const void** pos_dev, const void** nt_dev, i
 /* tight host copies: pos [count][V][3], nt [count][V][6] (nt may be NULL) */
 int pcl_skinbuf_download(pcl_skinbuf* s, int64_t slot_first, int64_t count, float* host_pos, float* host_nt);
 
+/* No counterpart in the reference.  Same result as pcl_batch_download_palette, for callers that must not
+ * allocate device memory: a render or simulation thread inside its frame loop, where cudaMalloc/cudaFree
+ * would stall every stream of the device and take an unbounded time, or a host application that gave the
+ * whole GPU memory budget to its own allocator at start-up, so that a later cudaMalloc can fail.
+ * pcl_batch_download_palette grows a device staging buffer with cudaMalloc when a larger range is asked
+ * for; this variant stages through a fixed array of PCL_STATIC_EXPORT_MAX_BYTES that is part of the
+ * library image (every GPU that loads the library holds it until the process exits) and calls neither
+ * cudaMalloc nor cudaFree nor any other allocating routine.
+ *   - limit: count * J * 64 bytes <= PCL_STATIC_EXPORT_MAX_BYTES (2259 instances of the 58-bone player
+ *     skeleton), otherwise PCL_ERR_UNSUPPORTED and nothing is written; split the range into several calls.
+ *   - the first call on a device looks up the array's device address (a one-time set-up); make that first
+ *     call before starting any stream capture on the device.
+ *   - synchronous.  All calls on one GPU share the one array, from every context and thread: calls that
+ *     overlap on the GPU race and corrupt each other's result, so serialise them.  The array keeps the last
+ *     call's matrices; every call overwrites the part it uses, nothing has to start at zero. */
+#define PCL_STATIC_EXPORT_MAX_BYTES (8u << 20)
+int pcl_batch_download_palette_static(pcl_batch* b, int64_t first, int64_t count, float* host16);
+
 /* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
 /* key: "pose_warps_per_block" (1,2,4,8), "lbs_variant" (0 = coalesced 128-bit stores, 1 = TMA bulk
  * stores), "lbs_vsplit" (0 = auto), "lbs_inst_tile" (0 = auto, <= 16).  PCL_ERR_INVALID for unknown keys. */

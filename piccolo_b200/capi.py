@@ -17,6 +17,7 @@ PCL_ADVANCE_FIRST_ONLY = 1
 PCL_ADVANCE_ALL = 2
 PCL_SKIN_POS = 1
 PCL_SKIN_POS_NRM_TAN = 7
+PCL_STATIC_EXPORT_MAX_BYTES = 8 << 20
 
 _fp = C.POINTER(C.c_float)
 _ip = C.POINTER(C.c_int32)
@@ -61,6 +62,7 @@ SIGNATURES = {
     "pcl_skinbuf_dev": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _ip]),
     "pcl_skinbuf_download": (C.c_int, [_vp, _i64, _i64, _fp, _fp]),
     "pcl_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int32]),
+    "pcl_batch_download_palette_static": (C.c_int, [_vp, _i64, _i64, _fp]),
 }
 
 _lib = None
@@ -249,6 +251,14 @@ class Batch:
             out = np.zeros((count, self.J, 16), np.float32)
         fn = self.ctx.L.pcl_batch_download_palette_async if asynchronous else self.ctx.L.pcl_batch_download_palette
         self.ctx._ck(fn(self.h, first, count, _f(out)))
+        return out
+
+    def download_palette_static(self, first=0, count=None) -> np.ndarray:
+        """pcl_batch_download_palette_static: same matrices, staged through the library's fixed device array
+        (no device allocation; at most PCL_STATIC_EXPORT_MAX_BYTES per call)."""
+        count = self.N - first if count is None else count
+        out = np.zeros((count, self.J, 16), np.float32)
+        self.ctx._ck(self.ctx.L.pcl_batch_download_palette_static(self.h, first, count, _f(out)))
         return out
 
     def download_derived(self, first=0, count=None) -> np.ndarray:

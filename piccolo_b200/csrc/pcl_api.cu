@@ -46,6 +46,12 @@ namespace
     };
 } // namespace
 
+// Fixed staging area of pcl_batch_download_palette_static: lives in every GPU that loads this library,
+// from load until the process exits, and is shared by every call on that GPU.
+static __device__ __align__(256) unsigned char g_static_export[PCL_STATIC_EXPORT_MAX_BYTES];
+#define PCL_STATIC_MAX_DEVICES 64
+static void* g_static_export_addr[PCL_STATIC_MAX_DEVICES]; // device address of the array, per device (0 = not looked up yet)
+
 struct pcl_ctx
 {
     int          device = 0;
@@ -994,6 +1000,47 @@ extern "C"
             PCL_CK(c, cudaMemcpy2D(host_nt, (size_t)s->V * 24, s->d_nt + (size_t)slot_first * s->Vp * 6, (size_t)s->Vp * 24,
                                    (size_t)s->V * 24, (size_t)count, cudaMemcpyDeviceToHost));
         }
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // palette read-back without any device allocation (no counterpart in the reference)
+    // ------------------------------------------------------------------------------------------
+    int pcl_batch_download_palette_static(pcl_batch* b, int64_t first, int64_t count, float* host16)
+    {
+        if (!b || !host16 || first < 0 || count < 1 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_download_palette_static: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        if (!b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_download_palette_static: pcl_batch_pose / pcl_batch_tick has not run");
+        const SkelRec& s     = c->skels[b->skel];
+        const size_t   bytes = (size_t)count * s.J * 64;
+        if (bytes > (size_t)PCL_STATIC_EXPORT_MAX_BYTES)
+            return fail(c, PCL_ERR_UNSUPPORTED,
+                        "pcl_batch_download_palette_static: count * J * 64 bytes exceeds PCL_STATIC_EXPORT_MAX_BYTES (the fixed "
+                        "staging array); download in smaller ranges or use pcl_batch_download_palette");
+        if (c->device < 0 || c->device >= PCL_STATIC_MAX_DEVICES)
+            return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_download_palette_static: device index beyond the per-device address table");
+        PCL_CK(c, cudaSetDevice(c->device));
+        // One-time set-up per device, with that device current: in host code `g_static_export` is only a
+        // stand-in for the symbol, not an address the GPU understands, so ask the runtime where this
+        // device's copy of the array lives and hand THAT pointer to the kernel.
+        if (!g_static_export_addr[c->device])
+        {
+            void* p = nullptr;
+            PCL_CK(c, cudaGetSymbolAddress(&p, g_static_export));
+            g_static_export_addr[c->device] = p;
+        }
+        float4* staging = reinterpret_cast<float4*>(g_static_export_addr[c->device]);
+        PCL_CK(c, cudaStreamWaitEvent(c->copy, c->ev_pose, 0));
+        const long long total = count * s.J * 4; // every float4 of the range is overwritten: nothing to clear
+        export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, staging, first, count, s.J, s.pitch);
+        c->launches++;
+        PCL_CK(c, cudaGetLastError());
+        PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy));
+        c->copy_pending = true;
+        PCL_CK(c, cudaMemcpyAsync(host16, staging, bytes, cudaMemcpyDeviceToHost, c->copy));
+        PCL_CK(c, cudaStreamSynchronize(c->copy)); // the shared array is free again when this returns
         return PCL_OK;
     }
 }
