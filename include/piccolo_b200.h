@@ -151,7 +151,7 @@ int pcl_batch_keep_derived(pcl_batch* b, int32_t enable);
 /* Skinned vertex streams live in a device ring of `capacity` instance slots:
  *   positions        [capacity][Vp][3] float   (MeshVertex::VulkanMeshVertexPostition,
  *   normal+tangent   [capacity][Vp][6] float    ...VaryingEnableBlending, function/render/render_mesh.h:14-23)
- * Vp = V rounded up to a multiple of 4 (keeps every instance 16-byte aligned). */
+ * Vp = V rounded up to a multiple of 8 (keeps every instance and every 8-vertex run on 32-byte sectors). */
 int pcl_skinbuf_create(pcl_ctx* ctx, pcl_mesh mesh, int64_t capacity, int32_t flags, pcl_skinbuf** out);
 int pcl_skinbuf_destroy(pcl_skinbuf* s);
 /* engine/shader/glsl/mesh.vert:72-111 for instances [first, first+count) of the batch, written to ring
@@ -192,8 +192,10 @@ int pcl_skinbuf_download(pcl_skinbuf* s, int64_t slot_first, int64_t count, floa
 int pcl_batch_download_palette_static(pcl_batch* b, int64_t first, int64_t count, float* host16);
 
 /* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
-/* key: "pose_warps_per_block" (1,2,4,8), "lbs_variant" (0 = coalesced 128-bit stores, 1 = TMA bulk
- * stores), "lbs_vsplit" (0 = auto), "lbs_inst_tile" (0 = auto, <= 16).  PCL_ERR_INVALID for unknown keys. */
+/* key: "pose_warps_per_block" (0 = auto, 1,2,4,8); "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with
+ * coalesced 128-bit stores, 1 = same with TMA bulk stores, 2 = lane-per-instance crowd kernel);
+ * "lbs_vsplit" (0 = auto); "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only).
+ * PCL_ERR_INVALID for unknown keys. */
 int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
 
 #ifdef __cplusplus

@@ -43,6 +43,7 @@ namespace
         float * d_pos = nullptr, *d_nrm = nullptr, *d_tan = nullptr;
         int4*   d_idx = nullptr;
         float4* d_w   = nullptr;
+        VRec*   d_vrec = nullptr; // lane = instance form: slot-stable influences, see lbs_inst_kernel
     };
 } // namespace
 
@@ -66,7 +67,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_lbs_variant = 0, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0;
+    int32_t      opt_pose_wpb = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0;
     int          max_smem_optin = 0, sm_count = 0;
 };
 
@@ -246,7 +247,7 @@ extern "C"
         for (auto& cl : c->clips)
             cudaFree(cl.d_blob);
         for (auto& m : c->meshes)
-            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w);
+            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec);
         cudaFree(c->d_clips);
         cudaEventDestroy(c->ev_pose), cudaEventDestroy(c->ev_copy), cudaEventDestroy(c->t0), cudaEventDestroy(c->t1);
         cudaStreamDestroy(c->compute), cudaStreamDestroy(c->copy);
@@ -312,7 +313,7 @@ extern "C"
         std::string k(key);
         if (k == "pose_warps_per_block" && (v == 0 || v == 1 || v == 2 || v == 4 || v == 8))
             c->opt_pose_wpb = v;
-        else if (k == "lbs_variant" && (v == 0 || v == 1))
+        else if (k == "lbs_variant" && v >= -1 && v <= 2)
             c->opt_lbs_variant = v;
         else if (k == "lbs_vsplit" && v >= 0)
             c->opt_lbs_vsplit = v;
@@ -558,7 +559,7 @@ extern "C"
             return fail(c, PCL_ERR_INVALID, "pcl_upload_mesh: bad argument");
         PCL_CK(c, cudaSetDevice(c->device));
         MeshRec m;
-        m.V = V, m.Vp = (V + 3) & ~3, m.Vt = (V + LBS_VT - 1) / LBS_VT * LBS_VT, m.max_slot = max_slot;
+        m.V = V, m.Vp = (V + 7) & ~7, m.Vt = (V + LBS_VT - 1) / LBS_VT * LBS_VT, m.max_slot = max_slot;
         std::vector<float>  hp((size_t)m.Vt * 3, 0.f), hn((size_t)m.Vt * 3, 0.f), ht((size_t)m.Vt * 3, 0.f);
         std::vector<int4>   hi(m.Vt, make_int4(0, 0, 0, 0));
         std::vector<float4> hw(m.Vt, make_float4(0, 0, 0, 0));
@@ -589,9 +590,62 @@ extern "C"
             hi[v] = make_int4(id[0], id[1], id[2], id[3]);
             hw[v] = make_float4(w[0], w[1], w[2], w[3]);
         }
+        // lane = instance form.  Each vertex's (gated) influences are packed into four register slots so that
+        // a bone that was already resident for the previous vertex keeps its slot; unused slots keep the
+        // resident bone with weight 0 (an exact zero contribution).  The blend is then summed in slot order,
+        // which differs from the shader's x,y,z,w order only by a permutation of the same four products.
+        std::vector<VRec> hv(m.Vt);
+        std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
+        if (max_slot <= 0xffff)
+        {
+            int cur[4] = {0, 0, 0, 0};
+            for (int v = 0; v < V; v++)
+            {
+                const int   src_i[4] = {hi[v].x, hi[v].y, hi[v].z, hi[v].w};
+                const float src_w[4] = {hw[v].x, hw[v].y, hw[v].z, hw[v].w};
+                int         slot_i[4];
+                float       slot_w[4] = {0.f, 0.f, 0.f, 0.f};
+                bool        taken[4] = {false, false, false, false}, placed[4] = {false, false, false, false};
+                for (int k = 0; k < 4; k++) // keep resident bones where they are
+                    if (src_w[k] != 0.f)
+                        for (int sl = 0; sl < 4; sl++)
+                            if (!taken[sl] && cur[sl] == src_i[k])
+                            {
+                                taken[sl] = true, placed[k] = true, slot_w[sl] = src_w[k];
+                                break;
+                            }
+                for (int k = 0; k < 4; k++) // newcomers go to the free slots
+                    if (src_w[k] != 0.f && !placed[k])
+                        for (int sl = 0; sl < 4; sl++)
+                            if (!taken[sl])
+                            {
+                                taken[sl] = true, cur[sl] = src_i[k], slot_w[sl] = src_w[k];
+                                break;
+                            }
+                uint32_t mask = 0;
+                for (int sl = 0; sl < 4; sl++)
+                {
+                    slot_i[sl] = cur[sl];
+                    if (v == 0 || slot_i[sl] != ((sl < 2 ? (hv[v - 1].i01 >> (16 * sl)) : (hv[v - 1].i23 >> (16 * (sl - 2)))) & 0xffffu))
+                        mask |= 1u << sl;
+                }
+                VRec& r = hv[v];
+                r.px = hp[3 * (size_t)v], r.py = hp[3 * (size_t)v + 1], r.pz = hp[3 * (size_t)v + 2], r.w0 = slot_w[0];
+                r.nx = hn[3 * (size_t)v], r.ny = hn[3 * (size_t)v + 1], r.nz = hn[3 * (size_t)v + 2], r.w1 = slot_w[1];
+                r.tx = ht[3 * (size_t)v], r.ty = ht[3 * (size_t)v + 1], r.tz = ht[3 * (size_t)v + 2], r.w2 = slot_w[2];
+                r.w3   = slot_w[3];
+                r.i01  = (uint32_t)slot_i[0] | ((uint32_t)slot_i[1] << 16);
+                r.i23  = (uint32_t)slot_i[2] | ((uint32_t)slot_i[3] << 16);
+                r.mask = mask;
+            }
+            for (int v = V; v < m.Vt; v++) // padding keeps the last real vertex's slots resident
+                hv[v].i01 = hv[V - 1].i01, hv[v].i23 = hv[V - 1].i23;
+        }
         int rc;
         if ((rc = upload(c, &m.d_pos, hp)) || (rc = upload(c, &m.d_nrm, hn)) || (rc = upload(c, &m.d_tan, ht)) ||
             (rc = upload(c, &m.d_idx, hi)) || (rc = upload(c, &m.d_w, hw)))
+            return rc;
+        if (max_slot <= 0xffff && (rc = upload(c, &m.d_vrec, hv)))
             return rc;
         c->meshes.push_back(m);
         *out = (pcl_mesh)c->meshes.size() - 1;
@@ -866,6 +920,47 @@ extern "C"
         if (m.max_slot > s.J)
             return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: mesh references palette slots the skeleton does not have");
         PCL_CK(c, cudaSetDevice(c->device));
+        const bool nt = out->flags == PCL_SKIN_POS_NRM_TAN;
+        // crowd form (lane = instance) whenever a warp's 32 palettes fit in shared memory and there are
+        // enough instances to fill the lanes; otherwise the lane = vertex kernel
+        {
+            const int    prow   = (s.pitch * 3) | 1; // odd number of 16-byte units per palette row
+            const size_t smem_i = lbs_i_smem_bytes(prow);
+            const bool   fits   = m.d_vrec && smem_i <= (size_t)c->max_smem_optin;
+            int          var    = c->opt_lbs_variant;
+            if (var == 2 && !fits)
+                return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 2 needs 32 palettes in shared memory");
+            if (var < 0)
+                var = (fits && count >= 24) ? 2 : 0;
+            if (var == 2)
+            {
+                LbsIParams q {};
+                q.vrec = m.d_vrec, q.palette = b->d_palette, q.out_pos = out->d_pos, q.out_nt = out->d_nt;
+                q.first = first, q.count = count, q.slot_first = slot_first;
+                q.Vp = m.Vp, q.n_chunks = m.Vp / LBS_I_CHUNK, q.pitch = s.pitch, q.prow = prow;
+                const long long tiles = (count + 31) / 32;
+                int             vs    = c->opt_lbs_vsplit;
+                if (vs == 0) // >= 8 CTAs per SM overall, but keep runs long (each warp restarts cold)
+                    vs = (int)std::max<long long>(1, std::min<long long>(q.n_chunks / (LBS_I_WARPS * 16) + 1, (8LL * c->sm_count + tiles - 1) / tiles));
+                vs       = std::max(1, std::min(vs, q.n_chunks));
+                q.vsplit = vs;
+                const unsigned grid = (unsigned)(tiles * vs);
+                if (nt)
+                {
+                    PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i));
+                    lbs_inst_kernel<true><<<grid, LBS_I_WARPS * 32, smem_i, c->compute>>>(q);
+                }
+                else
+                {
+                    PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i));
+                    lbs_inst_kernel<false><<<grid, LBS_I_WARPS * 32, smem_i, c->compute>>>(q);
+                }
+                c->launches++;
+                PCL_CK(c, cudaGetLastError());
+                return PCL_OK;
+            }
+        }
+        const int lv_variant = c->opt_lbs_variant == 1 ? 1 : 0;
         LbsParams p {};
         p.pos = m.d_pos, p.nrm = m.d_nrm, p.tan = m.d_tan, p.idx = m.d_idx, p.w = m.d_w;
         p.palette = b->d_palette, p.out_pos = out->d_pos, p.out_nt = out->d_nt;
@@ -887,15 +982,14 @@ extern "C"
         vs       = std::min(vs, p.n_vtiles);
         p.vsplit = vs;
         const unsigned grid = (unsigned)(tiles * vs);
-        const bool     nt   = out->flags == PCL_SKIN_POS_NRM_TAN;
 #define PCL_LAUNCH_LBS(NT_, TMA_)                                                                                          \
     {                                                                                                                      \
         PCL_CK(c, cudaFuncSetAttribute(lbs_kernel<NT_, TMA_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
         lbs_kernel<NT_, TMA_><<<grid, LBS_THREADS, smem, c->compute>>>(p);                                                 \
     }
-        if (nt && c->opt_lbs_variant == 0) PCL_LAUNCH_LBS(true, false)
+        if (nt && lv_variant == 0) PCL_LAUNCH_LBS(true, false)
         else if (nt) PCL_LAUNCH_LBS(true, true)
-        else if (c->opt_lbs_variant == 0) PCL_LAUNCH_LBS(false, false)
+        else if (lv_variant == 0) PCL_LAUNCH_LBS(false, false)
         else PCL_LAUNCH_LBS(false, true)
 #undef PCL_LAUNCH_LBS
         c->launches++;

@@ -575,4 +575,213 @@ namespace pcl
             __syncwarp();
         }
     }
+
+    // -------------------------------------------------------------------------------------------
+    // K5, crowd form: lane = instance.
+    //
+    // The lane = vertex kernel above gathers 4 x 48 B of palette per vertex-instance from shared memory and
+    // is bound by the shared-memory pipe (ncu: L1/TEX 97 %, DRAM 42 %; profiles/r1_lbs_v0_*).  A bone's
+    // matrix is reused by every vertex bound to it, so here a warp takes 32 INSTANCES and walks a run of
+    // consecutive vertices: every lane keeps the four matrices of "its" instance in registers and reloads
+    // a slot only when the vertex stream says that slot's bone changes (a warp-uniform decision; the upload
+    // packs the influences into slots so that neighbouring vertices - which share bones in any real,
+    // fully-expanded mesh - keep their slots).  Vertex data is warp-uniform and read with broadcast loads.
+    //   - palettes: 32 instances x pitch x 48 B, one TMA bulk copy per instance into rows whose stride is an
+    //     odd number of 16-byte units (conflict-free 128-bit loads with lane = instance)
+    //   - vertex records (64 B, VRec): per-warp TMA bulk copies, LBS_I_VSTAGES chunks ahead
+    //   - results: 4 vertices are held in registers, written to a per-warp staging tile with 128-bit stores,
+    //     and every 8 vertices the tile is flushed with coalesced 128-bit stores: per instance a run of
+    //     8 vertices is 96 B of positions + 192 B of normal/tangent, i.e. whole 32-byte sectors.
+    // -------------------------------------------------------------------------------------------
+    struct alignas(16) VRec // one vertex, warp-uniform
+    {
+        float px, py, pz, w0;
+        float nx, ny, nz, w1;
+        float tx, ty, tz, w2;
+        float    w3;
+        uint32_t i01;  // palette slot of influence 0 | influence 1 << 16
+        uint32_t i23;
+        uint32_t mask; // bit k: influence k's bone differs from the previous vertex's influence k
+    };
+
+    struct LbsIParams
+    {
+        const VRec*   vrec;    // [Vt] zero padded to a multiple of LBS_I_CHUNK * anything the launch needs
+        const float4* palette; // [N][pitch][3]
+        float*        out_pos; // [cap][Vp][3]
+        float*        out_nt;  // [cap][Vp][6]
+        long long     first, count, slot_first;
+        int32_t       Vp, n_chunks, pitch, prow, vsplit; // prow: shared-memory palette row stride in float4 (odd)
+    };
+
+    constexpr int LBS_I_WARPS   = 8;
+    constexpr int LBS_I_CHUNK   = 8;  // vertices per flush
+    constexpr int LBS_I_VSTAGES = 4;  // vertex-record chunks in flight per warp
+    constexpr int LBS_I_POSROW  = LBS_I_CHUNK * 3 + 4; // floats; /4 odd -> conflict-free 128-bit column stores
+    constexpr int LBS_I_NTROW   = LBS_I_CHUNK * 6 + 4;
+
+    __host__ __device__ inline size_t lbs_i_smem_bytes(int prow)
+    {
+        return (size_t)32 * prow * 16                                             // palettes
+               + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4        // staging tiles
+               + (size_t)LBS_I_WARPS * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec)   // vertex records
+               + 8 * (1 + LBS_I_WARPS * LBS_I_VSTAGES) + 64;                      // mbarriers
+    }
+
+    template<bool NT>
+    __global__ void __launch_bounds__(LBS_I_WARPS * 32, 1) lbs_inst_kernel(const LbsIParams par)
+    {
+        extern __shared__ __align__(128) unsigned char lsm[];
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const int tile  = blockIdx.x / par.vsplit;
+        const int split = blockIdx.x - tile * par.vsplit;
+        const long long i0 = (long long)tile * 32;
+        const int       ni = (int)min(32LL, par.count - i0);
+
+        float4*   pal_s = reinterpret_cast<float4*>(lsm);
+        float*    spos  = reinterpret_cast<float*>(lsm + (size_t)32 * par.prow * 16) + (size_t)warp * 32 * (LBS_I_POSROW + LBS_I_NTROW);
+        float*    snt   = spos + 32 * LBS_I_POSROW;
+        VRec*     vring = reinterpret_cast<VRec*>(lsm + (size_t)32 * par.prow * 16 + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4) +
+                      (size_t)warp * LBS_I_VSTAGES * LBS_I_CHUNK;
+        uint64_t* bars  = reinterpret_cast<uint64_t*>(lsm + (size_t)32 * par.prow * 16 + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4 +
+                                                     (size_t)LBS_I_WARPS * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec));
+        uint64_t* vbar  = bars + 1 + warp * LBS_I_VSTAGES;
+
+        // this warp's run of vertex chunks
+        const int per_split = (par.n_chunks + par.vsplit - 1) / par.vsplit;
+        const int s_lo = split * per_split, s_hi = min(par.n_chunks, s_lo + per_split);
+        const int per_warp = (max(s_hi - s_lo, 0) + LBS_I_WARPS - 1) / LBS_I_WARPS;
+        const int c_lo = s_lo + warp * per_warp, c_hi = min(s_hi, c_lo + per_warp);
+
+        if (tid == 0)
+        {
+            mbar_init(&bars[0], 1);
+            for (int i = 0; i < LBS_I_WARPS * LBS_I_VSTAGES; i++)
+                mbar_init(&bars[1 + i], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (tid == 0)
+        {
+            const uint32_t row_bytes = (uint32_t)par.pitch * 48;
+            mbar_expect_tx(&bars[0], row_bytes * ni);
+            for (int i = 0; i < ni; i++)
+                tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + i0 + i) * par.pitch * 3, row_bytes, &bars[0]);
+        }
+        if (lane == 0)
+            for (int st = 0; st < LBS_I_VSTAGES && c_lo + st < c_hi; st++)
+            {
+                mbar_expect_tx(&vbar[st], LBS_I_CHUNK * sizeof(VRec));
+                tma_load(vring + st * LBS_I_CHUNK, par.vrec + (size_t)(c_lo + st) * LBS_I_CHUNK, LBS_I_CHUNK * sizeof(VRec), &vbar[st]);
+            }
+        mbar_wait(&bars[0], 0);
+        if (c_lo >= c_hi)
+            return;
+
+        const int     li   = min(lane, ni - 1); // idle lanes shadow the tile's last instance and never store
+        const float4* prow = pal_s + (size_t)li * par.prow;
+        float4 m[4][3];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            m[k][0] = m[k][1] = m[k][2] = make_float4(0, 0, 0, 0);
+        uint32_t force = 0xF; // first vertex of the run: every slot is cold
+
+        for (int c = c_lo; c < c_hi; c++)
+        {
+            const int      st = (c - c_lo) % LBS_I_VSTAGES;
+            const uint32_t ph = ((c - c_lo) / LBS_I_VSTAGES) & 1;
+            mbar_wait(&vbar[st], ph);
+            const VRec* vr = vring + st * LBS_I_CHUNK;
+#pragma unroll
+            for (int half = 0; half < 2; half++)
+            {
+                float4 op[3], on[6];
+                float* opf = reinterpret_cast<float*>(op);
+                float* onf = reinterpret_cast<float*>(on);
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                {
+                    const float4 a = *reinterpret_cast<const float4*>(&vr[half * 4 + j].px);
+                    const float4 b = *reinterpret_cast<const float4*>(&vr[half * 4 + j].nx);
+                    const float4 t = *reinterpret_cast<const float4*>(&vr[half * 4 + j].tx);
+                    const uint4  d = *reinterpret_cast<const uint4*>(&vr[half * 4 + j].w3);
+                    const uint32_t mask = d.w | force;
+                    force               = 0;
+                    if (mask & 1) { const float4* s = prow + (d.y & 0xffffu) * 3; m[0][0] = s[0], m[0][1] = s[1], m[0][2] = s[2]; }
+                    if (mask & 2) { const float4* s = prow + (d.y >> 16) * 3;     m[1][0] = s[0], m[1][1] = s[1], m[1][2] = s[2]; }
+                    if (mask & 4) { const float4* s = prow + (d.z & 0xffffu) * 3; m[2][0] = s[0], m[2][1] = s[1], m[2][2] = s[2]; }
+                    if (mask & 8) { const float4* s = prow + (d.z >> 16) * 3;     m[3][0] = s[0], m[3][1] = s[1], m[3][2] = s[2]; }
+                    const float w0 = a.w, w1 = b.w, w2 = t.w, w3 = __uint_as_float(d.x);
+                    // vertex_blending_matrix = sum_k joint_matrices[idx_k] * w_k (mesh.vert:77-102), in slot order
+                    float4 B[3];
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+                    {
+                        B[r].x = m[0][r].x * w0, B[r].y = m[0][r].y * w0, B[r].z = m[0][r].z * w0, B[r].w = m[0][r].w * w0;
+                        B[r].x += m[1][r].x * w1, B[r].y += m[1][r].y * w1, B[r].z += m[1][r].z * w1, B[r].w += m[1][r].w * w1;
+                        B[r].x += m[2][r].x * w2, B[r].y += m[2][r].y * w2, B[r].z += m[2][r].z * w2, B[r].w += m[2][r].w * w2;
+                        B[r].x += m[3][r].x * w3, B[r].y += m[3][r].y * w3, B[r].z += m[3][r].z * w3, B[r].w += m[3][r].w * w3;
+                    }
+                    // model_position = (B * vec4(p, 1)).xyz (mesh.vert:104)
+                    opf[j * 3 + 0] = B[0].x * a.x + B[0].y * a.y + B[0].z * a.z + B[0].w;
+                    opf[j * 3 + 1] = B[1].x * a.x + B[1].y * a.y + B[1].z * a.z + B[1].w;
+                    opf[j * 3 + 2] = B[2].x * a.x + B[2].y * a.y + B[2].z * a.z + B[2].w;
+                    if (NT)
+                    {
+                        // normalize(mat3(B) * n), normalize(mat3(B) * t) (mesh.vert:106-110)
+                        const float nx = B[0].x * b.x + B[0].y * b.y + B[0].z * b.z, ny = B[1].x * b.x + B[1].y * b.y + B[1].z * b.z,
+                                    nz = B[2].x * b.x + B[2].y * b.y + B[2].z * b.z;
+                        const float tx = B[0].x * t.x + B[0].y * t.y + B[0].z * t.z, ty = B[1].x * t.x + B[1].y * t.y + B[1].z * t.z,
+                                    tz = B[2].x * t.x + B[2].y * t.y + B[2].z * t.z;
+                        const float rn = rsqrtf(nx * nx + ny * ny + nz * nz);
+                        const float rt = rsqrtf(tx * tx + ty * ty + tz * tz);
+                        onf[j * 6 + 0] = nx * rn, onf[j * 6 + 1] = ny * rn, onf[j * 6 + 2] = nz * rn;
+                        onf[j * 6 + 3] = tx * rt, onf[j * 6 + 4] = ty * rt, onf[j * 6 + 5] = tz * rt;
+                    }
+                }
+                float4* sp = reinterpret_cast<float4*>(spos + lane * LBS_I_POSROW + half * 12);
+                sp[0] = op[0], sp[1] = op[1], sp[2] = op[2];
+                if (NT)
+                {
+                    float4* sn = reinterpret_cast<float4*>(snt + lane * LBS_I_NTROW + half * 24);
+#pragma unroll
+                    for (int q = 0; q < 6; q++)
+                        sn[q] = on[q];
+                }
+            }
+            __syncwarp();
+            // the records of this stage are consumed: refill it with the chunk LBS_I_VSTAGES ahead
+            if (lane == 0 && c + LBS_I_VSTAGES < c_hi)
+            {
+                mbar_expect_tx(&vbar[st], LBS_I_CHUNK * sizeof(VRec));
+                tma_load(vring + st * LBS_I_CHUNK, par.vrec + (size_t)(c + LBS_I_VSTAGES) * LBS_I_CHUNK, LBS_I_CHUNK * sizeof(VRec), &vbar[st]);
+            }
+            // flush: per instance 6 float4 of positions and 12 float4 of normal+tangent, coalesced
+            const size_t v0 = (size_t)c * LBS_I_CHUNK;
+#pragma unroll
+            for (int it = 0; it < 6; it++)
+            {
+                const int f = it * 32 + lane, il = f / 6, q = f - il * 6;
+                if (il < ni)
+                {
+                    const float4 v = *reinterpret_cast<const float4*>(spos + il * LBS_I_POSROW + q * 4);
+                    reinterpret_cast<float4*>(par.out_pos + ((size_t)(par.slot_first + i0 + il) * par.Vp + v0) * 3)[q] = v;
+                }
+            }
+            if (NT)
+            {
+#pragma unroll
+                for (int it = 0; it < 12; it++)
+                {
+                    const int f = it * 32 + lane, il = f / 12, q = f - il * 12;
+                    if (il < ni)
+                    {
+                        const float4 v = *reinterpret_cast<const float4*>(snt + il * LBS_I_NTROW + q * 4);
+                        reinterpret_cast<float4*>(par.out_nt + ((size_t)(par.slot_first + i0 + il) * par.Vp + v0) * 6)[q] = v;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
 } // namespace pcl

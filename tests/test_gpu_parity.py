@@ -265,7 +265,7 @@ def _skin(ctx, skel, clip, mesh_h, V, N, ph, flags, variant, vsplit=0, inst_tile
     pos, nt = sb.download()
     pal = b.download_palette()
     sb.close(), b.close()
-    ctx.set_option("lbs_variant", 0), ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_inst_tile", 0)
+    ctx.set_option("lbs_variant", -1), ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_inst_tile", 0)
     return pos, nt, pal
 
 
@@ -281,7 +281,7 @@ def _check_skin(oracle, mesh, pal, pos, nt):
             assert np.all(np.isnan(nt[i][~ok]).any(axis=1))  # normalize(0) stays NaN like the shader
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2])
 def test_lbs_reference_golden(ctx, player_dev, variant):
     """mesh.vert restated with the reference's Matrix4x4/Vector4 operators (oracle/_ref) on 2048 vertices."""
     from piccolo_b200 import capi
@@ -298,7 +298,7 @@ def test_lbs_reference_golden(ctx, player_dev, variant):
     assert np.all(pos[0][5] == 0) and np.all(np.isnan(nt[0][5]))  # vertex with zero total weight
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2])
 @pytest.mark.parametrize("V,N", [(16380, 37), (1001, 5), (255, 3), (4, 1), (513, 70)])
 def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
     from piccolo_b200 import capi
@@ -314,8 +314,10 @@ def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
             _check_skin(oracle, mesh, pal, pos, nt)
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, -1, 2])
 def test_lbs_config5_synthetic(ctx, oracle, variant):
+    """257 palette slots: 32 palettes do not fit in shared memory, so auto (-1) must fall back to the lane-per-vertex
+    kernel and forcing the crowd kernel (2) must be refused, not silently mis-skinned."""
     from piccolo_b200 import capi
     sk = A.make_synthetic_skeleton(256)
     cl, am = A.make_synthetic_clip(sk, 32)
@@ -323,10 +325,16 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     skel = ctx.upload_skeleton(sk)
     clip = ctx.upload_clip(skel, cl, am)
     mh = ctx.upload_mesh(mesh, 256)
-    N = 9
+    N = 40
     ph = np.linspace(0.05, 0.95, N, dtype=np.float32)
+    if variant == 2:
+        with pytest.raises(capi.PclError) as e:
+            _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
+        assert e.value.code == -3
+        ctx.set_option("lbs_variant", -1)
+        return
     pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
-    _check_skin(oracle, mesh, pal, pos, nt)
+    _check_skin(oracle, mesh, pal[::5], pos[::5], nt[::5])
 
 
 def test_lbs_ring_slots_and_linearity(ctx, player_dev, player):
