@@ -376,33 +376,64 @@ def make_variant_clip(base: AnimationClip, frames: int, seed: int, max_deg: floa
 
 
 def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42) -> MeshData:
-    """Synthetic stand-in for the missing robot.mesh_bind.json: vertices on capsules around the bind-pose
-    bones, each bound to its 1-4 nearest bones with inverse-distance weights; fully expanded triangles
-    (index_buffer[i] == i, as the reference's binding upload requires, render_resource.cpp:705-712)."""
+    """Synthetic stand-in for the missing robot.mesh_bind.json: a tessellated tube
+    (capsule side) around every bone, emitted as FULLY EXPANDED triangles in strip order - three vertices per
+    triangle, index_buffer[i] == i, which is the only case in which the reference's per-index binding upload is
+    self-consistent (render_resource.cpp:705-712).  Every vertex is bound to the bones among its 4 nearest whose
+    distance is within 1.6x the nearest one (1-4 influences, inverse-distance weights), so - like any real
+    character mesh - neighbouring vertices share most of their bones.  Indices are stored +1, 0 = empty slot
+    (animation_loader.cpp:40-71)."""
     rng = np.random.default_rng(seed)
     P, _, _ = bind_model_transforms(skel)
     J = skel.J
-    per = np.full(J, V // J)
-    per[: V - per.sum()] += 1
-    owner = np.repeat(np.arange(J), per)
-    u = rng.normal(size=(V, 3))
-    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    n_tri = max(1, V // 3)
+    per = np.full(J, n_tri // J)
+    per[: n_tri - per.sum()] += 1
     par = np.array([p if (p != INT_MAX and p < i) else i for i, p in enumerate(skel.parent_index)])
-    t = rng.uniform(0, 1, size=(V, 1))
-    centre = P[owner] * (1 - t) + P[par[owner]] * t
-    pos = centre + u * rng.uniform(0.02, 0.06, size=(V, 1))
-    nrm = u
-    tan = np.cross(u, np.roll(u, 1, axis=1))
-    tan /= np.maximum(np.linalg.norm(tan, axis=1, keepdims=True), 1e-9)
+    pos_l, nrm_l, tan_l = [], [], []
+    for b in range(J):
+        nt = int(per[b])
+        if nt == 0:
+            continue
+        a0, a1 = P[par[b]], P[b]
+        axis = a1 - a0
+        L = np.linalg.norm(axis)
+        axis = axis / L if L > 1e-6 else np.array([0.0, 0.0, 1.0])
+        L = max(L, 0.05)
+        ref = np.array([1.0, 0, 0]) if abs(axis[0]) < 0.9 else np.array([0, 1.0, 0])
+        e1 = np.cross(axis, ref)
+        e1 /= np.linalg.norm(e1)
+        e2 = np.cross(axis, e1)
+        radius = 0.03 + 0.02 * rng.uniform()
+        seg = 8
+        rings = max(1, int(np.ceil(nt / (2 * seg))))
+
+        def surf(ring, s):
+            th = 2 * np.pi * (s % seg) / seg
+            d = np.cos(th) * e1 + np.sin(th) * e2
+            return a0 + axis * (L * ring / rings) + radius * d, d, axis
+
+        tris = []
+        for r in range(rings):
+            for s_ in range(seg):
+                q00, q01, q10, q11 = surf(r, s_), surf(r, s_ + 1), surf(r + 1, s_), surf(r + 1, s_ + 1)
+                tris.append((q00, q01, q10))
+                tris.append((q01, q11, q10))
+        for t in tris[:nt]:
+            for pnt, d, ax in t:
+                pos_l.append(pnt), nrm_l.append(d), tan_l.append(ax)
+    pos, nrm, tan = np.array(pos_l), np.array(nrm_l), np.array(tan_l)
+    # V may not be a multiple of 3: top up with copies of the last vertex / trim
+    if pos.shape[0] < V:
+        k = V - pos.shape[0]
+        pos, nrm, tan = (np.concatenate([a, np.repeat(a[-1:], k, 0)], 0) for a in (pos, nrm, tan))
+    pos, nrm, tan = pos[:V], nrm[:V], tan[:V]
     d = np.linalg.norm(pos[:, None, :] - P[None, :, :], axis=2)  # [V,J]
-    nearest = np.argsort(d, axis=1)[:, :4]
-    k = rng.integers(1, 5, size=V)  # 1..4 influences
-    idx = np.zeros((V, 4), np.int32)
-    w = np.zeros((V, 4), F32)
-    for s in range(4):
-        on = k > s
-        idx[on, s] = nearest[on, s] + 1
-        w[on, s] = (1.0 / (d[np.arange(V), nearest[:, s]][on] + 1e-3)).astype(F32)
+    nearest = np.argsort(d, axis=1, kind="stable")[:, :4]
+    dn = np.take_along_axis(d, nearest, 1)
+    on = dn <= 1.6 * dn[:, :1] + 1e-9
+    idx = np.where(on, nearest + 1, 0).astype(np.int32)
+    w = np.where(on, 1.0 / (dn + 1e-3), 0.0).astype(F32)
     uv = rng.uniform(0, 1, size=(V, 2))
     return MeshData(pos.astype(F32), nrm.astype(F32), tan.astype(F32), uv.astype(F32), np.arange(V, dtype=np.int32), idx, w)
 

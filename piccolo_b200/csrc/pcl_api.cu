@@ -596,7 +596,7 @@ extern "C"
         // which differs from the shader's x,y,z,w order only by a permutation of the same four products.
         std::vector<VRec> hv(m.Vt);
         std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
-        if (max_slot <= 0xffff)
+        if (max_slot * 3 <= 0xffff)
         {
             int cur[4] = {0, 0, 0, 0};
             for (int v = 0; v < V; v++)
@@ -626,7 +626,7 @@ extern "C"
                 for (int sl = 0; sl < 4; sl++)
                 {
                     slot_i[sl] = cur[sl];
-                    if (v == 0 || slot_i[sl] != ((sl < 2 ? (hv[v - 1].i01 >> (16 * sl)) : (hv[v - 1].i23 >> (16 * (sl - 2)))) & 0xffffu))
+                    if (v == 0 || (uint32_t)slot_i[sl] * 3u != ((sl < 2 ? (hv[v - 1].i01 >> (16 * sl)) : (hv[v - 1].i23 >> (16 * (sl - 2)))) & 0xffffu))
                         mask |= 1u << sl;
                 }
                 VRec& r = hv[v];
@@ -634,8 +634,8 @@ extern "C"
                 r.nx = hn[3 * (size_t)v], r.ny = hn[3 * (size_t)v + 1], r.nz = hn[3 * (size_t)v + 2], r.w1 = slot_w[1];
                 r.tx = ht[3 * (size_t)v], r.ty = ht[3 * (size_t)v + 1], r.tz = ht[3 * (size_t)v + 2], r.w2 = slot_w[2];
                 r.w3   = slot_w[3];
-                r.i01  = (uint32_t)slot_i[0] | ((uint32_t)slot_i[1] << 16);
-                r.i23  = (uint32_t)slot_i[2] | ((uint32_t)slot_i[3] << 16);
+                r.i01  = (uint32_t)slot_i[0] * 3u | (((uint32_t)slot_i[1] * 3u) << 16);
+                r.i23  = (uint32_t)slot_i[2] * 3u | (((uint32_t)slot_i[3] * 3u) << 16);
                 r.mask = mask;
             }
             for (int v = V; v < m.Vt; v++) // padding keeps the last real vertex's slots resident
@@ -645,7 +645,7 @@ extern "C"
         if ((rc = upload(c, &m.d_pos, hp)) || (rc = upload(c, &m.d_nrm, hn)) || (rc = upload(c, &m.d_tan, ht)) ||
             (rc = upload(c, &m.d_idx, hi)) || (rc = upload(c, &m.d_w, hw)))
             return rc;
-        if (max_slot <= 0xffff && (rc = upload(c, &m.d_vrec, hv)))
+        if (max_slot * 3 <= 0xffff && (rc = upload(c, &m.d_vrec, hv)))
             return rc;
         c->meshes.push_back(m);
         *out = (pcl_mesh)c->meshes.size() - 1;

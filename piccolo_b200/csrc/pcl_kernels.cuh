@@ -599,7 +599,7 @@ namespace pcl
         float nx, ny, nz, w1;
         float tx, ty, tz, w2;
         float    w3;
-        uint32_t i01;  // palette slot of influence 0 | influence 1 << 16
+        uint32_t i01;  // 3 * palette slot of influence 0 | 3 * slot of influence 1 << 16 (16-byte units into a palette row)
         uint32_t i23;
         uint32_t mask; // bit k: influence k's bone differs from the previous vertex's influence k
     };
@@ -626,6 +626,46 @@ namespace pcl
                + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4        // staging tiles
                + (size_t)LBS_I_WARPS * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec)   // vertex records
                + 8 * (1 + LBS_I_WARPS * LBS_I_VSTAGES) + 64;                      // mbarriers
+    }
+
+    // one bone matrix (3 rows) from this lane's palette row; off3 = slot * 3 (16-byte units)
+    __device__ __forceinline__ void lbs_i_load(float4 (&m)[3], const float4* prow, uint32_t off3)
+    {
+        const float4* s = prow + off3;
+        m[0] = s[0], m[1] = s[1], m[2] = s[2];
+    }
+
+    // Flush of one 8-vertex chunk with coalesced 128-bit stores.  Lane -> (staging row, 16-byte unit) maps
+    // every quarter-warp onto ONE row (positions: 6 units, lanes 6,7 of each quarter idle; normal/tangent
+    // units 0-7) or onto rows r and r+4 (units 8-11 of the 12-unit normal/tangent rows), which keeps the
+    // reads conflict-free with the odd row strides the 128-bit column stores need.  All lane-dependent
+    // address parts are hoisted by the caller; per store only uniform offsets are added.
+    template<bool NT, bool FULL>
+    __device__ __forceinline__ void lbs_i_flush(const float* spos, const float* snt, int s_pos0, int s_nt0, int s_nt2,
+                                                float4* g_pos0, float4* g_nt0, float4* g_nt2, size_t rowstep_pos /*float4 per 4 instances*/,
+                                                size_t rowstep_nt, size_t chunk_pos /*float4*/, size_t chunk_nt, int lane, int ni)
+    {
+        const int a = lane >> 3, b = lane & 7, c4 = ((lane >> 2) & 1) * 4;
+        if (b < 6)
+        {
+#pragma unroll
+            for (int it = 0; it < 8; it++)
+                if (FULL || it * 4 + a < ni)
+                    g_pos0[chunk_pos + it * rowstep_pos] = *reinterpret_cast<const float4*>(spos + s_pos0 + it * 4 * LBS_I_POSROW);
+        }
+        if (NT)
+        {
+#pragma unroll
+            for (int g = 0; g < 4; g++)
+            {
+                if (FULL || g * 8 + a < ni)
+                    g_nt0[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + g * 8 * LBS_I_NTROW);
+                if (FULL || g * 8 + 4 + a < ni)
+                    g_nt0[chunk_nt + (2 * g + 1) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + (g * 8 + 4) * LBS_I_NTROW);
+                if (FULL || g * 8 + a + c4 < ni)
+                    g_nt2[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt2 + g * 8 * LBS_I_NTROW);
+            }
+        }
     }
 
     template<bool NT>
@@ -680,11 +720,21 @@ namespace pcl
 
         const int     li   = min(lane, ni - 1); // idle lanes shadow the tile's last instance and never store
         const float4* prow = pal_s + (size_t)li * par.prow;
+        // the run starts cold: bring in the four bones of its first vertex
         float4 m[4][3];
-#pragma unroll
-        for (int k = 0; k < 4; k++)
-            m[k][0] = m[k][1] = m[k][2] = make_float4(0, 0, 0, 0);
-        uint32_t force = 0xF; // first vertex of the run: every slot is cold
+        {
+            const uint4 d = __ldg(reinterpret_cast<const uint4*>(&par.vrec[(size_t)c_lo * LBS_I_CHUNK].w3));
+            lbs_i_load(m[0], prow, d.y & 0xffffu), lbs_i_load(m[1], prow, d.y >> 16);
+            lbs_i_load(m[2], prow, d.z & 0xffffu), lbs_i_load(m[3], prow, d.z >> 16);
+        }
+        // lane-dependent parts of the flush addresses (see lbs_i_flush)
+        const int    fa = lane >> 3, fb = lane & 7, fc4 = ((lane >> 2) & 1) * 4, fd = lane & 3;
+        const int    s_pos0 = fa * LBS_I_POSROW + fb * 4, s_nt0 = fa * LBS_I_NTROW + fb * 4, s_nt2 = (fa + fc4) * LBS_I_NTROW + (8 + fd) * 4;
+        const size_t S0 = (size_t)(par.slot_first + i0);
+        float4*      g_pos0 = reinterpret_cast<float4*>(par.out_pos + (S0 + fa) * par.Vp * 3) + fb;
+        float4*      g_nt0  = NT ? reinterpret_cast<float4*>(par.out_nt + (S0 + fa) * par.Vp * 6) + fb : nullptr;
+        float4*      g_nt2  = NT ? reinterpret_cast<float4*>(par.out_nt + (S0 + fa + fc4) * par.Vp * 6) + 8 + fd : nullptr;
+        const size_t rowstep_pos = (size_t)par.Vp * 3, rowstep_nt = (size_t)par.Vp * 6; // float4 units per 4 instances
 
         for (int c = c_lo; c < c_hi; c++)
         {
@@ -705,12 +755,13 @@ namespace pcl
                     const float4 b = *reinterpret_cast<const float4*>(&vr[half * 4 + j].nx);
                     const float4 t = *reinterpret_cast<const float4*>(&vr[half * 4 + j].tx);
                     const uint4  d = *reinterpret_cast<const uint4*>(&vr[half * 4 + j].w3);
-                    const uint32_t mask = d.w | force;
-                    force               = 0;
-                    if (mask & 1) { const float4* s = prow + (d.y & 0xffffu) * 3; m[0][0] = s[0], m[0][1] = s[1], m[0][2] = s[2]; }
-                    if (mask & 2) { const float4* s = prow + (d.y >> 16) * 3;     m[1][0] = s[0], m[1][1] = s[1], m[1][2] = s[2]; }
-                    if (mask & 4) { const float4* s = prow + (d.z & 0xffffu) * 3; m[2][0] = s[0], m[2][1] = s[1], m[2][2] = s[2]; }
-                    if (mask & 8) { const float4* s = prow + (d.z >> 16) * 3;     m[3][0] = s[0], m[3][1] = s[1], m[3][2] = s[2]; }
+                    if (d.w) // some slot changes bone at this vertex (warp-uniform, rare in a coherent mesh)
+                    {
+                        if (d.w & 1) lbs_i_load(m[0], prow, d.y & 0xffffu);
+                        if (d.w & 2) lbs_i_load(m[1], prow, d.y >> 16);
+                        if (d.w & 4) lbs_i_load(m[2], prow, d.z & 0xffffu);
+                        if (d.w & 8) lbs_i_load(m[3], prow, d.z >> 16);
+                    }
                     const float w0 = a.w, w1 = b.w, w2 = t.w, w3 = __uint_as_float(d.x);
                     // vertex_blending_matrix = sum_k joint_matrices[idx_k] * w_k (mesh.vert:77-102), in slot order
                     float4 B[3];
@@ -756,31 +807,11 @@ namespace pcl
                 mbar_expect_tx(&vbar[st], LBS_I_CHUNK * sizeof(VRec));
                 tma_load(vring + st * LBS_I_CHUNK, par.vrec + (size_t)(c + LBS_I_VSTAGES) * LBS_I_CHUNK, LBS_I_CHUNK * sizeof(VRec), &vbar[st]);
             }
-            // flush: per instance 6 float4 of positions and 12 float4 of normal+tangent, coalesced
-            const size_t v0 = (size_t)c * LBS_I_CHUNK;
-#pragma unroll
-            for (int it = 0; it < 6; it++)
-            {
-                const int f = it * 32 + lane, il = f / 6, q = f - il * 6;
-                if (il < ni)
-                {
-                    const float4 v = *reinterpret_cast<const float4*>(spos + il * LBS_I_POSROW + q * 4);
-                    reinterpret_cast<float4*>(par.out_pos + ((size_t)(par.slot_first + i0 + il) * par.Vp + v0) * 3)[q] = v;
-                }
-            }
-            if (NT)
-            {
-#pragma unroll
-                for (int it = 0; it < 12; it++)
-                {
-                    const int f = it * 32 + lane, il = f / 12, q = f - il * 12;
-                    if (il < ni)
-                    {
-                        const float4 v = *reinterpret_cast<const float4*>(snt + il * LBS_I_NTROW + q * 4);
-                        reinterpret_cast<float4*>(par.out_nt + ((size_t)(par.slot_first + i0 + il) * par.Vp + v0) * 6)[q] = v;
-                    }
-                }
-            }
+            const size_t chunk_pos = (size_t)c * (LBS_I_CHUNK * 3 / 4), chunk_nt = (size_t)c * (LBS_I_CHUNK * 6 / 4);
+            if (ni == 32)
+                lbs_i_flush<NT, true>(spos, snt, s_pos0, s_nt0, s_nt2, g_pos0, g_nt0, g_nt2, rowstep_pos, rowstep_nt, chunk_pos, chunk_nt, lane, ni);
+            else
+                lbs_i_flush<NT, false>(spos, snt, s_pos0, s_nt0, s_nt2, g_pos0, g_nt0, g_nt2, rowstep_pos, rowstep_nt, chunk_pos, chunk_nt, lane, ni);
             __syncwarp();
         }
     }

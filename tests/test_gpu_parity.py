@@ -337,7 +337,8 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     _check_skin(oracle, mesh, pal[::5], pos[::5], nt[::5])
 
 
-def test_lbs_ring_slots_and_linearity(ctx, player_dev, player):
+@pytest.mark.parametrize("variant", [0, 2])
+def test_lbs_ring_slots_and_linearity(ctx, player_dev, player, variant):
     """Ring addressing + a size-independent property: skinning is linear in the vertex position stream."""
     from piccolo_b200 import capi
     skel, clip = player_dev
@@ -348,6 +349,7 @@ def test_lbs_ring_slots_and_linearity(ctx, player_dev, player):
     b = ctx.batch(skel, N, 1)
     b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=np.linspace(0, 1, N, dtype=np.float32))
     b.pose()
+    ctx.set_option("lbs_variant", variant)
     s1, s2 = ctx.skinbuf(h1, 16380, 16, capi.PCL_SKIN_POS), ctx.skinbuf(h2, 16380, 16, capi.PCL_SKIN_POS)
     b.skin(h1, s1, first=40, count=8, slot_first=4)
     b.skin(h2, s2, first=40, count=8, slot_first=4)
@@ -360,8 +362,12 @@ def test_lbs_ring_slots_and_linearity(ctx, player_dev, player):
     full = ctx.skinbuf(h1, 16380, N, capi.PCL_SKIN_POS)
     b.skin(h1, full)
     pf, _ = full.download()
-    assert np.array_equal(pf[40:48], p1)  # same instances through a different slot / launch shape: bit-identical
+    ctx.set_option("lbs_vsplit", 5)
+    b.skin(h1, s1, first=40, count=8, slot_first=8)
+    ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_variant", -1)
+    assert np.array_equal(pf[40:48], p1)  # same instances through a different slot / tile position: bit-identical
     assert np.array_equal(pf[0:4], s1.download(0, 4)[0])
+    assert np.array_equal(s1.download(8, 8)[0], p1)  # and through a different vertex split
     for x in (s1, s2, full, b):
         x.close()
 
