@@ -50,9 +50,21 @@ def build_host(force: bool = False) -> str:
     return HOST_LIB
 
 
+def build_host_test(force: bool = False) -> str:
+    """piccolo_b200/host/test_host: the driver tests/test_host_*.py run against the host C++ mirror."""
+    hdir = os.path.join(PKG, "host")
+    exe = os.path.join(hdir, "test_host")
+    src = os.path.join(hdir, "test_host.cpp")
+    if force or _newer(exe, [src, HOST_LIB, os.path.join(hdir, "piccolo_anim.h")]):
+        subprocess.check_call([os.environ.get("CXX", "g++"), "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), "-I", hdir, "-o", exe, src,
+                               "-L", PKG, "-lpiccolo_host", "-lpiccolo_b200", "-Wl,-rpath,$ORIGIN/.."])
+    return exe
+
+
 def build_all(force: bool = False, verbose: bool = False):
     build_cuda(force, verbose)
     build_host(force)
+    build_host_test(force)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,192 @@
+// Driver for the host C++ mirror, used by tests/test_host_*.py.  It talks to the classes the way the
+// reference's callers do (GObject::load/tick, MeshComponent::tick, LevelDebugger::drawBones) and dumps
+// what they would see as raw little-endian arrays: each record = int32 tag, int32 count, payload.
+#include "piccolo_anim.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace Piccolo;
+
+static FILE* g_out = nullptr;
+static void  putf(int tag, const std::vector<float>& v)
+{
+    int32_t h[2] = {tag, (int32_t)v.size()};
+    fwrite(h, 4, 2, g_out);
+    fwrite(v.data(), 4, v.size(), g_out);
+}
+static void puti(int tag, const std::vector<int32_t>& v)
+{
+    int32_t h[2] = {tag | 0x40000000, (int32_t)v.size()};
+    fwrite(h, 4, 2, g_out);
+    fwrite(v.data(), 4, v.size(), g_out);
+}
+static void putResult(int tag, const AnimationResult& r)
+{
+    std::vector<float>   m;
+    std::vector<int32_t> idx;
+    for (const auto& n : r.node)
+    {
+        idx.push_back(n.index);
+        const float* p = &n.transform.v0;
+        m.insert(m.end(), p, p + 16);
+    }
+    putf(tag, m);
+    puti(tag, idx);
+}
+
+static int cmd_load(int argc, char** argv)
+{
+    if (argc < 8)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    AnimationLoader L;
+    auto            sk = L.loadSkeletonData(argv[3]);
+    auto            cl = L.loadAnimationClipData(argv[4]);
+    auto            mp = L.loadAnimSkelMap(argv[5]);
+    auto            mk = L.loadSkeletonMask(argv[6]);
+    g_out              = fopen(argv[7], "wb");
+    std::vector<int32_t> meta = {(int32_t)sk->bones_map.size(), sk->is_flat, sk->in_topological_order, sk->root_index, cl->total_frame,
+                                 cl->node_count, (int32_t)cl->node_channels.size()};
+    puti(1, meta);
+    std::vector<int32_t> idx, par;
+    std::vector<float>   pos, rot, scl, tp;
+    for (const RawBone& b : sk->bones_map)
+    {
+        idx.push_back(b.index), par.push_back(b.parent_index);
+        pos.insert(pos.end(), {b.binding_pose.m_position.x, b.binding_pose.m_position.y, b.binding_pose.m_position.z});
+        scl.insert(scl.end(), {b.binding_pose.m_scale.x, b.binding_pose.m_scale.y, b.binding_pose.m_scale.z});
+        rot.insert(rot.end(), {b.binding_pose.m_rotation.w, b.binding_pose.m_rotation.x, b.binding_pose.m_rotation.y, b.binding_pose.m_rotation.z});
+        const float* m = &b.tpose_matrix.v0;
+        tp.insert(tp.end(), m, m + 16);
+    }
+    puti(2, idx), puti(3, par), putf(4, pos), putf(5, rot), putf(6, scl), putf(7, tp);
+    std::vector<int32_t> counts;
+    std::vector<float>   kp, kr, ks;
+    for (const auto& ch : cl->node_channels)
+    {
+        counts.insert(counts.end(), {(int32_t)ch.position_keys.size(), (int32_t)ch.rotation_keys.size(), (int32_t)ch.scaling_keys.size()});
+        for (auto& k : ch.position_keys) kp.insert(kp.end(), {k.x, k.y, k.z});
+        for (auto& k : ch.rotation_keys) kr.insert(kr.end(), {k.w, k.x, k.y, k.z});
+        for (auto& k : ch.scaling_keys) ks.insert(ks.end(), {k.x, k.y, k.z});
+    }
+    puti(8, counts), putf(9, kp), putf(10, kr), putf(11, ks);
+    puti(12, std::vector<int32_t>(mp->convert.begin(), mp->convert.end()));
+    puti(13, std::vector<int32_t>(mk->enabled.begin(), mk->enabled.end()));
+    // a missing file leaves a default-constructed asset and raises nothing (asset_manager.h:25-29)
+    auto none = L.loadSkeletonData("does/not/exist.json");
+    puti(14, {(int32_t)none->bones_map.size(), none->is_flat});
+    fclose(g_out);
+    std::printf("skeleton_path_in_mask=%s\n", mk->skeleton_file_path.c_str());
+    return 0;
+}
+
+// AnimationComponent as GObject::load + n x GObject::tick would drive it
+static int cmd_tick(int argc, char** argv)
+{
+    if (argc < 7)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    auto               res = AnimationLoader().loadAnimationComponentRes(argv[3]);
+    const int          n   = std::atoi(argv[4]);
+    const float        dt  = (float)std::atof(argv[5]);
+    g_out                  = fopen(argv[6], "wb");
+    AnimationComponent comp;
+    comp.setAnimationRes(*res);
+    comp.postLoadResource(std::weak_ptr<GObject>());
+    std::vector<float> phases;
+    for (int t = 0; t < n; t++)
+    {
+        comp.tick(dt);
+        phases.push_back(comp.getAnimationRes().blend_state.blend_ratio[0]);
+        if (t == 0 || t == 1 || t == 45 || t == 46 || t == n - 1)
+            putResult(100 + t, comp.getResult());
+    }
+    putf(1, phases);
+    // what LevelDebugger::drawBones reads (level_debugger.cpp:110-146)
+    const Skeleton&      sk    = comp.getSkeleton();
+    const Bone*          bones = sk.getBones();
+    std::vector<float>   der;
+    std::vector<int32_t> parent, ids;
+    for (int i = 0; i < sk.getBonesCount(); i++)
+    {
+        const Vector3&    p = bones[i]._getDerivedPosition();
+        const Quaternion& q = bones[i]._getDerivedOrientation();
+        const Vector3&    s = bones[i]._getDerivedScale();
+        der.insert(der.end(), {p.x, p.y, p.z, q.w, q.x, q.y, q.z, s.x, s.y, s.z});
+        const Node* par = bones[i].getParent();
+        parent.push_back(par ? (int32_t)(static_cast<const Bone*>(par) - bones) : -1);
+        ids.push_back((int32_t)bones[i].getID());
+    }
+    putf(2, der), puti(3, parent), puti(4, ids);
+    std::printf("bones=%d first=%s last=%s ctx=%s\n", sk.getBonesCount(), sk.getBonesCount() ? bones[0].getName().c_str() : "-",
+                sk.getBonesCount() ? bones[sk.getBonesCount() - 1].getName().c_str() : "-", Runtime::context() ? "gpu" : "none");
+    fclose(g_out);
+    Runtime::shutdown();
+    return 0;
+}
+
+// crowd: N components in one AnimationBatch, then skinning
+static int cmd_batch(int argc, char** argv)
+{
+    if (argc < 9)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    auto          res = AnimationLoader().loadAnimationComponentRes(argv[3]);
+    const int64_t N   = std::atoll(argv[4]);
+    const int     n   = std::atoi(argv[5]);
+    const float   dt  = (float)std::atof(argv[6]);
+    auto          mesh = AnimationLoader().loadMeshData(argv[7]);
+    g_out              = fopen(argv[8], "wb");
+    AnimationBatch batch;
+    if (!batch.create(*res, N))
+    {
+        std::printf("create failed: %s\n", Runtime::lastError());
+        return 1;
+    }
+    const int          K = res->blend_state.clip_count;
+    std::vector<float> ph((size_t)N * K);
+    for (int64_t i = 0; i < N; i++)
+        for (int k = 0; k < K; k++)
+            ph[i * K + k] = (float)i / (float)N;
+    batch.setPhases(ph);
+    for (int t = 0; t < n; t++)
+        batch.tick(dt);
+    putf(1, batch.getPhases());
+    std::vector<float> mats;
+    batch.getResults(0, N, mats);
+    putf(2, mats);
+    putResult(3, batch.getResult(N - 1));
+    if (!mesh->vertex_buffer.empty())
+    {
+        const int64_t cnt = N < 8 ? N : 8;
+        if (!batch.attachMesh(*mesh, cnt, true) || !batch.skin(N - cnt, cnt))
+        {
+            std::printf("skin failed: %s\n", Runtime::lastError());
+            return 1;
+        }
+        std::vector<float> pos, nt;
+        batch.downloadSkinned(0, cnt, pos, nt);
+        putf(4, pos), putf(5, nt);
+    }
+    fclose(g_out);
+    std::printf("batch ok N=%lld J=%d\n", (long long)N, batch.boneCount());
+    Runtime::shutdown();
+    return 0;
+}
+
+int main(int argc, char** argv)
+{
+    if (argc < 2)
+        return 2;
+    if (!std::strcmp(argv[1], "load"))
+        return cmd_load(argc, argv);
+    if (!std::strcmp(argv[1], "tick"))
+        return cmd_tick(argc, argv);
+    if (!std::strcmp(argv[1], "batch"))
+        return cmd_batch(argc, argv);
+    return 2;
+}

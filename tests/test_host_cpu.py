@@ -1,0 +1,60 @@
+"""Host C++ mirror, CPU side: the JSON loader reproduces the reference reader's sparse-default semantics
+(engine/template/allSerializer.ipp.mustache:28-33) and the classes stay silently inert without a GPU, the way the
+reference stays silent on an invalid skeleton (skeleton.cpp:24-28,41-44)."""
+import os
+
+import numpy as np
+import pytest
+
+import hostutil as H
+from piccolo_b200 import assets as A
+from oracle import pyoracle as O
+
+
+def _check_load(dump, sk, cl, am, mk):
+    d = H.read_dump(dump)
+    assert d["1i"].tolist() == [sk.J, int(sk.is_flat), int(sk.in_topological_order), sk.root_index, cl.total_frame, cl.node_count, cl.C]
+    assert np.array_equal(d["2i"], sk.index) and np.array_equal(d["3i"], sk.parent_index)
+    assert np.array_equal(d["4"].reshape(-1, 3), sk.bind_pos) and np.array_equal(d["5"].reshape(-1, 4), sk.bind_rot)
+    assert np.array_equal(d["6"].reshape(-1, 3), sk.bind_scl) and np.array_equal(d["7"].reshape(-1, 16), sk.tpose)
+    counts = d["8i"].reshape(-1, 3)
+    assert counts[:, 0].tolist() == [k.shape[0] for k in cl.pos_keys]
+    assert counts[:, 1].tolist() == [k.shape[0] for k in cl.rot_keys]
+    assert np.array_equal(d["9"].reshape(-1, 3), np.concatenate(cl.pos_keys))
+    assert np.array_equal(d["10"].reshape(-1, 4), np.concatenate(cl.rot_keys))
+    assert np.array_equal(d["11"].reshape(-1, 3), np.concatenate(cl.scl_keys))
+    assert np.array_equal(d["12i"], am.convert) and np.array_equal(d["13i"], mk.enabled)
+    assert d["14i"].tolist() == [0, 0]  # missing file => default-constructed asset, no exception
+
+
+@pytest.mark.parametrize("sparse", [False, True])
+def test_loader_matches_fixture_bit_for_bit(player, tmp_path, sparse):
+    urls = H.write_player_tree(str(tmp_path), player, sparse=sparse)
+    out = tmp_path / "load.bin"
+    r = H.run(["load", tmp_path, urls["skeleton"], urls["clip"], urls["map"], urls["mask"], out])
+    assert r.returncode == 0, r.stderr
+    assert "skeleton_path_in_mask=" + urls["skeleton"] in r.stdout
+    _check_load(out, *player)
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(O.REFERENCE_ROOT, "engine", "asset")), reason="reference tree not present")
+def test_loader_on_the_bundled_reference_json(player, tmp_path):
+    """The real, sparse asset files: root and 'biped' have no parent_index key, rotations are '{}', tpose lists v0..v11."""
+    out = tmp_path / "load.bin"
+    r = H.run(["load", os.path.join(O.REFERENCE_ROOT, "engine"), H.DATA + "skeleton_data_root.skeleton.json",
+               H.DATA + "W2_CrouchWalk_Aim_F_Loop_IP.animation_clip.json", H.DATA + "anim.skeleton_map.json", H.DATA + "anim.skeleton_mask.json", out])
+    assert r.returncode == 0, r.stderr
+    _check_load(out, *player)
+
+
+def test_component_is_inert_without_a_gpu(player, tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    urls = H.write_player_tree(str(tmp_path), player)
+    out = tmp_path / "tick.bin"
+    r = H.run(["tick", tmp_path, urls["object"], 3, 1 / 60, out])
+    assert r.returncode == 0, r.stderr
+    assert "bones=0" in r.stdout and "ctx=none" in r.stdout and "no CPU path" in r.stderr
+    d = H.read_dump(out)
+    assert d["100"].size == 0 and len(d["1"]) == 3  # phases still advance, results stay empty (like m_bones == nullptr)
