@@ -94,6 +94,7 @@ static int cmd_tick(int argc, char** argv)
     const int          n   = std::atoi(argv[4]);
     const float        dt  = (float)std::atof(argv[5]);
     g_out                  = fopen(argv[6], "wb");
+    { // the component (and its device batch) must be gone before the runtime is shut down
     AnimationComponent comp;
     comp.setAnimationRes(*res);
     comp.postLoadResource(std::weak_ptr<GObject>());
@@ -124,7 +125,9 @@ static int cmd_tick(int argc, char** argv)
     putf(2, der), puti(3, parent), puti(4, ids);
     std::printf("bones=%d first=%s last=%s ctx=%s\n", sk.getBonesCount(), sk.getBonesCount() ? bones[0].getName().c_str() : "-",
                 sk.getBonesCount() ? bones[sk.getBonesCount() - 1].getName().c_str() : "-", Runtime::context() ? "gpu" : "none");
+    }
     fclose(g_out);
+    std::fflush(stdout);
     Runtime::shutdown();
     return 0;
 }
@@ -141,6 +144,7 @@ static int cmd_batch(int argc, char** argv)
     const float   dt  = (float)std::atof(argv[6]);
     auto          mesh = AnimationLoader().loadMeshData(argv[7]);
     g_out              = fopen(argv[8], "wb");
+    {
     AnimationBatch batch;
     if (!batch.create(*res, N))
     {
@@ -174,6 +178,8 @@ static int cmd_batch(int argc, char** argv)
     }
     fclose(g_out);
     std::printf("batch ok N=%lld J=%d\n", (long long)N, batch.boneCount());
+    }
+    std::fflush(stdout);
     Runtime::shutdown();
     return 0;
 }
