@@ -98,16 +98,27 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def build_workload(n_inst):
+def build_workload(first, n_inst):
+    """Instances [first, first + n_inst) of the global crowd (per-instance inputs depend only on the global id,
+    so a rank's shard is identical to the same range of an unsharded run)."""
     from piccolo_b200 import assets as A
     sk, cl, am, mk = A.load_player()
     run = A.make_variant_clip(cl, 17, seed=1234)
     mesh = A.make_player_mesh(sk, V=V_PLAYER, seed=42)
-    i = np.arange(n_inst, dtype=np.float64)
+    i = np.arange(first, first + n_inst, dtype=np.float64)
     w = np.modf(i * 0.7548776662)[0].astype(np.float32)
     weight = np.stack([w, np.float32(1) - w], 1)
     phase = np.stack([np.modf(i * 0.6180339887)[0], np.modf(i * 0.6180339887 + 0.5)[0]], 1).astype(np.float32)
     return sk, cl, run, am, mk, mesh, phase, weight
+
+
+def profiled_traffic():
+    """DRAM bytes per LBS launch from the committed ncu capture of this very launch shape (25 000 instances)."""
+    p = os.path.join(ROOT, "profiles", "lbs_traffic.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return None
 
 
 def lbs_algorithmic_bytes(count, V, J, out_bytes):
@@ -118,42 +129,29 @@ def lbs_algorithmic_bytes(count, V, J, out_bytes):
 def run_ours(args):
     import torch
     from piccolo_b200 import capi
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    dist = None
+    from piccolo_b200.sharding import RankGroup, shard_range
+    grp = RankGroup(backend="nccl", device=torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))))
+    rank, local, world = grp.rank, grp.local, grp.world
     torch.cuda.set_device(local)
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    barrier, max_over_ranks = grp.barrier, grp.max
 
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    N = args.instances
-    sk, cl, run, am, mk, mesh, phase, weight = build_workload(N)
+    N = args.instances  # per GPU (weak scaling): the global crowd has N * world instances
+    first, count = shard_range(N * world, world, rank)
+    assert count == N
+    sk, cl, run, am, mk, mesh, phase, weight = build_workload(first, N)
     ctx = capi.Context(local)
     skel = ctx.upload_skeleton(sk)
     c0, c1 = ctx.upload_clip(skel, cl, am), ctx.upload_clip(skel, run, am)
     mh = ctx.upload_mesh(mesh, sk.J)
     b = ctx.batch(skel, N, 2)
-    # every rank animates its own shard: offset the phases so shards differ
-    phase = np.modf(phase.astype(np.float64) + 0.37 * rank)[0].astype(np.float32)
     b.set(clip_ids=np.tile(np.int32([c0, c1]), (N, 1)), phase=phase, weight=weight, clip_len=np.tile(np.float32([CLIP_LEN, 17.0 / 30.0]), (N, 1)))
     ring = min(RING_SLOTS, N)
     sb = ctx.skinbuf(mh, mesh.V, ring, capi.PCL_SKIN_POS_NRM_TAN)
     chunks = [(f, min(ring, N - f)) for f in range(0, N, ring)]
     if args.lbs_variant is not None:
         ctx.set_option("lbs_variant", args.lbs_variant)
+    if args.lbs_warps:
+        ctx.set_option("lbs_warps", args.lbs_warps)
 
     def skin_all():
         for f, n in chunks:
@@ -202,13 +200,18 @@ def run_ours(args):
     per_launch = np.mean([lbs_algorithmic_bytes(n, mesh.V, sk.J, 36) for _, n in chunks])
     achieved = per_launch / (lbs_ms * 1e-3) / 1e9
     pose_bytes = N * (2 * 12 + 60 * 48)
-    roofline = {"bound": "hbm", "kernel": "lbs_kernel<NT=1>", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "lbs_inst_kernel<NT=1>" if (args.lbs_variant in (None, -1, 2)) else "lbs_kernel<NT=1>", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(per_launch), "launch_ms": round(lbs_ms, 4),
                 "frac_of_nominal_8000": round(achieved / 8000.0, 4),
                 "pose_kernel": {"launch_ms": round(pose_ms, 4), "achieved": round(pose_bytes / (pose_ms * 1e-3) / 1e9, 1),
                                 "frac": round(pose_bytes / (pose_ms * 1e-3) / 1e9 / peak, 4),
                                 "joints_per_s": round(N * sk.J / (pose_ms * 1e-3), 0)}}
+
+    tr = profiled_traffic()
+    if tr and tr.get("instances_per_launch") == chunks[0][1] and tr.get("vertices") == mesh.V:
+        roofline["traffic"] = tr["dram_bytes_per_launch"]
+        roofline["traffic_source"] = tr["source"]
 
     # ---- end to end through the C ABI with host buffers -------------------------------------------
     for _ in range(max(1, args.warmup // 2)):
@@ -245,9 +248,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(sk, cl, am, mk, mesh, budget_s=args.cpu_budget)
     sb.close(), b.close(), ctx.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    grp.close()
     if rank == 0:
         print(json.dumps(out), flush=True)
 
@@ -309,7 +310,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sk, cl, run, am, mk, mesh, phase, weight = build_workload(1024)
+    sk, cl, run, am, mk, mesh, phase, weight = build_workload(0, 1024)
     threads = os.cpu_count() or 1
     budget = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     rates, kind, sample = [], "port", ""
@@ -339,6 +340,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--instances", type=int, default=100000, help="instances per GPU")
     ap.add_argument("--lbs-variant", type=int, default=None)
+    ap.add_argument("--lbs-warps", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=16.0)
     args = ap.parse_args()

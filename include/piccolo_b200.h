@@ -194,7 +194,8 @@ int pcl_batch_download_palette_static(pcl_batch* b, int64_t first, int64_t count
 /* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
 /* key: "pose_warps_per_block" (0 = auto, 1,2,4,8); "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with
  * coalesced 128-bit stores, 1 = same with TMA bulk stores, 2 = lane-per-instance crowd kernel);
- * "lbs_vsplit" (0 = auto); "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only).
+ * "lbs_warps" (0 = auto, 8, 12: resident warps per SM of the crowd kernel); "lbs_vsplit" (0 = auto);
+ * "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only).
  * PCL_ERR_INVALID for unknown keys. */
 int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
 

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libpiccolo_b200.so")
+LIB_PATH = os.environ.get("PICCOLO_B200_LIB") or os.path.join(PKG, "libpiccolo_b200.so")  # env override: kernel experiments only
 
 PCL_ADVANCE_FIRST_ONLY = 1
 PCL_ADVANCE_ALL = 2

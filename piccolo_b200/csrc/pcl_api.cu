@@ -67,7 +67,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0;
+    int32_t      opt_pose_wpb = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0;
     int          max_smem_optin = 0, sm_count = 0;
 };
 
@@ -315,6 +315,8 @@ extern "C"
             c->opt_pose_wpb = v;
         else if (k == "lbs_variant" && v >= -1 && v <= 2)
             c->opt_lbs_variant = v;
+        else if (k == "lbs_warps" && (v == 0 || v == 8 || v == 12))
+            c->opt_lbs_warps = v;
         else if (k == "lbs_vsplit" && v >= 0)
             c->opt_lbs_vsplit = v;
         else if (k == "lbs_inst_tile" && v >= 0 && v <= 16)
@@ -925,7 +927,11 @@ extern "C"
         // enough instances to fill the lanes; otherwise the lane = vertex kernel
         {
             const int    prow   = (s.pitch * 3) | 1; // odd number of 16-byte units per palette row
-            const size_t smem_i = lbs_i_smem_bytes(prow);
+            int          warps  = c->opt_lbs_warps ? c->opt_lbs_warps : 12;
+            if (warps == 12 && lbs_i_smem_bytes(prow, 12, true) > (size_t)c->max_smem_optin)
+                warps = 8;
+            const bool   half   = warps == 12;
+            const size_t smem_i = lbs_i_smem_bytes(prow, warps, half);
             const bool   fits   = m.d_vrec && smem_i <= (size_t)c->max_smem_optin;
             int          var    = c->opt_lbs_variant;
             if (var == 2 && !fits)
@@ -941,20 +947,20 @@ extern "C"
                 const long long tiles = (count + 31) / 32;
                 int             vs    = c->opt_lbs_vsplit;
                 if (vs == 0) // >= 8 CTAs per SM overall, but keep runs long (each warp restarts cold)
-                    vs = (int)std::max<long long>(1, std::min<long long>(q.n_chunks / (LBS_I_WARPS * 16) + 1, (8LL * c->sm_count + tiles - 1) / tiles));
+                    vs = (int)std::max<long long>(1, std::min<long long>(q.n_chunks / (warps * 16) + 1, (8LL * c->sm_count + tiles - 1) / tiles));
                 vs       = std::max(1, std::min(vs, q.n_chunks));
                 q.vsplit = vs;
                 const unsigned grid = (unsigned)(tiles * vs);
-                if (nt)
-                {
-                    PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i));
-                    lbs_inst_kernel<true><<<grid, LBS_I_WARPS * 32, smem_i, c->compute>>>(q);
-                }
-                else
-                {
-                    PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i));
-                    lbs_inst_kernel<false><<<grid, LBS_I_WARPS * 32, smem_i, c->compute>>>(q);
-                }
+#define PCL_LAUNCH_LBSI(NT_, W_, H_)                                                                                               \
+    {                                                                                                                              \
+        PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<NT_, W_, H_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i)); \
+        lbs_inst_kernel<NT_, W_, H_><<<grid, W_ * 32, smem_i, c->compute>>>(q);                                                    \
+    }
+                if (nt && half) PCL_LAUNCH_LBSI(true, 12, true)
+                else if (nt) PCL_LAUNCH_LBSI(true, 8, false)
+                else if (half) PCL_LAUNCH_LBSI(false, 12, true)
+                else PCL_LAUNCH_LBSI(false, 8, false)
+#undef PCL_LAUNCH_LBSI
                 c->launches++;
                 PCL_CK(c, cudaGetLastError());
                 return PCL_OK;

@@ -614,18 +614,19 @@ namespace pcl
         int32_t       Vp, n_chunks, pitch, prow, vsplit; // prow: shared-memory palette row stride in float4 (odd)
     };
 
-    constexpr int LBS_I_WARPS   = 8;
-    constexpr int LBS_I_CHUNK   = 8;  // vertices per flush
+    constexpr int LBS_I_CHUNK   = 8;  // vertices per position flush
     constexpr int LBS_I_VSTAGES = 4;  // vertex-record chunks in flight per warp
     constexpr int LBS_I_POSROW  = LBS_I_CHUNK * 3 + 4; // floats; /4 odd -> conflict-free 128-bit column stores
-    constexpr int LBS_I_NTROW   = LBS_I_CHUNK * 6 + 4;
+    // normal+tangent staging row: a whole chunk (12 units) or, in the HALF form that trades a little flush
+    // efficiency for 50 % more resident warps, 4 vertices (6 units)
+    __host__ __device__ constexpr int lbs_i_ntrow(bool half) { return half ? 4 * 6 + 4 : LBS_I_CHUNK * 6 + 4; }
 
-    __host__ __device__ inline size_t lbs_i_smem_bytes(int prow)
+    __host__ __device__ inline size_t lbs_i_smem_bytes(int prow, int warps, bool half)
     {
         return (size_t)32 * prow * 16                                             // palettes
-               + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4        // staging tiles
-               + (size_t)LBS_I_WARPS * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec)   // vertex records
-               + 8 * (1 + LBS_I_WARPS * LBS_I_VSTAGES) + 64;                      // mbarriers
+               + (size_t)warps * 32 * (LBS_I_POSROW + lbs_i_ntrow(half)) * 4       // staging tiles
+               + (size_t)warps * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec)        // vertex records
+               + 8 * (1 + warps * LBS_I_VSTAGES) + 64;                            // mbarriers
     }
 
     // one bone matrix (3 rows) from this lane's palette row; off3 = slot * 3 (16-byte units)
@@ -635,42 +636,44 @@ namespace pcl
         m[0] = s[0], m[1] = s[1], m[2] = s[2];
     }
 
-    // Flush of one 8-vertex chunk with coalesced 128-bit stores.  Lane -> (staging row, 16-byte unit) maps
-    // every quarter-warp onto ONE row (positions: 6 units, lanes 6,7 of each quarter idle; normal/tangent
-    // units 0-7) or onto rows r and r+4 (units 8-11 of the 12-unit normal/tangent rows), which keeps the
-    // reads conflict-free with the odd row strides the 128-bit column stores need.  All lane-dependent
-    // address parts are hoisted by the caller; per store only uniform offsets are added.
-    template<bool NT, bool FULL>
-    __device__ __forceinline__ void lbs_i_flush(const float* spos, const float* snt, int s_pos0, int s_nt0, int s_nt2,
-                                                float4* g_pos0, float4* g_nt0, float4* g_nt2, size_t rowstep_pos /*float4 per 4 instances*/,
-                                                size_t rowstep_nt, size_t chunk_pos /*float4*/, size_t chunk_nt, int lane, int ni)
+    // Flushes with coalesced 128-bit stores.  Lane -> (staging row, 16-byte unit) maps every quarter-warp
+    // onto ONE row (6-unit rows: lanes 6,7 of each quarter idle; 12-unit rows: units 0-7) or onto rows r and
+    // r+4 (units 8-11 of the 12-unit rows), which keeps the reads conflict-free with the odd row strides the
+    // 128-bit column stores need.  All lane-dependent address parts are hoisted by the caller.
+    template<bool FULL, int ROW>
+    __device__ __forceinline__ void lbs_i_flush6(const float* tile, int s0, float4* g0, size_t rowstep, size_t off, int lane, int ni)
     {
-        const int a = lane >> 3, b = lane & 7, c4 = ((lane >> 2) & 1) * 4;
+        const int a = lane >> 3, b = lane & 7;
         if (b < 6)
         {
 #pragma unroll
             for (int it = 0; it < 8; it++)
                 if (FULL || it * 4 + a < ni)
-                    g_pos0[chunk_pos + it * rowstep_pos] = *reinterpret_cast<const float4*>(spos + s_pos0 + it * 4 * LBS_I_POSROW);
+                    g0[off + it * rowstep] = *reinterpret_cast<const float4*>(tile + s0 + it * 4 * ROW);
         }
-        if (NT)
-        {
+    }
+    template<bool FULL, int ROW>
+    __device__ __forceinline__ void lbs_i_flush12(const float* snt, int s_nt0, int s_nt2, float4* g_nt0, float4* g_nt2, size_t rowstep_nt,
+                                                 size_t chunk_nt, int lane, int ni)
+    {
+        const int a = lane >> 3, c4 = ((lane >> 2) & 1) * 4;
 #pragma unroll
-            for (int g = 0; g < 4; g++)
-            {
-                if (FULL || g * 8 + a < ni)
-                    g_nt0[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + g * 8 * LBS_I_NTROW);
-                if (FULL || g * 8 + 4 + a < ni)
-                    g_nt0[chunk_nt + (2 * g + 1) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + (g * 8 + 4) * LBS_I_NTROW);
-                if (FULL || g * 8 + a + c4 < ni)
-                    g_nt2[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt2 + g * 8 * LBS_I_NTROW);
-            }
+        for (int g = 0; g < 4; g++)
+        {
+            if (FULL || g * 8 + a < ni)
+                g_nt0[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + g * 8 * ROW);
+            if (FULL || g * 8 + 4 + a < ni)
+                g_nt0[chunk_nt + (2 * g + 1) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + (g * 8 + 4) * ROW);
+            if (FULL || g * 8 + a + c4 < ni)
+                g_nt2[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt2 + g * 8 * ROW);
         }
     }
 
-    template<bool NT>
-    __global__ void __launch_bounds__(LBS_I_WARPS * 32, 1) lbs_inst_kernel(const LbsIParams par)
+    template<bool NT, int WARPS, bool HALF>
+    __global__ void __launch_bounds__(WARPS * 32, 1) lbs_inst_kernel(const LbsIParams par)
     {
+        constexpr int LBS_I_WARPS = WARPS;
+        constexpr int LBS_I_NTROW = lbs_i_ntrow(HALF);
         extern __shared__ __align__(128) unsigned char lsm[];
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int tile  = blockIdx.x / par.vsplit;
@@ -794,10 +797,20 @@ namespace pcl
                 sp[0] = op[0], sp[1] = op[1], sp[2] = op[2];
                 if (NT)
                 {
-                    float4* sn = reinterpret_cast<float4*>(snt + lane * LBS_I_NTROW + half * 24);
+                    float4* sn = reinterpret_cast<float4*>(snt + lane * LBS_I_NTROW + (HALF ? 0 : half * 24));
 #pragma unroll
                     for (int q = 0; q < 6; q++)
                         sn[q] = on[q];
+                    if (HALF)
+                    {
+                        __syncwarp();
+                        const size_t off = (size_t)c * (LBS_I_CHUNK * 6 / 4) + half * 6;
+                        if (ni == 32)
+                            lbs_i_flush6<true, LBS_I_NTROW>(snt, s_nt0, g_nt0, rowstep_nt, off, lane, ni);
+                        else
+                            lbs_i_flush6<false, LBS_I_NTROW>(snt, s_nt0, g_nt0, rowstep_nt, off, lane, ni);
+                        __syncwarp();
+                    }
                 }
             }
             __syncwarp();
@@ -809,9 +822,17 @@ namespace pcl
             }
             const size_t chunk_pos = (size_t)c * (LBS_I_CHUNK * 3 / 4), chunk_nt = (size_t)c * (LBS_I_CHUNK * 6 / 4);
             if (ni == 32)
-                lbs_i_flush<NT, true>(spos, snt, s_pos0, s_nt0, s_nt2, g_pos0, g_nt0, g_nt2, rowstep_pos, rowstep_nt, chunk_pos, chunk_nt, lane, ni);
+            {
+                lbs_i_flush6<true, LBS_I_POSROW>(spos, s_pos0, g_pos0, rowstep_pos, chunk_pos, lane, ni);
+                if (NT && !HALF)
+                    lbs_i_flush12<true, LBS_I_NTROW>(snt, s_nt0, s_nt2, g_nt0, g_nt2, rowstep_nt, chunk_nt, lane, ni);
+            }
             else
-                lbs_i_flush<NT, false>(spos, snt, s_pos0, s_nt0, s_nt2, g_pos0, g_nt0, g_nt2, rowstep_pos, rowstep_nt, chunk_pos, chunk_nt, lane, ni);
+            {
+                lbs_i_flush6<false, LBS_I_POSROW>(spos, s_pos0, g_pos0, rowstep_pos, chunk_pos, lane, ni);
+                if (NT && !HALF)
+                    lbs_i_flush12<false, LBS_I_NTROW>(snt, s_nt0, s_nt2, g_nt0, g_nt2, rowstep_nt, chunk_nt, lane, ni);
+            }
             __syncwarp();
         }
     }

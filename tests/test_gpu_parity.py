@@ -309,9 +309,11 @@ def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
     mh = ctx.upload_mesh(mesh, 58)
     ph = np.random.default_rng(V).uniform(0, 1, N).astype(np.float32)
     for flags in (capi.PCL_SKIN_POS_NRM_TAN, capi.PCL_SKIN_POS):
-        for vsplit, it in ((0, 0), (1, 16), (3, 5)):
+        for vsplit, it, warps in ((0, 0, 0), (1, 16, 8), (3, 5, 12)):
+            ctx.set_option("lbs_warps", warps)
             pos, nt, pal = _skin(ctx, skel, clip, mh, V, N, ph, flags, variant, vsplit, it)
             _check_skin(oracle, mesh, pal, pos, nt)
+    ctx.set_option("lbs_warps", 0)
 
 
 @pytest.mark.parametrize("variant", [0, 1, -1, 2])
