@@ -596,7 +596,7 @@ extern "C"
         // a bone that was already resident for the previous vertex keeps its slot; unused slots keep the
         // resident bone with weight 0 (an exact zero contribution).  The blend is then summed in slot order,
         // which differs from the shader's x,y,z,w order only by a permutation of the same four products.
-        std::vector<VRec> hv(m.Vt);
+        std::vector<VRec> hv((size_t)m.Vt + LBS_I_SCH * LBS_I_CHUNK); // tail padding: a record stage may overrun the last chunk
         std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
         if (max_slot * 3 <= 0xffff)
         {
@@ -640,7 +640,7 @@ extern "C"
                 r.i23  = (uint32_t)slot_i[2] * 3u | (((uint32_t)slot_i[3] * 3u) << 16);
                 r.mask = mask;
             }
-            for (int v = V; v < m.Vt; v++) // padding keeps the last real vertex's slots resident
+            for (size_t v = V; v < hv.size(); v++) // padding keeps the last real vertex's slots resident
                 hv[v].i01 = hv[V - 1].i01, hv[v].i23 = hv[V - 1].i23;
         }
         int rc;
@@ -927,7 +927,7 @@ extern "C"
         // enough instances to fill the lanes; otherwise the lane = vertex kernel
         {
             const int    prow   = (s.pitch * 3) | 1; // odd number of 16-byte units per palette row
-            int          warps  = c->opt_lbs_warps ? c->opt_lbs_warps : 12;
+            int          warps  = c->opt_lbs_warps ? c->opt_lbs_warps : 8; // measured: 8 warps + whole-chunk flush beats 12 warps + half flush
             if (warps == 12 && lbs_i_smem_bytes(prow, 12, true) > (size_t)c->max_smem_optin)
                 warps = 8;
             const bool   half   = warps == 12;
@@ -946,8 +946,21 @@ extern "C"
                 q.Vp = m.Vp, q.n_chunks = m.Vp / LBS_I_CHUNK, q.pitch = s.pitch, q.prow = prow;
                 const long long tiles = (count + 31) / 32;
                 int             vs    = c->opt_lbs_vsplit;
-                if (vs == 0) // >= 8 CTAs per SM overall, but keep runs long (each warp restarts cold)
-                    vs = (int)std::max<long long>(1, std::min<long long>(q.n_chunks / (warps * 16) + 1, (8LL * c->sm_count + tiles - 1) / tiles));
+                if (vs == 0)
+                {
+                    // One CTA per SM is resident, so the grid runs in waves of sm_count CTAs: pick the vertex split
+                    // whose last wave is fullest (ties: fewer splits, i.e. longer runs - every warp restarts cold),
+                    // among splits that leave each warp at least 16 chunks and, for small launches, give every SM work.
+                    const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_chunks / (warps * 16)));
+                    double    best   = -1.0;
+                    for (int cand = 1; cand <= max_vs; cand++)
+                    {
+                        const double waves = (double)(tiles * cand) / c->sm_count;
+                        const double eff   = waves / std::ceil(waves);
+                        if (eff > best + 0.02)
+                            best = eff, vs = cand;
+                    }
+                }
                 vs       = std::max(1, std::min(vs, q.n_chunks));
                 q.vsplit = vs;
                 const unsigned grid = (unsigned)(tiles * vs);

@@ -615,7 +615,8 @@ namespace pcl
     };
 
     constexpr int LBS_I_CHUNK   = 8;  // vertices per position flush
-    constexpr int LBS_I_VSTAGES = 4;  // vertex-record chunks in flight per warp
+    constexpr int LBS_I_VSTAGES = 3;  // vertex-record stages in flight per warp
+    constexpr int LBS_I_SCH     = 2;  // chunks per stage: one mbarrier wait (~100 cycles even when complete) per 16 vertices
     constexpr int LBS_I_POSROW  = LBS_I_CHUNK * 3 + 4; // floats; /4 odd -> conflict-free 128-bit column stores
     // normal+tangent staging row: a whole chunk (12 units) or, in the HALF form that trades a little flush
     // efficiency for 50 % more resident warps, 4 vertices (6 units)
@@ -625,7 +626,7 @@ namespace pcl
     {
         return (size_t)32 * prow * 16                                             // palettes
                + (size_t)warps * 32 * (LBS_I_POSROW + lbs_i_ntrow(half)) * 4       // staging tiles
-               + (size_t)warps * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec)        // vertex records
+               + (size_t)warps * LBS_I_VSTAGES * LBS_I_SCH * LBS_I_CHUNK * sizeof(VRec) // vertex records
                + 8 * (1 + warps * LBS_I_VSTAGES) + 64;                            // mbarriers
     }
 
@@ -685,9 +686,9 @@ namespace pcl
         float*    spos  = reinterpret_cast<float*>(lsm + (size_t)32 * par.prow * 16) + (size_t)warp * 32 * (LBS_I_POSROW + LBS_I_NTROW);
         float*    snt   = spos + 32 * LBS_I_POSROW;
         VRec*     vring = reinterpret_cast<VRec*>(lsm + (size_t)32 * par.prow * 16 + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4) +
-                      (size_t)warp * LBS_I_VSTAGES * LBS_I_CHUNK;
+                      (size_t)warp * LBS_I_VSTAGES * LBS_I_SCH * LBS_I_CHUNK;
         uint64_t* bars  = reinterpret_cast<uint64_t*>(lsm + (size_t)32 * par.prow * 16 + (size_t)LBS_I_WARPS * 32 * (LBS_I_POSROW + LBS_I_NTROW) * 4 +
-                                                     (size_t)LBS_I_WARPS * LBS_I_VSTAGES * LBS_I_CHUNK * sizeof(VRec));
+                                                     (size_t)LBS_I_WARPS * LBS_I_VSTAGES * LBS_I_SCH * LBS_I_CHUNK * sizeof(VRec));
         uint64_t* vbar  = bars + 1 + warp * LBS_I_VSTAGES;
 
         // this warp's run of vertex chunks
@@ -711,11 +712,12 @@ namespace pcl
             for (int i = 0; i < ni; i++)
                 tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + i0 + i) * par.pitch * 3, row_bytes, &bars[0]);
         }
+        constexpr uint32_t STAGE_BYTES = LBS_I_SCH * LBS_I_CHUNK * sizeof(VRec); // the record array is padded, a stage may overrun c_hi
         if (lane == 0)
-            for (int st = 0; st < LBS_I_VSTAGES && c_lo + st < c_hi; st++)
+            for (int st = 0; st < LBS_I_VSTAGES && c_lo + st * LBS_I_SCH < c_hi; st++)
             {
-                mbar_expect_tx(&vbar[st], LBS_I_CHUNK * sizeof(VRec));
-                tma_load(vring + st * LBS_I_CHUNK, par.vrec + (size_t)(c_lo + st) * LBS_I_CHUNK, LBS_I_CHUNK * sizeof(VRec), &vbar[st]);
+                mbar_expect_tx(&vbar[st], STAGE_BYTES);
+                tma_load(vring + st * LBS_I_SCH * LBS_I_CHUNK, par.vrec + (size_t)(c_lo + st * LBS_I_SCH) * LBS_I_CHUNK, STAGE_BYTES, &vbar[st]);
             }
         mbar_wait(&bars[0], 0);
         if (c_lo >= c_hi)
@@ -741,10 +743,15 @@ namespace pcl
 
         for (int c = c_lo; c < c_hi; c++)
         {
-            const int      st = (c - c_lo) % LBS_I_VSTAGES;
-            const uint32_t ph = ((c - c_lo) / LBS_I_VSTAGES) & 1;
-            mbar_wait(&vbar[st], ph);
-            const VRec* vr = vring + st * LBS_I_CHUNK;
+            const int sidx = (c - c_lo) / LBS_I_SCH, sub = (c - c_lo) - sidx * LBS_I_SCH;
+            const int st   = sidx % LBS_I_VSTAGES;
+            if (sub == 0)
+                mbar_wait(&vbar[st], (uint32_t)(sidx / LBS_I_VSTAGES) & 1);
+            const VRec* vr = vring + (st * LBS_I_SCH + sub) * LBS_I_CHUNK;
+            // records are fetched one vertex ahead so that the broadcast loads overlap the previous vertex's math
+            float4 na = *reinterpret_cast<const float4*>(&vr[0].px), nb = *reinterpret_cast<const float4*>(&vr[0].nx);
+            float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].tx);
+            uint4  nd = *reinterpret_cast<const uint4*>(&vr[0].w3);
 #pragma unroll
             for (int half = 0; half < 2; half++)
             {
@@ -754,10 +761,15 @@ namespace pcl
 #pragma unroll
                 for (int j = 0; j < 4; j++)
                 {
-                    const float4 a = *reinterpret_cast<const float4*>(&vr[half * 4 + j].px);
-                    const float4 b = *reinterpret_cast<const float4*>(&vr[half * 4 + j].nx);
-                    const float4 t = *reinterpret_cast<const float4*>(&vr[half * 4 + j].tx);
-                    const uint4  d = *reinterpret_cast<const uint4*>(&vr[half * 4 + j].w3);
+                    const float4 a = na, b = nb, t = nt_;
+                    const uint4  d = nd;
+                    if (half * 4 + j + 1 < LBS_I_CHUNK)
+                    {
+                        na  = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].px);
+                        nb  = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].nx);
+                        nt_ = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].tx);
+                        nd  = *reinterpret_cast<const uint4*>(&vr[half * 4 + j + 1].w3);
+                    }
                     if (d.w) // some slot changes bone at this vertex (warp-uniform, rare in a coherent mesh)
                     {
                         if (d.w & 1) lbs_i_load(m[0], prow, d.y & 0xffffu);
@@ -814,11 +826,12 @@ namespace pcl
                 }
             }
             __syncwarp();
-            // the records of this stage are consumed: refill it with the chunk LBS_I_VSTAGES ahead
-            if (lane == 0 && c + LBS_I_VSTAGES < c_hi)
+            // the records of this stage are consumed: refill it with the stage LBS_I_VSTAGES ahead
+            if (lane == 0 && sub == LBS_I_SCH - 1 && c_lo + (sidx + LBS_I_VSTAGES) * LBS_I_SCH < c_hi)
             {
-                mbar_expect_tx(&vbar[st], LBS_I_CHUNK * sizeof(VRec));
-                tma_load(vring + st * LBS_I_CHUNK, par.vrec + (size_t)(c + LBS_I_VSTAGES) * LBS_I_CHUNK, LBS_I_CHUNK * sizeof(VRec), &vbar[st]);
+                mbar_expect_tx(&vbar[st], STAGE_BYTES);
+                tma_load(vring + st * LBS_I_SCH * LBS_I_CHUNK, par.vrec + (size_t)(c_lo + (sidx + LBS_I_VSTAGES) * LBS_I_SCH) * LBS_I_CHUNK, STAGE_BYTES,
+                         &vbar[st]);
             }
             const size_t chunk_pos = (size_t)c * (LBS_I_CHUNK * 3 / 4), chunk_nt = (size_t)c * (LBS_I_CHUNK * 6 / 4);
             if (ni == 32)
