@@ -192,7 +192,8 @@ int pcl_skinbuf_download(pcl_skinbuf* s, int64_t slot_first, int64_t count, floa
 int pcl_batch_download_palette_static(pcl_batch* b, int64_t first, int64_t count, float* host16);
 
 /* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
-/* key: "pose_warps_per_block" (0 = auto, 1,2,4,8); "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with
+/* key: "pose_warps_per_block" (0 = auto, 1,2,4,8); "pose_generic" (1 = always use the channel-ordered pose kernel,
+ * 0 = use the step-ordered one whenever the skeleton's clips allow it); "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with
  * coalesced 128-bit stores, 1 = same with TMA bulk stores, 2 = lane-per-instance crowd kernel);
  * "lbs_warps" (0 = auto, 8, 12: resident warps per SM of the crowd kernel); "lbs_vsplit" (0 = auto);
  * "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only).

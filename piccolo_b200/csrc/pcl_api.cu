@@ -22,6 +22,8 @@ namespace
     {
         int32_t              J = 0, pitch = 0, nslot = 0;
         std::vector<int32_t> index, parent, order;
+        std::vector<StepRec> h_steps;       // host copy: source of the __constant__ upload
+        int32_t              n_clips = 0, n_simple = 0;
         StepRec*             d_steps = nullptr;
         int32_t*             d_masks = nullptr; // [n_masks][J]
         int32_t              n_masks = 0, cap_masks = 0;
@@ -53,6 +55,15 @@ static __device__ __align__(256) unsigned char g_static_export[PCL_STATIC_EXPORT
 #define PCL_STATIC_MAX_DEVICES 64
 static void* g_static_export_addr[PCL_STATIC_MAX_DEVICES]; // device address of the array, per device (0 = not looked up yet)
 
+// Which skeleton's step records currently sit in the device's __constant__ bank (pose_simple_kernel).  The bank is
+// per device, shared by every context on it.
+struct ConstOwner
+{
+    pcl_ctx* ctx  = nullptr;
+    int      skel = -1;
+};
+static ConstOwner g_const_owner[PCL_STATIC_MAX_DEVICES];
+
 struct pcl_ctx
 {
     int          device = 0;
@@ -67,7 +78,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0;
     int          max_smem_optin = 0, sm_count = 0;
 };
 
@@ -242,6 +253,8 @@ extern "C"
             return PCL_ERR_INVALID;
         cudaSetDevice(c->device);
         cudaDeviceSynchronize();
+        if (c->device < PCL_STATIC_MAX_DEVICES && g_const_owner[c->device].ctx == c)
+            g_const_owner[c->device] = ConstOwner();
         for (auto& s : c->skels)
             cudaFree(s.d_steps), cudaFree(s.d_masks);
         for (auto& cl : c->clips)
@@ -313,6 +326,8 @@ extern "C"
         std::string k(key);
         if (k == "pose_warps_per_block" && (v == 0 || v == 1 || v == 2 || v == 4 || v == 8))
             c->opt_pose_wpb = v;
+        else if (k == "pose_generic" && (v == 0 || v == 1))
+            c->opt_pose_generic = v;
         else if (k == "lbs_variant" && v >= -1 && v <= 2)
             c->opt_lbs_variant = v;
         else if (k == "lbs_warps" && (v == 0 || v == 8 || v == 12))
@@ -398,6 +413,7 @@ extern "C"
         int rc = upload(c, &s.d_steps, steps);
         if (rc != PCL_OK)
             return rc;
+        s.h_steps = steps;
         c->skels.push_back(std::move(s));
         *out = (pcl_skel)c->skels.size() - 1;
         return PCL_OK;
@@ -488,10 +504,40 @@ extern "C"
                 keys[((size_t)n * F + k) * 3 + 2] = make_float4(s[0], s[1], s[2], 0.f);
             }
         }
-        // one device blob: keys | first | next | hi_clamp
+        // step-ordered form for pose_simple_kernel: possible when no bone is driven by two played channels
+        SkelRec&             sk     = c->skels[skel];
+        bool                 simple = true;
+        for (int n = 0; n < NCH && simple; n++)
+            if (convert[n] != -1 && next[n] >= 0)
+                simple = false;
+        const int            Jp = (J + POSE_G - 1) / POSE_G * POSE_G + POSE_G;
+        std::vector<float4>  skeys;
+        std::vector<int32_t> shic;
+        if (simple)
+        {
+            skeys.assign((size_t)Jp * F * 3, make_float4(0, 0, 0, 0));
+            shic.assign(Jp, -F);
+            for (int st = 0; st < Jp; st++)
+            {
+                const int ch = st < J ? first[sk.order[st]] : -1;
+                for (int k = 0; k < F; k++)
+                    if (ch >= 0)
+                        for (int r = 0; r < 3; r++)
+                            skeys[((size_t)st * F + k) * 3 + r] = keys[((size_t)ch * F + k) * 3 + r];
+                    else
+                    {
+                        skeys[((size_t)st * F + k) * 3 + 1] = make_float4(1, 0, 0, 0); // rotation (w,x,y,z) = identity
+                        skeys[((size_t)st * F + k) * 3 + 2] = make_float4(1, 1, 1, 0); // scale 1, translation stays 0
+                    }
+                if (ch >= 0)
+                    shic[st] = hic[ch];
+            }
+        }
+        // one device blob: keys | first | next | hi_clamp | step-ordered keys | step-ordered clamps
         const size_t kb = keys.size() * sizeof(float4), fb = (size_t)J * 4, nb = next.size() * 4, hb = hic.size() * 4;
+        const size_t skb = skeys.size() * sizeof(float4), shb = shic.size() * 4;
         auto         up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
-        const size_t total = up16(kb) + up16(fb) + up16(nb) + up16(hb);
+        const size_t total = up16(kb) + up16(fb) + up16(nb) + up16(hb) + up16(skb) + up16(shb) + 16;
         ClipHost     ch;
         ch.skel = skel;
         PCL_CK(c, cudaMalloc(&ch.d_blob, total));
@@ -500,6 +546,12 @@ extern "C"
         PCL_CK(c, cudaMemcpy(d + up16(kb), first.data(), fb, cudaMemcpyHostToDevice));
         PCL_CK(c, cudaMemcpy(d + up16(kb) + up16(fb), next.data(), nb, cudaMemcpyHostToDevice));
         PCL_CK(c, cudaMemcpy(d + up16(kb) + up16(fb) + up16(nb), hic.data(), hb, cudaMemcpyHostToDevice));
+        unsigned char* d2 = d + up16(kb) + up16(fb) + up16(nb) + up16(hb);
+        if (simple)
+        {
+            PCL_CK(c, cudaMemcpy(d2, skeys.data(), skb, cudaMemcpyHostToDevice));
+            PCL_CK(c, cudaMemcpy(d2 + up16(skb), shic.data(), shb, cudaMemcpyHostToDevice));
+        }
         ch.rec.keys           = (const float4*)d;
         ch.rec.first_chan     = (const int32_t*)(d + up16(kb));
         ch.rec.next_chan      = (const int32_t*)(d + up16(kb) + up16(fb));
@@ -507,6 +559,11 @@ extern "C"
         ch.rec.F              = F;
         ch.rec.total_frame_m1 = total_frame - 1;
         ch.rec.C              = C;
+        ch.rec.simple         = simple ? 1 : 0;
+        ch.rec.keys_step      = simple ? (const float4*)d2 : nullptr;
+        ch.rec.hic_step       = simple ? (const int32_t*)(d2 + up16(skb)) : nullptr;
+        sk.n_clips++;
+        sk.n_simple += simple ? 1 : 0;
         c->clips.push_back(ch);
         const int id = (int)c->clips.size() - 1;
         if (id >= c->cap_clips)
@@ -824,10 +881,32 @@ extern "C"
             wpb >>= 1;
         const size_t   smem = per_warp * wpb;
         const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
-#define PCL_LAUNCH_POSE(KK)                                                                                          \
-    {                                                                                                                \
-        PCL_CK(c, cudaFuncSetAttribute(pose_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
-        pose_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                    \
+        // step-ordered kernel when every clip of this skeleton has that form and the step records fit the constant bank
+        const bool simple = c->opt_pose_generic == 0 && s.J <= POSE_CMAX && s.n_clips > 0 && s.n_simple == s.n_clips &&
+                            c->device < PCL_STATIC_MAX_DEVICES;
+        if (simple)
+        {
+            ConstOwner& own = g_const_owner[c->device];
+            if (own.ctx != c || own.skel != b->skel)
+            {
+                if (own.ctx && own.ctx != c) // another context's kernels may still be reading the bank
+                    PCL_CK(c, cudaStreamSynchronize(own.ctx->compute));
+                PCL_CK(c, cudaMemcpyToSymbolAsync(c_steps, s.h_steps.data(), s.h_steps.size() * sizeof(StepRec), 0, cudaMemcpyHostToDevice, c->compute));
+                own.ctx = c, own.skel = b->skel;
+            }
+        }
+#define PCL_LAUNCH_POSE(KK)                                                                                                 \
+    {                                                                                                                       \
+        if (simple)                                                                                                         \
+        {                                                                                                                   \
+            PCL_CK(c, cudaFuncSetAttribute(pose_simple_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            pose_simple_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                \
+        }                                                                                                                   \
+        else                                                                                                                \
+        {                                                                                                                   \
+            PCL_CK(c, cudaFuncSetAttribute(pose_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+            pose_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                       \
+        }                                                                                                                   \
     }
         switch (b->K)
         {

@@ -38,7 +38,11 @@ namespace pcl
         int32_t F;
         int32_t total_frame_m1;    // total_frame - 1
         int32_t C;
-        int32_t pad;
+        int32_t simple;            // every bone is driven by at most one played channel: the step-ordered form below exists
+        // step-ordered form (pose_simple_kernel): one track per processing step, the identity track for bones no
+        // channel drives, so a key's address depends only on (step, frame) - no dependent loads on the hot path
+        const float4*  keys_step;  // [Jp][F][3]
+        const int32_t* hic_step;   // [Jp]  hi_clamp of the step's channel (>= 0), or -F for an identity track (clamp F-1)
     };
 
     struct PoseParams
@@ -295,6 +299,281 @@ namespace pcl
                     const int    bone = __ldg(&par.steps[s].joint);
                     const float4 v    = *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
                     par.palette[((size_t)(inst0 + il) * par.pitch + bone + 1) * 3 + (rm - g * 3)] = v;
+                }
+            }
+            __syncwarp();
+        }
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // pose kernel, step-ordered form: same mapping and arithmetic as pose_kernel, for the common case in
+    // which every clip of the launch drives each bone with at most one channel (ClipRec::simple) and the
+    // skeleton's step records fit the constant bank.
+    //   - step records (bind TRS, inverse bind, parent/slot plan) come from __constant__ memory: uniform
+    //     loads through the constant cache instead of 7 global loads per bone per lane
+    //   - keys are read from the clip's step-ordered copy: the address depends on (step, frame) only, so the
+    //     six 128-bit key loads of bone s+1 are issued before bone s is computed (L2 latency hidden);
+    //     the clamp values of a whole group of POSE_G bones arrive as ONE 128-bit load
+    //   - bones without a channel sample the identity track, which reproduces the bind pose exactly
+    //     (q_bind * (1,0,0,0), s_bind * 1, p_bind + 0), so there is no per-bone branching
+    //   - the palette flush uses the conflict-free row mapping of the LBS kernel with hoisted addressing
+    // -------------------------------------------------------------------------------------------
+    constexpr int POSE_CMAX = 320; // bones whose step records fit the constant bank (320 * 112 B = 35 KB)
+    __constant__ StepRec c_steps[POSE_CMAX];
+
+    struct KeyPair
+    {
+        float4 p0, q0, s0, p1, q1, s1;
+    };
+    struct SimpleSlot
+    {
+        const float4*  keys;
+        const int32_t* hic;
+        int32_t        F, lo, hi, mask_off;
+        float          r, w;
+    };
+    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int hc)
+    {
+        const int     h  = max(min(st.hi, hc), 0);
+        const int     l  = max(min(st.lo, h), 0);
+        const float4* kl = st.keys + ((size_t)s * st.F + l) * 3;
+        const float4* kh = st.keys + ((size_t)s * st.F + h) * 3;
+        KeyPair       k;
+        k.p0 = __ldg(kl), k.q0 = __ldg(kl + 1), k.s0 = __ldg(kl + 2);
+        k.p1 = __ldg(kh), k.q1 = __ldg(kh + 1), k.s1 = __ldg(kh + 2);
+        return k;
+    }
+    __device__ __forceinline__ void sample_keys(const KeyPair& k, float r, float3& P, float3& S, Quat& Q)
+    {
+        P = lerp3(make_float3(k.p0.x, k.p0.y, k.p0.z), make_float3(k.p1.x, k.p1.y, k.p1.z), r);
+        S = lerp3(make_float3(k.s0.x, k.s0.y, k.s0.z), make_float3(k.s1.x, k.s1.y, k.s1.z), r);
+        Q = qnlerp(r, Quat {k.q0.x, k.q0.y, k.q0.z, k.q0.w}, Quat {k.q1.x, k.q1.y, k.q1.z, k.q1.w});
+    }
+    __device__ __forceinline__ int pick4(const int4& v, int g) { return g == 0 ? v.x : (g == 1 ? v.y : (g == 2 ? v.z : v.w)); }
+    __device__ __forceinline__ int hic_decode(int v) { return v < 0 ? -1 - v : v; } // identity tracks are stored as -F
+
+    template<int K>
+    __global__ void __launch_bounds__(256) pose_simple_kernel(const PoseParams par)
+    {
+        extern __shared__ __align__(16) float smem[];
+        const int       lane  = threadIdx.x & 31;
+        const int       wib   = threadIdx.x >> 5;
+        const long long wglob = (long long)blockIdx.x * (blockDim.x >> 5) + wib;
+        const long long inst0 = wglob * 32;
+        if (inst0 >= par.N)
+            return;
+        const long long inst   = min(inst0 + lane, par.N - 1);
+        const bool      active = (inst0 + lane) < par.N;
+        const int       ni     = (int)min(32LL, par.N - inst0);
+        float*          slots  = smem + (size_t)wib * pose_smem_floats_per_warp(par.nslot);
+        float*          stage  = slots + (size_t)par.nslot * 10 * 32;
+        constexpr int   SROW   = POSE_G * 12 + 4;
+
+        SimpleSlot st[K];
+#pragma unroll
+        for (int k = 0; k < K; k++)
+        {
+            const size_t  o  = (size_t)k * par.N + inst;
+            const ClipRec cr = par.clips[__ldg(par.clip_ids + o)];
+            float         ph = par.phase[o];
+            if (par.advance == 2 || (par.advance == 1 && k == 0))
+            {
+                ph += par.dt / __ldg(par.clip_len + o); // animation_component.cpp:19-21
+                ph -= floorf(ph);
+                if (active)
+                    par.phase[o] = ph;
+            }
+            const float exact = ph * (float)cr.total_frame_m1; // skeleton.cpp:52-55
+            st[k].lo = (int)floorf(exact), st[k].hi = (int)ceilf(exact), st[k].r = exact - (float)st[k].lo;
+            st[k].keys = cr.keys_step, st[k].hic = cr.hic_step, st[k].F = cr.F;
+            st[k].w = (K > 1) ? __ldg(par.weight + o) : 1.0f;
+            const int mid = (K > 1 && par.mask_ids) ? __ldg(par.mask_ids + o) : -1;
+            st[k].mask_off = mid < 0 ? -1 : mid * par.J;
+        }
+        if (active)
+        {
+            float4* p0 = par.palette + (size_t)inst * par.pitch * 3; // slot 0 = identity (mesh_component.cpp:72-79)
+            p0[0] = make_float4(1, 0, 0, 0), p0[1] = make_float4(0, 1, 0, 0), p0[2] = make_float4(0, 0, 1, 0);
+        }
+        // lane-dependent parts of the flush addresses (rows = instances, 12 units = POSE_G bones x 3 rows)
+        const int fa = lane >> 3, fb = lane & 7, fc4 = ((lane >> 2) & 1) * 4, fd = lane & 3;
+        const int s_f0 = fa * SROW + fb * 4, s_f2 = (fa + fc4) * SROW + (8 + fd) * 4;
+        float4*   g_f0 = par.palette + (size_t)(inst0 + fa) * par.pitch * 3 + fb;
+        float4*   g_f2 = par.palette + (size_t)(inst0 + fa + fc4) * par.pitch * 3 + 8 + fd;
+        const size_t rowstep = (size_t)par.pitch * 3 * 4; // float4 per 4 instances
+
+        TRS prev;
+        prev.p = make_float3(0, 0, 0), prev.q = Quat {1, 0, 0, 0}, prev.s = make_float3(1, 1, 1);
+
+        // software pipeline: clamp values one group ahead, keys one bone ahead (register budget allows it for K <= 2)
+        constexpr bool PREFETCH = K <= 2;
+        int4    hic_cur[K], hic_nxt[K];
+        KeyPair nk[PREFETCH ? K : 1];
+#pragma unroll
+        for (int k = 0; k < K; k++)
+        {
+            hic_cur[k] = __ldg(reinterpret_cast<const int4*>(st[k].hic));
+            hic_nxt[k] = hic_cur[k];
+            if (PREFETCH)
+                nk[k] = fetch_keys(st[k], 0, hic_decode(hic_cur[k].x));
+        }
+
+        for (int s0 = 0; s0 < par.n_steps_padded; s0 += POSE_G)
+        {
+            if (s0 + POSE_G < par.n_steps_padded)
+            {
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                    hic_nxt[k] = __ldg(reinterpret_cast<const int4*>(st[k].hic + s0 + POSE_G));
+            }
+            bool contiguous = true; // the group's palette slots are consecutive (always, unless the upload re-ordered the bones)
+#pragma unroll
+            for (int g = 0; g < POSE_G; g++)
+            {
+                const int s = s0 + g;
+                if (s >= par.J)
+                    break;
+                const StepRec& rec  = c_steps[s];
+                const int      bone = rec.joint;
+                contiguous          = contiguous && (bone == c_steps[s0].joint + g);
+                KeyPair ck[K];
+                int     hcur[K];
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                {
+                    hcur[k] = pick4(hic_cur[k], g);
+                    if (PREFETCH)
+                    {
+                        ck[k] = nk[k];
+                        if (s + 1 < par.J) // keys of the next bone are requested before this one is computed
+                            nk[k] = fetch_keys(st[k], s + 1, hic_decode(g + 1 < POSE_G ? pick4(hic_cur[k], g + 1) : hic_nxt[k].x));
+                    }
+                    else
+                        ck[k] = fetch_keys(st[k], s, hic_decode(hcur[k]));
+                }
+                TRS loc; // resetSkeleton -> Node::resetToInitialPose, skeleton.cpp:45, node.cpp:197-206
+                loc.p = make_float3(rec.bpos.x, rec.bpos.y, rec.bpos.z), loc.q = Quat {rec.brot.x, rec.brot.y, rec.brot.z, rec.brot.w};
+                loc.s = make_float3(rec.bscl.x, rec.bscl.y, rec.bscl.z);
+                if (K == 1)
+                {
+                    // skeleton.cpp:88-100; rotate(LOCAL) node.cpp:135-157, scale :182-186, translate(AREN) :107-132
+                    float3 P, S;
+                    Quat   Q;
+                    sample_keys(ck[0], st[0].r, P, S, Q);
+                    loc.q = qmul(loc.q, qnormalise(Q));
+                    loc.s = loc.s * S;
+                    loc.p = loc.p + P;
+                }
+                else
+                {
+                    // documented blend extension; weights as animation_system.cpp:117-149
+                    float wsum = 0.f;
+                    bool  en[K], touched = false;
+#pragma unroll
+                    for (int k = 0; k < K; k++)
+                    {
+                        en[k] = st[k].mask_off < 0 ? true : (__ldg(par.masks + st[k].mask_off + bone) != 0);
+                        if (en[k])
+                            wsum += st[k].w;
+                        touched |= hcur[k] >= 0;
+                    }
+                    TRS  acc;
+                    Quat qref {1, 0, 0, 0};
+                    bool any = false;
+                    acc.p = make_float3(0, 0, 0), acc.q = Quat {0, 0, 0, 0}, acc.s = make_float3(0, 0, 0);
+#pragma unroll
+                    for (int k = 0; k < K; k++)
+                    {
+                        const float wn = en[k] ? st[k].w / wsum : 0.f;
+                        TRS         d;
+                        sample_keys(ck[k], st[k].r, d.p, d.s, d.q); // identity track == identity delta, exactly
+                        if (fabsf(wsum) >= 0.0001f && wn != 0.f)
+                        {
+                            if (!any)
+                            {
+                                qref  = d.q;
+                                acc.p = wn * d.p, acc.s = wn * d.s, acc.q = qscale(d.q, wn);
+                                any   = true;
+                            }
+                            else
+                            {
+                                const float sg = (qdot(d.q, qref) < 0.0f) ? -wn : wn;
+                                acc.p = acc.p + wn * d.p, acc.s = acc.s + wn * d.s;
+                                acc.q = Quat {acc.q.w + d.q.w * sg, acc.q.x + d.q.x * sg, acc.q.y + d.q.y * sg, acc.q.z + d.q.z * sg};
+                            }
+                        }
+                    }
+                    if (any && touched)
+                    {
+                        loc.q = qmul(loc.q, qnormalise(acc.q));
+                        loc.s = loc.s * acc.s;
+                        loc.p = loc.p + acc.p;
+                    }
+                }
+                // m_bones[i].update(), skeleton.cpp:110-113 -> Node::updateDerivedTransform node.cpp:32-65
+                TRS der;
+                if (rec.psrc == -1)
+                    der = loc;
+                else
+                {
+                    TRS par_trs = prev;
+                    if (rec.psrc >= 0)
+                    {
+                        const float* sp = slots + (size_t)rec.psrc * 320 + lane;
+                        par_trs.p = make_float3(sp[0], sp[32], sp[64]);
+                        par_trs.q = Quat {sp[96], sp[128], sp[160], sp[192]};
+                        par_trs.s = make_float3(sp[224], sp[256], sp[288]);
+                    }
+                    der = compose(par_trs, loc);
+                }
+                if (rec.store >= 0)
+                {
+                    float* sp = slots + (size_t)rec.store * 320 + lane;
+                    sp[0] = der.p.x, sp[32] = der.p.y, sp[64] = der.p.z;
+                    sp[96] = der.q.w, sp[128] = der.q.x, sp[160] = der.q.y, sp[192] = der.q.z;
+                    sp[224] = der.s.x, sp[256] = der.s.y, sp[288] = der.s.z;
+                }
+                prev = der;
+                if (par.derived && active)
+                {
+                    float* o = par.derived + ((size_t)inst * par.J + bone) * 10;
+                    o[0] = der.p.x, o[1] = der.p.y, o[2] = der.p.z, o[3] = der.q.w, o[4] = der.q.x;
+                    o[5] = der.q.y, o[6] = der.q.z, o[7] = der.s.x, o[8] = der.s.y, o[9] = der.s.z;
+                }
+                float4 r0, r1, r2; // outputAnimationResult, skeleton.cpp:119-156
+                palette_rows(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                float4* row = reinterpret_cast<float4*>(stage + (size_t)lane * SROW + g * 12);
+                row[0] = r0, row[1] = r1, row[2] = r2;
+            }
+#pragma unroll
+            for (int k = 0; k < K; k++)
+                hic_cur[k] = hic_nxt[k];
+            __syncwarp();
+            if (contiguous && ni == 32 && s0 + POSE_G <= par.J)
+            {
+                // 32 rows x 12 units, conflict-free (see lbs_i_flush12); the group's 4 slots are 12 consecutive units
+                const size_t off = (size_t)(c_steps[s0].joint + 1) * 3;
+#pragma unroll
+                for (int gq = 0; gq < 4; gq++)
+                {
+                    g_f0[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW);
+                    g_f0[off + (2 * gq + 1) * rowstep] = *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW);
+                    g_f2[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW);
+                }
+            }
+            else
+            {
+#pragma unroll
+                for (int it = 0; it < POSE_G * 3; it++)
+                {
+                    const int f  = it * 32 + lane;
+                    const int il = f / (POSE_G * 3);
+                    const int rm = f % (POSE_G * 3);
+                    const int g  = rm / 3;
+                    const int s  = s0 + g;
+                    if (s < par.J && il < ni)
+                        par.palette[((size_t)(inst0 + il) * par.pitch + c_steps[s].joint + 1) * 3 + (rm - g * 3)] =
+                            *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
                 }
             }
             __syncwarp();

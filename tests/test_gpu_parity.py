@@ -138,6 +138,26 @@ def test_pose_ragged_batch_sizes(ctx, player_dev, oracle, player, N):
     ctx.set_option("pose_warps_per_block", 0)
 
 
+def test_channel_ordered_pose_kernel_stays_correct(ctx, player_dev, oracle, player):
+    """The generic (channel-ordered) kernel is what runs for clips with several channels per bone; force it on the
+    bundled clip and on a blend so that both pose kernels are held to the same goldens."""
+    skel, clip = player_dev
+    sk, cl, am, mk = player
+    g = np.load(os.path.join(GOLDEN, "pose_golden.npz"))
+    ctx.set_option("pose_generic", 1)
+    try:
+        mats = gpu_pose(ctx, skel, np.full((len(g["phases"]), 1), clip), g["phases"])
+        assert_mats_close(mats, g["mats"])
+        other = ctx.upload_clip(skel, A.make_variant_clip(cl, 29, seed=5), am)
+        rng = np.random.default_rng(3)
+        ph, w = rng.uniform(0, 1, (500, 2)).astype(np.float32), rng.uniform(0.1, 1, (500, 2)).astype(np.float32)
+        two = gpu_pose(ctx, skel, np.tile(np.int32([clip, other]), (500, 1)), ph, weight=w)
+    finally:
+        ctx.set_option("pose_generic", 0)
+    same = gpu_pose(ctx, skel, np.tile(np.int32([clip, other]), (500, 1)), ph, weight=w)
+    assert np.abs(two - same).max() <= 2e-6  # both kernels, same arithmetic: differ only by instruction scheduling/FMA
+
+
 def _variants(cl, frames=(17, 23, 29, 31, 37, 41, 47)):
     return [cl] + [A.make_variant_clip(cl, f, seed=100 + i) for i, f in enumerate(frames)]
 
