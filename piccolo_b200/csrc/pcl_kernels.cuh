@@ -332,9 +332,19 @@ namespace pcl
         int32_t        F, lo, hi, mask_off;
         float          r, w;
     };
-    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int hc)
+    // `after` is an opaque zero derived from a value the caller has just computed.  Adding it to the address
+    // pins the loads BEHIND that computation: without it ptxas hoists the next bone's loads right in front of
+    // the current bone's first use, where they share a scoreboard slot with the loads being waited for, and
+    // the intended one-bone prefetch distance collapses to zero (seen in profiles/r1_pose_v1_*).
+    __device__ __forceinline__ int opaque_zero(float v)
     {
-        const int     h  = max(min(st.hi, hc), 0);
+        int z;
+        asm volatile("and.b32 %0, %1, 0;" : "=r"(z) : "r"(__float_as_int(v)));
+        return z;
+    }
+    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int hc, int after = 0)
+    {
+        const int     h  = max(min(st.hi, hc), 0) + after;
         const int     l  = max(min(st.lo, h), 0);
         const float4* kl = st.keys + ((size_t)s * st.F + l) * 3;
         const float4* kh = st.keys + ((size_t)s * st.F + h) * 3;
@@ -442,14 +452,20 @@ namespace pcl
                 for (int k = 0; k < K; k++)
                 {
                     hcur[k] = pick4(hic_cur[k], g);
-                    if (PREFETCH)
-                    {
-                        ck[k] = nk[k];
-                        if (s + 1 < par.J) // keys of the next bone are requested before this one is computed
-                            nk[k] = fetch_keys(st[k], s + 1, hic_decode(g + 1 < POSE_G ? pick4(hic_cur[k], g + 1) : hic_nxt[k].x));
-                    }
-                    else
-                        ck[k] = fetch_keys(st[k], s, hic_decode(hcur[k]));
+                    ck[k]   = PREFETCH ? nk[k] : fetch_keys(st[k], s, hic_decode(hcur[k]));
+                }
+                // this bone's samples first (they consume the keys requested one bone ago) ...
+                float3 P[K], S[K];
+                Quat   Q[K];
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                    sample_keys(ck[k], st[k].r, P[k], S[k], Q[k]);
+                // ... then the next bone's keys are requested; they land while the rest of this bone is computed
+                if (PREFETCH && s + 1 < par.J)
+                {
+#pragma unroll
+                    for (int k = 0; k < K; k++)
+                        nk[k] = fetch_keys(st[k], s + 1, hic_decode(g + 1 < POSE_G ? pick4(hic_cur[k], g + 1) : hic_nxt[k].x), opaque_zero(Q[k].w));
                 }
                 TRS loc; // resetSkeleton -> Node::resetToInitialPose, skeleton.cpp:45, node.cpp:197-206
                 loc.p = make_float3(rec.bpos.x, rec.bpos.y, rec.bpos.z), loc.q = Quat {rec.brot.x, rec.brot.y, rec.brot.z, rec.brot.w};
@@ -457,12 +473,9 @@ namespace pcl
                 if (K == 1)
                 {
                     // skeleton.cpp:88-100; rotate(LOCAL) node.cpp:135-157, scale :182-186, translate(AREN) :107-132
-                    float3 P, S;
-                    Quat   Q;
-                    sample_keys(ck[0], st[0].r, P, S, Q);
-                    loc.q = qmul(loc.q, qnormalise(Q));
-                    loc.s = loc.s * S;
-                    loc.p = loc.p + P;
+                    loc.q = qmul(loc.q, qnormalise(Q[0]));
+                    loc.s = loc.s * S[0];
+                    loc.p = loc.p + P[0];
                 }
                 else
                 {
@@ -485,8 +498,8 @@ namespace pcl
                     for (int k = 0; k < K; k++)
                     {
                         const float wn = en[k] ? st[k].w / wsum : 0.f;
-                        TRS         d;
-                        sample_keys(ck[k], st[k].r, d.p, d.s, d.q); // identity track == identity delta, exactly
+                        TRS         d; // an identity track samples to the identity delta, exactly
+                        d.p = P[k], d.s = S[k], d.q = Q[k];
                         if (fabsf(wsum) >= 0.0001f && wn != 0.f)
                         {
                             if (!any)
@@ -909,6 +922,30 @@ namespace pcl
                + 8 * (1 + warps * LBS_I_VSTAGES) + 64;                            // mbarriers
     }
 
+#ifndef PCL_LBS_FFMA2
+#define PCL_LBS_FFMA2 1
+#endif
+    // packed fp32 pairs (sm_100: fma.rn.f32x2, mul.rn.f32x2)
+    __device__ __forceinline__ unsigned long long pack2(float a, float b)
+    {
+        unsigned long long r;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+        return r;
+    }
+    __device__ __forceinline__ void unpack2(unsigned long long v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+    __device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c)
+    {
+        unsigned long long d;
+        asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+        return d;
+    }
+    __device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b)
+    {
+        unsigned long long d;
+        asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+        return d;
+    }
+
     // one bone matrix (3 rows) from this lane's palette row; off3 = slot * 3 (16-byte units)
     __device__ __forceinline__ void lbs_i_load(float4 (&m)[3], const float4* prow, uint32_t off3)
     {
@@ -1058,6 +1095,23 @@ namespace pcl
                     }
                     const float w0 = a.w, w1 = b.w, w2 = t.w, w3 = __uint_as_float(d.x);
                     // vertex_blending_matrix = sum_k joint_matrices[idx_k] * w_k (mesh.vert:77-102), in slot order
+#if PCL_LBS_FFMA2
+                    // Blackwell packed fp32 (fma.rn.f32x2 / SASS FFMA2): two matrix entries per instruction, same
+                    // rounding as two scalar FMAs
+                    float4 B[3];
+                    {
+                        const unsigned long long ww0 = pack2(w0, w0), ww1 = pack2(w1, w1), ww2 = pack2(w2, w2), ww3 = pack2(w3, w3);
+#pragma unroll
+                        for (int r = 0; r < 3; r++)
+                        {
+                            unsigned long long lo = mul2(pack2(m[0][r].x, m[0][r].y), ww0), hi = mul2(pack2(m[0][r].z, m[0][r].w), ww0);
+                            lo = fma2(pack2(m[1][r].x, m[1][r].y), ww1, lo), hi = fma2(pack2(m[1][r].z, m[1][r].w), ww1, hi);
+                            lo = fma2(pack2(m[2][r].x, m[2][r].y), ww2, lo), hi = fma2(pack2(m[2][r].z, m[2][r].w), ww2, hi);
+                            lo = fma2(pack2(m[3][r].x, m[3][r].y), ww3, lo), hi = fma2(pack2(m[3][r].z, m[3][r].w), ww3, hi);
+                            unpack2(lo, B[r].x, B[r].y), unpack2(hi, B[r].z, B[r].w);
+                        }
+                    }
+#else
                     float4 B[3];
 #pragma unroll
                     for (int r = 0; r < 3; r++)
@@ -1067,6 +1121,7 @@ namespace pcl
                         B[r].x += m[2][r].x * w2, B[r].y += m[2][r].y * w2, B[r].z += m[2][r].z * w2, B[r].w += m[2][r].w * w2;
                         B[r].x += m[3][r].x * w3, B[r].y += m[3][r].y * w3, B[r].z += m[3][r].z * w3, B[r].w += m[3][r].w * w3;
                     }
+#endif
                     // model_position = (B * vec4(p, 1)).xyz (mesh.vert:104)
                     opf[j * 3 + 0] = B[0].x * a.x + B[0].y * a.y + B[0].z * a.z + B[0].w;
                     opf[j * 3 + 1] = B[1].x * a.x + B[1].y * a.y + B[1].z * a.z + B[1].w;
