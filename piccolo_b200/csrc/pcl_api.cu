@@ -879,11 +879,13 @@ extern "C"
             wpb = warps >= 8LL * 4 * c->sm_count ? 4 : (warps >= 8LL * 2 * c->sm_count ? 2 : 1);
         while (wpb > 1 && per_warp * wpb > (size_t)c->max_smem_optin)
             wpb >>= 1;
-        const size_t   smem = per_warp * wpb;
-        const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
         // step-ordered kernel when every clip of this skeleton has that form and the step records fit the constant bank
         const bool simple = c->opt_pose_generic == 0 && s.J <= POSE_CMAX && s.n_clips > 0 && s.n_simple == s.n_clips &&
                             c->device < PCL_STATIC_MAX_DEVICES;
+        if (simple)
+            wpb = std::min(wpb, POSE_S_THREADS / 32);
+        const size_t   smem = per_warp * wpb;
+        const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
         if (simple)
         {
             ConstOwner& own = g_const_owner[c->device];
