@@ -191,6 +191,21 @@ int pcl_skinbuf_download(pcl_skinbuf* s, int64_t slot_first, int64_t count, floa
 #define PCL_STATIC_EXPORT_MAX_BYTES (8u << 20)
 int pcl_batch_download_palette_static(pcl_batch* b, int64_t first, int64_t count, float* host16);
 
+/* ---- render hand-off ------------------------------------------------------------------------------
+ * The per-draw-call joint SSBO of the reference's mesh passes: mat4 joint_matrices[1024 * 64] per draw,
+ * joint_matrices[1024 * instance_in_draw + slot], row-major 4x4, slot 0 = identity, <= 64 instances per draw
+ * (function/render/passes/main_camera_pass.cpp:2284-2298, function/render/render_common.h:19-20,70-73,
+ * engine/shader/include/constants.h:3-7).  pcl_batch_export_render writes instances [first, first+count) into draws
+ * draw_first + i/64 at instance slot i%64, touching only the J+1 live slots of each instance like the reference's copy
+ * loop; the buffer (4 MiB per draw, zeroed at creation) is what a Vulkan/CUDA interop SSBO would alias - the interop
+ * itself is out of scope (no graphics stack on this box). */
+typedef struct pcl_renderbuf pcl_renderbuf;
+int pcl_renderbuf_create(pcl_ctx* ctx, int64_t draws, pcl_renderbuf** out);
+int pcl_renderbuf_destroy(pcl_renderbuf* r);
+int pcl_batch_export_render(pcl_batch* b, int64_t first, int64_t count, pcl_renderbuf* r, int64_t draw_first);
+int pcl_renderbuf_dev(pcl_renderbuf* r, const void** dptr);
+int pcl_renderbuf_download(pcl_renderbuf* r, int64_t draw, float* host /*[64][1024][16]*/);
+
 /* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
 /* key: "pose_warps_per_block" (0 = auto, 1,2,4,8); "pose_generic" (1 = always use the channel-ordered pose kernel,
  * 0 = use the step-ordered one whenever the skeleton's clips allow it); "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with

@@ -62,6 +62,11 @@ SIGNATURES = {
     "pcl_skinbuf_dev": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _ip]),
     "pcl_skinbuf_download": (C.c_int, [_vp, _i64, _i64, _fp, _fp]),
     "pcl_set_option": (C.c_int, [_vp, C.c_char_p, C.c_int32]),
+    "pcl_renderbuf_create": (C.c_int, [_vp, _i64, C.POINTER(_vp)]),
+    "pcl_renderbuf_destroy": (C.c_int, [_vp]),
+    "pcl_batch_export_render": (C.c_int, [_vp, _i64, _i64, _vp, _i64]),
+    "pcl_renderbuf_dev": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "pcl_renderbuf_download": (C.c_int, [_vp, _i64, _fp]),
     "pcl_batch_download_palette_static": (C.c_int, [_vp, _i64, _i64, _fp]),
 }
 
@@ -267,6 +272,10 @@ class Batch:
         self.ctx._ck(self.ctx.L.pcl_batch_download_derived(self.h, first, count, _f(out)))
         return out
 
+    def export_render(self, rb: "RenderBuf", first=0, count=None, draw_first=0):
+        count = self.N - first if count is None else count
+        self.ctx._ck(self.ctx.L.pcl_batch_export_render(self.h, first, count, rb.h, draw_first))
+
     def palette_dev(self):
         p, pitch, fps = _vp(), C.c_int32(), C.c_int32()
         self.ctx._ck(self.ctx.L.pcl_batch_palette_dev(self.h, C.byref(p), C.byref(pitch), C.byref(fps)))
@@ -291,3 +300,23 @@ class SkinBuf:
         nt = np.zeros((count, self.V, 6), np.float32) if self.flags == PCL_SKIN_POS_NRM_TAN else None
         self.ctx._ck(self.ctx.L.pcl_skinbuf_download(self.h, slot_first, count, _f(pos), _f(nt)))
         return pos, nt
+
+
+class RenderBuf:
+    """Per-draw-call joint SSBOs in the reference renderer's layout (pcl_renderbuf_*)."""
+
+    def __init__(self, ctx: Context, draws: int):
+        self.ctx, self.draws = ctx, int(draws)
+        h = _vp()
+        ctx._ck(ctx.L.pcl_renderbuf_create(ctx.h, self.draws, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.ctx.L.pcl_renderbuf_destroy(self.h)
+            self.h = None
+
+    def download(self, draw: int) -> np.ndarray:
+        out = np.zeros((64, 1024, 16), np.float32)
+        self.ctx._ck(self.ctx.L.pcl_renderbuf_download(self.h, draw, _f(out)))
+        return out

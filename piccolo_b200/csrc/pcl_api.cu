@@ -97,6 +97,13 @@ struct pcl_batch
     bool      posed = false;
 };
 
+struct pcl_renderbuf
+{
+    pcl_ctx*  ctx;
+    long long draws;
+    float4*   d_mats = nullptr; // [draws][64][1024][4] float4
+};
+
 struct pcl_skinbuf
 {
     pcl_ctx*  ctx;
@@ -1194,6 +1201,77 @@ extern "C"
             PCL_CK(c, cudaMemcpy2D(host_nt, (size_t)s->V * 24, s->d_nt + (size_t)slot_first * s->Vp * 6, (size_t)s->Vp * 24,
                                    (size_t)s->V * 24, (size_t)count, cudaMemcpyDeviceToHost));
         }
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // render hand-off
+    // ------------------------------------------------------------------------------------------
+    int pcl_renderbuf_create(pcl_ctx* c, int64_t draws, pcl_renderbuf** out)
+    {
+        if (!c || !out || draws < 1)
+            return fail(c, PCL_ERR_INVALID, "pcl_renderbuf_create: bad argument");
+        PCL_CK(c, cudaSetDevice(c->device));
+        pcl_renderbuf* r = new pcl_renderbuf();
+        r->ctx = c, r->draws = draws;
+        const size_t bytes = (size_t)draws * RENDER_MAX_INSTANCES * RENDER_MAX_JOINTS * 64;
+        cudaError_t  e     = cudaMalloc((void**)&r->d_mats, bytes);
+        if (e != cudaSuccess)
+        {
+            delete r;
+            (void)cudaGetLastError();
+            return fail(c, PCL_ERR_OOM, std::string("pcl_renderbuf_create: ") + cudaGetErrorString(e));
+        }
+        PCL_CK(c, cudaMemsetAsync(r->d_mats, 0, bytes, c->compute));
+        *out = r;
+        return PCL_OK;
+    }
+    int pcl_renderbuf_destroy(pcl_renderbuf* r)
+    {
+        if (!r)
+            return PCL_ERR_INVALID;
+        cudaSetDevice(r->ctx->device);
+        cudaStreamSynchronize(r->ctx->compute);
+        cudaFree(r->d_mats);
+        delete r;
+        return PCL_OK;
+    }
+    int pcl_batch_export_render(pcl_batch* b, int64_t first, int64_t count, pcl_renderbuf* rb, int64_t draw_first)
+    {
+        if (!b || !rb || rb->ctx != b->ctx)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_export_render: bad handle");
+        pcl_ctx* c = b->ctx;
+        if (first < 0 || count < 1 || first + count > b->N || draw_first < 0 ||
+            draw_first + (count + RENDER_MAX_INSTANCES - 1) / RENDER_MAX_INSTANCES > rb->draws)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_export_render: range outside the batch or the render buffer");
+        if (!b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_export_render: pcl_batch_pose / pcl_batch_tick has not run");
+        const SkelRec& s = c->skels[b->skel];
+        if (s.J + 1 > RENDER_MAX_JOINTS)
+            return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_export_render: more than 1023 bones (m_mesh_vertex_blending_max_joint_count)");
+        PCL_CK(c, cudaSetDevice(c->device));
+        const long long total = count * (s.J + 1) * 4;
+        render_export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->compute>>>(b->d_palette, rb->d_mats, first, count, s.J + 1, s.pitch, draw_first);
+        c->launches++;
+        PCL_CK(c, cudaGetLastError());
+        return PCL_OK;
+    }
+    int pcl_renderbuf_dev(pcl_renderbuf* r, const void** dptr)
+    {
+        if (!r || !dptr)
+            return PCL_ERR_INVALID;
+        *dptr = r->d_mats;
+        return PCL_OK;
+    }
+    int pcl_renderbuf_download(pcl_renderbuf* r, int64_t draw, float* host)
+    {
+        if (!r || !host || draw < 0 || draw >= r->draws)
+            return fail(r ? r->ctx : nullptr, PCL_ERR_INVALID, "pcl_renderbuf_download: draw outside the buffer");
+        pcl_ctx* c = r->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        const size_t per = (size_t)RENDER_MAX_INSTANCES * RENDER_MAX_JOINTS * 64;
+        PCL_CK(c, cudaMemcpy(host, (const char*)r->d_mats + (size_t)draw * per, per, cudaMemcpyDeviceToHost));
         return PCL_OK;
     }
 

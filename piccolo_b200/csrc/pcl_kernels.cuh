@@ -631,6 +631,32 @@ namespace pcl
     }
 
     // -------------------------------------------------------------------------------------------
+    // render hand-off: compact palette -> the per-draw-call joint SSBO of the reference's mesh passes,
+    // joint_matrices[1024 * instance_in_draw + slot] (4x4 row-major, <= 64 instances per draw):
+    // function/render/passes/main_camera_pass.cpp:2284-2298, function/render/render_common.h:19-20,70-73,
+    // engine/shader/include/constants.h:3-7.  Only the J+1 live slots of an instance are written, like the
+    // reference's memcpy loop; one thread per 16-byte row.
+    // -------------------------------------------------------------------------------------------
+    constexpr int RENDER_MAX_INSTANCES = 64;   // m_mesh_per_drawcall_max_instance_count
+    constexpr int RENDER_MAX_JOINTS    = 1024; // m_mesh_vertex_blending_max_joint_count
+    __global__ void render_export_kernel(const float4* __restrict__ palette, float4* __restrict__ out, long long first, long long count,
+                                         int slots, int pitch, long long draw_first)
+    {
+        long long t     = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        long long total = count * slots * 4;
+        if (t >= total)
+            return;
+        const int       r    = (int)(t & 3);
+        const long long e    = t >> 2;
+        const long long i    = e / slots;
+        const int       slot = (int)(e - i * slots);
+        const long long draw = draw_first + i / RENDER_MAX_INSTANCES;
+        const int       in   = (int)(i % RENDER_MAX_INSTANCES);
+        const float4    v    = (r == 3) ? make_float4(0, 0, 0, 1) : palette[((size_t)(first + i) * pitch + slot) * 3 + r];
+        out[(((size_t)draw * RENDER_MAX_INSTANCES + in) * RENDER_MAX_JOINTS + slot) * 4 + r] = v;
+    }
+
+    // -------------------------------------------------------------------------------------------
     // K5: linear-blend skinning, engine/shader/glsl/mesh.vert:72-111
     // -------------------------------------------------------------------------------------------
     struct LbsParams

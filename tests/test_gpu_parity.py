@@ -394,6 +394,72 @@ def test_lbs_ring_slots_and_linearity(ctx, player_dev, player, variant):
         x.close()
 
 
+def test_lbs_full_size_config3_properties(ctx, oracle, player):
+    """BASELINE.json config 3 at full size (100 000 instances, 2-clip blend, 16 380 vertices, 25 000-slot ring): sampled
+    instances match the oracle, and an instance's skinned streams do not depend on the launch it was part of."""
+    from piccolo_b200 import capi
+    sk, cl, am, mk = player
+    run = A.make_variant_clip(cl, 17, seed=1234)
+    mesh = A.make_player_mesh(sk, V=16380, seed=42)
+    skel = ctx.upload_skeleton(sk)
+    c0, c1 = ctx.upload_clip(skel, cl, am), ctx.upload_clip(skel, run, am)
+    mh = ctx.upload_mesh(mesh, 58)
+    N, ring = 100000, 25000
+    i = np.arange(N, dtype=np.float64)
+    w = np.modf(i * 0.7548776662)[0].astype(np.float32)
+    weight = np.stack([w, np.float32(1) - w], 1)
+    phase = np.stack([np.modf(i * 0.6180339887)[0], np.modf(i * 0.6180339887 + 0.5)[0]], 1).astype(np.float32)
+    b = ctx.batch(skel, N, 2)
+    b.set(clip_ids=np.tile(np.int32([c0, c1]), (N, 1)), phase=phase, weight=weight)
+    b.pose()
+    sb = ctx.skinbuf(mh, mesh.V, ring, capi.PCL_SKIN_POS_NRM_TAN)
+    small = ctx.skinbuf(mh, mesh.V, 64, capi.PCL_SKIN_POS_NRM_TAN)
+    ctx.set_option("lbs_variant", 2)
+    orc_clips = [oracle.clip(cl, am), oracle.clip(run, am)]
+    sv = oracle.skeleton(sk)
+    for chunk in (0, 3):
+        b.skin(mh, sb, first=chunk * ring, count=ring, slot_first=0)
+        for slot in (0, 12345, ring - 1):
+            inst = chunk * ring + slot
+            pos, nt = sb.download(slot, 1)
+            ref = oracle.pose_batch(sv, orc_clips, np.int32([[0, 1]]), phase[inst:inst + 1], weight=weight[inst:inst + 1])
+            rp, rn, rt = oracle.lbs(mesh, oracle.palette_slots(ref[0]))
+            assert np.abs(pos[0] - rp).max() <= POS_TOL * max(1.0, np.abs(rp).max())
+            assert np.abs(nt[0][:, :3] - rn).max() <= 1e-4 and np.abs(nt[0][:, 3:] - rt).max() <= 1e-4
+            lo = max(0, min(inst - 7, N - 64))  # the same instance inside a different 64-instance launch, other tile lane
+            b.skin(mh, small, first=lo, count=64, slot_first=0)
+            p2, n2 = small.download(inst - lo, 1)
+            assert np.array_equal(p2, pos) and np.array_equal(n2, nt)
+    ctx.set_option("lbs_variant", -1)
+    for x in (sb, small, b):
+        x.close()
+
+
+def test_render_handoff_layout(ctx, player_dev):
+    """joint_matrices[1024 * instance_in_draw + slot], 64 instances per draw, slot 0 = identity, only J+1 slots touched
+    (main_camera_pass.cpp:2284-2298; mesh_component.cpp:72-79)."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    N = 150
+    b = ctx.batch(skel, N, 1)
+    b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=np.linspace(0, 1, N, endpoint=False, dtype=np.float32))
+    b.pose()
+    pal = b.download_palette()
+    rb = capi.RenderBuf(ctx, 4)
+    b.export_render(rb, first=0, count=N, draw_first=1)  # draws 1..3
+    eye = np.eye(4, dtype=np.float32).reshape(16)
+    assert not rb.download(0).any()
+    for d in range(3):
+        m = rb.download(1 + d)
+        n_in = min(64, N - 64 * d)
+        assert np.array_equal(m[:n_in, 1:59], pal[64 * d:64 * d + n_in])  # bit-identical to AnimationResult
+        assert np.array_equal(m[:n_in, 0], np.broadcast_to(eye, (n_in, 16)))
+        assert not m[:n_in, 59:].any() and not m[n_in:].any()
+    with pytest.raises(capi.PclError):
+        b.export_render(rb, first=0, count=N, draw_first=2)  # would need draws 2..4
+    rb.close(), b.close()
+
+
 # ------------------------------------------------------------------------------------------------
 # boundary behaviour
 # ------------------------------------------------------------------------------------------------
