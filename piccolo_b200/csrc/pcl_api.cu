@@ -1016,9 +1016,11 @@ extern "C"
         {
             const int    prow   = (s.pitch * 3) | 1; // odd number of 16-byte units per palette row
             int          warps  = c->opt_lbs_warps ? c->opt_lbs_warps : 8; // measured: 8 warps + whole-chunk flush beats 12 warps + half flush
-            if (warps == 12 && lbs_i_smem_bytes(prow, 12, true) > (size_t)c->max_smem_optin)
-                warps = 8;
-            const bool   half   = warps == 12;
+            bool         half   = false;
+            if (warps == 12 && lbs_i_smem_bytes(prow, 12, false) > (size_t)c->max_smem_optin)
+                half = true; // 12 warps only fit with the smaller normal/tangent staging rows
+            if (warps == 12 && half && lbs_i_smem_bytes(prow, 12, true) > (size_t)c->max_smem_optin)
+                warps = 8, half = false;
             const size_t smem_i = lbs_i_smem_bytes(prow, warps, half);
             const bool   fits   = m.d_vrec && smem_i <= (size_t)c->max_smem_optin;
             int          var    = c->opt_lbs_variant;
@@ -1057,9 +1059,11 @@ extern "C"
         PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<NT_, W_, H_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i)); \
         lbs_inst_kernel<NT_, W_, H_><<<grid, W_ * 32, smem_i, c->compute>>>(q);                                                    \
     }
-                if (nt && half) PCL_LAUNCH_LBSI(true, 12, true)
+                if (nt && warps == 12 && half) PCL_LAUNCH_LBSI(true, 12, true)
+                else if (nt && warps == 12) PCL_LAUNCH_LBSI(true, 12, false)
                 else if (nt) PCL_LAUNCH_LBSI(true, 8, false)
-                else if (half) PCL_LAUNCH_LBSI(false, 12, true)
+                else if (warps == 12 && half) PCL_LAUNCH_LBSI(false, 12, true)
+                else if (warps == 12) PCL_LAUNCH_LBSI(false, 12, false)
                 else PCL_LAUNCH_LBSI(false, 8, false)
 #undef PCL_LAUNCH_LBSI
                 c->launches++;

@@ -983,6 +983,17 @@ namespace pcl
         m[0] = s[0], m[1] = s[1], m[2] = s[2];
     }
 
+    // skinned streams are written once and never re-read by this engine: streaming (evict-first) stores
+#ifndef PCL_ST_MODE
+#define PCL_ST_MODE 0 /* measured: plain, .cg and .cs stores are within noise of each other */
+#endif
+#if PCL_ST_MODE == 1
+#define PCL_ST(p, v) __stcs((p), (v))
+#elif PCL_ST_MODE == 2
+#define PCL_ST(p, v) __stcg((p), (v))
+#else
+#define PCL_ST(p, v) (*(p) = (v))
+#endif
     // Flushes with coalesced 128-bit stores.  Lane -> (staging row, 16-byte unit) maps every quarter-warp
     // onto ONE row (6-unit rows: lanes 6,7 of each quarter idle; 12-unit rows: units 0-7) or onto rows r and
     // r+4 (units 8-11 of the 12-unit rows), which keeps the reads conflict-free with the odd row strides the
@@ -996,7 +1007,7 @@ namespace pcl
 #pragma unroll
             for (int it = 0; it < 8; it++)
                 if (FULL || it * 4 + a < ni)
-                    g0[off + it * rowstep] = *reinterpret_cast<const float4*>(tile + s0 + it * 4 * ROW);
+                    PCL_ST(&g0[off + it * rowstep], *reinterpret_cast<const float4*>(tile + s0 + it * 4 * ROW));
         }
     }
     template<bool FULL, int ROW>
@@ -1008,11 +1019,11 @@ namespace pcl
         for (int g = 0; g < 4; g++)
         {
             if (FULL || g * 8 + a < ni)
-                g_nt0[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + g * 8 * ROW);
+                PCL_ST(&g_nt0[chunk_nt + (2 * g) * rowstep_nt], *reinterpret_cast<const float4*>(snt + s_nt0 + g * 8 * ROW));
             if (FULL || g * 8 + 4 + a < ni)
-                g_nt0[chunk_nt + (2 * g + 1) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt0 + (g * 8 + 4) * ROW);
+                PCL_ST(&g_nt0[chunk_nt + (2 * g + 1) * rowstep_nt], *reinterpret_cast<const float4*>(snt + s_nt0 + (g * 8 + 4) * ROW));
             if (FULL || g * 8 + a + c4 < ni)
-                g_nt2[chunk_nt + (2 * g) * rowstep_nt] = *reinterpret_cast<const float4*>(snt + s_nt2 + g * 8 * ROW);
+                PCL_ST(&g_nt2[chunk_nt + (2 * g) * rowstep_nt], *reinterpret_cast<const float4*>(snt + s_nt2 + g * 8 * ROW));
         }
     }
 

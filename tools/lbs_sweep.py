@@ -14,6 +14,9 @@ ap.add_argument("--vertices", type=int, default=49998)
 ap.add_argument("--coherent", type=int, default=0, help="1: tube mesh with neighbouring vertices sharing bones; 0: SURVEY's random binding")
 ap.add_argument("--variant", type=int, default=-1)
 ap.add_argument("--steps", type=int, default=10)
+ap.add_argument("--inst-tile", type=int, default=0)
+ap.add_argument("--vsplit", type=int, default=0)
+ap.add_argument("--warps", type=int, default=0)
 args = ap.parse_args()
 peak = 6540.2
 try:
@@ -28,6 +31,9 @@ skel = ctx.upload_skeleton(sk)
 clip = ctx.upload_clip(skel, cl, am)
 mh = ctx.upload_mesh(mesh, sk.J)
 ctx.set_option("lbs_variant", args.variant)
+ctx.set_option("lbs_inst_tile", args.inst_tile)
+ctx.set_option("lbs_vsplit", args.vsplit)
+ctx.set_option("lbs_warps", args.warps)
 for flags, O in ((capi.PCL_SKIN_POS, 12), (capi.PCL_SKIN_POS_NRM_TAN, 36)):
     for N in args.n:
         b = ctx.batch(skel, N, 1)

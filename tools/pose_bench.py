@@ -12,6 +12,7 @@ ap.add_argument("--k", type=int, nargs="+", default=[1, 2])
 ap.add_argument("--clips", type=int, default=8)
 ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--wpb", type=int, default=0)
+ap.add_argument("--sorted", type=int, default=0, help="1: instances grouped by clip id (what a crowd manager would do)")
 args = ap.parse_args()
 sk, cl, am, mk = A.load_player()
 frames = (17, 23, 29, 31, 37, 41, 47)
@@ -29,7 +30,10 @@ for K in args.k:
     for N in args.n:
         rng = np.random.default_rng(7)
         b = ctx.batch(skel, N, K)
-        b.set(clip_ids=ids[rng.integers(0, len(ids), (N, K))], phase=rng.uniform(0, 1, (N, K)).astype(np.float32),
+        pick = rng.integers(0, len(ids), (N, K))
+        if args.sorted:
+            pick = pick[np.argsort(pick[:, 0], kind='stable')]
+        b.set(clip_ids=ids[pick], phase=rng.uniform(0, 1, (N, K)).astype(np.float32),
               weight=rng.uniform(0.1, 1, (N, K)).astype(np.float32))
         for _ in range(3):
             b.pose()
