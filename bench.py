@@ -126,6 +126,60 @@ def lbs_algorithmic_bytes(count, V, J, out_bytes):
     return count * (V * out_bytes + (J + 1) * 48) + V * 68
 
 
+def other_configs(ctx, capi, sk, cl, am, skel, clip0, peak):
+    """configs[1] (10 k instances, single clip, pose only), configs[3] (1 M-instance crowd, 8 mixed clips, random phases,
+    pose only; this GPU's shard when sharded) and configs[4] (256 joints x 49 998 vertices LBS stress, N = 512)."""
+    from piccolo_b200 import assets as A
+    out = {}
+
+    def time_it(fn, reps):
+        for _ in range(3):
+            fn()
+        ctx.sync()
+        ctx.timer_begin()
+        for _ in range(reps):
+            fn()
+        return ctx.timer_end() / reps
+
+    # config 2
+    n = 10000
+    b = ctx.batch(skel, n, 1)
+    b.set(clip_ids=np.full((n, 1), clip0, np.int32), phase=np.modf(np.arange(n) * 0.6180339887)[0].astype(np.float32))
+    ms = time_it(b.pose, 50)
+    out["config2_10k_pose"] = {"ms": round(ms, 4), "instances_per_s": round(n / ms * 1e3), "joints_per_s": round(n * sk.J / ms * 1e3),
+                               "GBps": round(n * (12 + 60 * 48) / ms / 1e6, 1)}
+    b.close()
+    # config 4
+    n = 1000000
+    clips = [clip0] + [ctx.upload_clip(skel, A.make_variant_clip(cl, f, seed=100 + i), am) for i, f in enumerate((17, 23, 29, 31, 37, 41, 47))]
+    rng = np.random.default_rng(7)
+    b = ctx.batch(skel, n, 1)
+    b.set(clip_ids=np.int32(clips)[rng.integers(0, 8, (n, 1))], phase=rng.uniform(0, 1, (n, 1)).astype(np.float32))
+    ms = time_it(b.pose, 10)
+    gb = n * (12 + 60 * 48) / ms / 1e6
+    out["config4_1M_mixed_clips_pose"] = {"ms": round(ms, 4), "instances_per_s": round(n / ms * 1e3), "joints_per_s": round(n * sk.J / ms * 1e3),
+                                          "GBps": round(gb, 1), "frac": round(gb / peak, 4)}
+    b.close()
+    # config 5
+    sk5 = A.make_synthetic_skeleton(256)
+    cl5, am5 = A.make_synthetic_clip(sk5, 32)
+    mesh5 = A.make_synthetic_mesh(sk5, V=49998)
+    s5 = ctx.upload_skeleton(sk5)
+    c5 = ctx.upload_clip(s5, cl5, am5)
+    m5 = ctx.upload_mesh(mesh5, 256)
+    n = 512
+    b = ctx.batch(s5, n, 1)
+    b.set(clip_ids=np.full((n, 1), c5, np.int32), phase=np.linspace(0, 1, n, endpoint=False, dtype=np.float32))
+    b.pose()
+    sb5 = ctx.skinbuf(m5, mesh5.V, n, capi.PCL_SKIN_POS_NRM_TAN)
+    ms = time_it(lambda: b.skin(m5, sb5), 10)
+    gb = (n * (mesh5.V * 36 + 257 * 48) + mesh5.V * 68) / ms / 1e6
+    out["config5_256j_50kv_lbs_N512"] = {"ms": round(ms, 4), "vertices_per_s": round(n * mesh5.V / ms * 1e3), "GBps": round(gb, 1), "frac": round(gb / peak, 4),
+                                         "note": "random 4-bone bindings (worst case for bone reuse); lane-per-vertex kernel"}
+    sb5.close(), b.close()
+    return out
+
+
 def run_ours(args):
     import torch
     from piccolo_b200 import capi
@@ -232,6 +286,13 @@ def run_ours(args):
     e2e_ms = max_over_ranks(max(e2e_ms, e2e_wall))  # host-side work counts too
     barrier()
 
+    # ---- the other BASELINE.json configs, measured briefly on rank 0's GPU (informational; parity for them is in tests/) ----
+    others = None
+    if rank == 0 and not args.no_other_configs:
+        sb.close()  # give the 14.7 GB ring back first
+        sb = None
+        others = other_configs(ctx, capi, sk, cl, am, skel, c0, peak)
+
     total = N * world
     out = {
         "metric": "animated+skinned instances/sec", "value": round(total * args.steps / (ms * 1e-3), 1), "unit": "instances/s",
@@ -251,9 +312,13 @@ def run_ours(args):
         "joints_per_s": round(total * sk.J * args.steps / (ms * 1e-3), 0),
         "skinned_vertices_per_s": round(total * mesh.V * args.steps / (ms * 1e-3), 0),
     }
+    if others:
+        out["other_configs"] = others
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(sk, cl, am, mk, mesh, budget_s=args.cpu_budget)
-    sb.close(), b.close(), ctx.close()
+    if sb is not None:
+        sb.close()
+    b.close(), ctx.close()
     grp.close()
     if rank == 0:
         print(json.dumps(out), flush=True)
@@ -348,6 +413,7 @@ def main():
     ap.add_argument("--lbs-variant", type=int, default=None)
     ap.add_argument("--lbs-warps", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=16.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

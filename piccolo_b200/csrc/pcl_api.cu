@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -80,6 +81,7 @@ struct pcl_ctx
     int32_t      cap_clips = 0;
     int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0;
     int          max_smem_optin = 0, sm_count = 0;
+    std::map<const void*, size_t> smem_attr; // largest dynamic shared memory size already enabled per kernel
 };
 
 struct pcl_batch
@@ -131,6 +133,9 @@ namespace
             return fail(ctx, e__ == cudaErrorMemoryAllocation ? PCL_ERR_OOM : PCL_ERR_CUDA,                             \
                         std::string(#call) + ": " + cudaGetErrorString(e__));                                           \
     } while (0)
+
+    // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (device, kernel, size class) instead of on every launch
+    int ensure_smem(pcl_ctx* c, const void* func, size_t bytes);
 
     template<typename T>
     int upload(pcl_ctx* c, T** dptr, const std::vector<T>& h)
@@ -205,6 +210,17 @@ namespace
     }
 
     bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size(); }
+
+    int ensure_smem(pcl_ctx* c, const void* func, size_t bytes)
+    {
+        size_t& have = c->smem_attr[func];
+        if (bytes > have)
+        {
+            PCL_CK(c, cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+            have = bytes;
+        }
+        return PCL_OK;
+    }
 } // namespace
 
 extern "C"
@@ -908,12 +924,12 @@ extern "C"
     {                                                                                                                       \
         if (simple)                                                                                                         \
         {                                                                                                                   \
-            PCL_CK(c, cudaFuncSetAttribute(pose_simple_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK>, smem); if (rc__) return rc__; } \
             pose_simple_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                \
         }                                                                                                                   \
         else                                                                                                                \
         {                                                                                                                   \
-            PCL_CK(c, cudaFuncSetAttribute(pose_kernel<KK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));       \
+            { int rc__ = ensure_smem(c, (const void*)pose_kernel<KK>, smem); if (rc__) return rc__; }       \
             pose_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                       \
         }                                                                                                                   \
     }
@@ -1056,7 +1072,7 @@ extern "C"
                 const unsigned grid = (unsigned)(tiles * vs);
 #define PCL_LAUNCH_LBSI(NT_, W_, H_)                                                                                               \
     {                                                                                                                              \
-        PCL_CK(c, cudaFuncSetAttribute(lbs_inst_kernel<NT_, W_, H_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_i)); \
+        { int rc__ = ensure_smem(c, (const void*)lbs_inst_kernel<NT_, W_, H_>, smem_i); if (rc__) return rc__; }                  \
         lbs_inst_kernel<NT_, W_, H_><<<grid, W_ * 32, smem_i, c->compute>>>(q);                                                    \
     }
                 if (nt && warps == 12 && half) PCL_LAUNCH_LBSI(true, 12, true)
@@ -1095,7 +1111,7 @@ extern "C"
         const unsigned grid = (unsigned)(tiles * vs);
 #define PCL_LAUNCH_LBS(NT_, TMA_)                                                                                          \
     {                                                                                                                      \
-        PCL_CK(c, cudaFuncSetAttribute(lbs_kernel<NT_, TMA_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+        { int rc__ = ensure_smem(c, (const void*)lbs_kernel<NT_, TMA_>, smem); if (rc__) return rc__; }                      \
         lbs_kernel<NT_, TMA_><<<grid, LBS_THREADS, smem, c->compute>>>(p);                                                 \
     }
         if (nt && lv_variant == 0) PCL_LAUNCH_LBS(true, false)
