@@ -544,14 +544,15 @@ extern "C"
             {
                 const int ch = st < J ? first[sk.order[st]] : -1;
                 for (int k = 0; k < F; k++)
+                {
+                    // {p.xyz, s.x} {q.wxyz} {s.y, s.z, -, -}; bones without a channel get the identity track
+                    float4 kp = make_float4(0, 0, 0, 0), kq = make_float4(1, 0, 0, 0), ks = make_float4(1, 1, 1, 0);
                     if (ch >= 0)
-                        for (int r = 0; r < 3; r++)
-                            skeys[((size_t)st * F + k) * 3 + r] = keys[((size_t)ch * F + k) * 3 + r];
-                    else
-                    {
-                        skeys[((size_t)st * F + k) * 3 + 1] = make_float4(1, 0, 0, 0); // rotation (w,x,y,z) = identity
-                        skeys[((size_t)st * F + k) * 3 + 2] = make_float4(1, 1, 1, 0); // scale 1, translation stays 0
-                    }
+                        kp = keys[((size_t)ch * F + k) * 3], kq = keys[((size_t)ch * F + k) * 3 + 1], ks = keys[((size_t)ch * F + k) * 3 + 2];
+                    skeys[((size_t)st * F + k) * 3 + 0] = make_float4(kp.x, kp.y, kp.z, ks.x);
+                    skeys[((size_t)st * F + k) * 3 + 1] = kq;
+                    skeys[((size_t)st * F + k) * 3 + 2] = make_float4(ks.y, ks.z, 0.f, 0.f);
+                }
                 if (ch >= 0)
                     shic[st] = hic[ch];
             }

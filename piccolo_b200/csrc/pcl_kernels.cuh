@@ -321,9 +321,15 @@ namespace pcl
     constexpr int POSE_CMAX = 320; // bones whose step records fit the constant bank (320 * 112 B = 35 KB)
     __constant__ StepRec c_steps[POSE_CMAX];
 
+    // A step-ordered key is 48 bytes: {p.x p.y p.z s.x} {q.w q.x q.y q.z} {s.y s.z - -}.  Only the first 40 are ever
+    // loaded (128 + 128 + 64 bit), so no loaded register is dead: a dead lane of a vector load gets re-used by
+    // ptxas as a scratch register at once, and the write-after-write hazard then stalls the warp for the full
+    // load latency right behind the prefetch (seen as long_scoreboard on the first FMUL after the LDGs in
+    // profiles/r1_pose_v2_*).
     struct KeyPair
     {
-        float4 p0, q0, s0, p1, q1, s1;
+        float4 a0, q0, a1, q1;
+        float2 c0, c1;
     };
     struct SimpleSlot
     {
@@ -333,9 +339,7 @@ namespace pcl
         float          r, w;
     };
     // `after` is an opaque zero derived from a value the caller has just computed.  Adding it to the address
-    // pins the loads BEHIND that computation: without it ptxas hoists the next bone's loads right in front of
-    // the current bone's first use, where they share a scoreboard slot with the loads being waited for, and
-    // the intended one-bone prefetch distance collapses to zero (seen in profiles/r1_pose_v1_*).
+    // pins the loads BEHIND that computation, i.e. behind the consumption of the keys requested one bone ago.
     __device__ __forceinline__ int opaque_zero(float v)
     {
         int z;
@@ -349,14 +353,14 @@ namespace pcl
         const float4* kl = st.keys + ((size_t)s * st.F + l) * 3;
         const float4* kh = st.keys + ((size_t)s * st.F + h) * 3;
         KeyPair       k;
-        k.p0 = __ldg(kl), k.q0 = __ldg(kl + 1), k.s0 = __ldg(kl + 2);
-        k.p1 = __ldg(kh), k.q1 = __ldg(kh + 1), k.s1 = __ldg(kh + 2);
+        k.a0 = __ldg(kl), k.q0 = __ldg(kl + 1), k.c0 = __ldg(reinterpret_cast<const float2*>(kl + 2));
+        k.a1 = __ldg(kh), k.q1 = __ldg(kh + 1), k.c1 = __ldg(reinterpret_cast<const float2*>(kh + 2));
         return k;
     }
     __device__ __forceinline__ void sample_keys(const KeyPair& k, float r, float3& P, float3& S, Quat& Q)
     {
-        P = lerp3(make_float3(k.p0.x, k.p0.y, k.p0.z), make_float3(k.p1.x, k.p1.y, k.p1.z), r);
-        S = lerp3(make_float3(k.s0.x, k.s0.y, k.s0.z), make_float3(k.s1.x, k.s1.y, k.s1.z), r);
+        P = lerp3(make_float3(k.a0.x, k.a0.y, k.a0.z), make_float3(k.a1.x, k.a1.y, k.a1.z), r);
+        S = lerp3(make_float3(k.a0.w, k.c0.x, k.c0.y), make_float3(k.a1.w, k.c1.x, k.c1.y), r);
         Q = qnlerp(r, Quat {k.q0.x, k.q0.y, k.q0.z, k.q0.w}, Quat {k.q1.x, k.q1.y, k.q1.z, k.q1.w});
     }
     __device__ __forceinline__ int pick4(const int4& v, int g) { return g == 0 ? v.x : (g == 1 ? v.y : (g == 2 ? v.z : v.w)); }
