@@ -249,23 +249,31 @@ extern "C"
         if (device < 0 || device >= n)
             return fail(nullptr, PCL_ERR_INVALID, "pcl_create: device index out of range");
         PCL_CK(nullptr, cudaSetDevice(device));
-        pcl_ctx* c = new pcl_ctx();
-        c->device  = device;
         cudaDeviceProp prop;
         PCL_CK(nullptr, cudaGetDeviceProperties(&prop, device));
+        if (prop.major < 10)
+            return fail(nullptr, PCL_ERR_UNSUPPORTED, "pcl_create: kernels are built for sm_100a (Blackwell) only");
+        pcl_ctx* c        = new pcl_ctx();
+        c->device         = device;
         c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
         c->sm_count       = prop.multiProcessorCount;
-        if (prop.major < 10)
+        cudaError_t e     = cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_pose, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreate(&c->t0);
+        if (e == cudaSuccess) e = cudaEventCreate(&c->t1);
+        if (e != cudaSuccess)
         {
+            if (c->t1) cudaEventDestroy(c->t1);
+            if (c->t0) cudaEventDestroy(c->t0);
+            if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+            if (c->ev_pose) cudaEventDestroy(c->ev_pose);
+            if (c->copy) cudaStreamDestroy(c->copy);
+            if (c->compute) cudaStreamDestroy(c->compute);
             delete c;
-            return fail(nullptr, PCL_ERR_UNSUPPORTED, "pcl_create: kernels are built for sm_100a (Blackwell) only");
+            return fail(nullptr, PCL_ERR_CUDA, std::string("pcl_create: ") + cudaGetErrorString(e));
         }
-        PCL_CK(nullptr, cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking));
-        PCL_CK(nullptr, cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
-        PCL_CK(nullptr, cudaEventCreateWithFlags(&c->ev_pose, cudaEventDisableTiming));
-        PCL_CK(nullptr, cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
-        PCL_CK(nullptr, cudaEventCreate(&c->t0));
-        PCL_CK(nullptr, cudaEventCreate(&c->t1));
         *out = c;
         return PCL_OK;
     }
