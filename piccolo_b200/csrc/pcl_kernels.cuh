@@ -980,6 +980,14 @@ namespace pcl
         return d;
     }
 
+    // one MUFU.RSQ, no denormal rescue sequence (a squared normal below 1e-38 has no direction worth keeping)
+    __device__ __forceinline__ float rsqrt_ftz(float x)
+    {
+        float r;
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+        return r;
+    }
+
     // one bone matrix (3 rows) from this lane's palette row; off3 = slot * 3 (16-byte units)
     __device__ __forceinline__ void lbs_i_load(float4 (&m)[3], const float4* prow, uint32_t off3)
     {
@@ -1178,8 +1186,8 @@ namespace pcl
                                     nz = B[2].x * b.x + B[2].y * b.y + B[2].z * b.z;
                         const float tx = B[0].x * t.x + B[0].y * t.y + B[0].z * t.z, ty = B[1].x * t.x + B[1].y * t.y + B[1].z * t.z,
                                     tz = B[2].x * t.x + B[2].y * t.y + B[2].z * t.z;
-                        const float rn = rsqrtf(nx * nx + ny * ny + nz * nz);
-                        const float rt = rsqrtf(tx * tx + ty * ty + tz * tz);
+                        const float rn = rsqrt_ftz(nx * nx + ny * ny + nz * nz);
+                        const float rt = rsqrt_ftz(tx * tx + ty * ty + tz * tz);
                         onf[j * 6 + 0] = nx * rn, onf[j * 6 + 1] = ny * rn, onf[j * 6 + 2] = nz * rn;
                         onf[j * 6 + 3] = tx * rt, onf[j * 6 + 4] = ty * rt, onf[j * 6 + 5] = tz * rt;
                     }
