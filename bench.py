@@ -392,7 +392,22 @@ def cpu_reference_rate(sk, cl, am, mk, mesh, budget_s, threads):
 def cpu_baseline(sk, cl, am, mk, mesh, budget_s=16.0):
     threads = os.cpu_count() or 1
     rate, kind, sample = cpu_reference_rate(sk, cl, am, mk, mesh, budget_s, threads)
-    return {"value": round(rate, 2), "unit": "instances/s", "cores": threads, "kind": kind, "sample": sample}
+    out = {"value": round(rate, 2), "unit": "instances/s", "cores": threads, "kind": kind, "sample": sample}
+    try:  # single-core figures of the reference's own code, 10 000 iterations after warm-up
+        from oracle import pyoracle as O
+        if O.RefLib.available():
+            with tempfile.TemporaryDirectory() as td:
+                ref, h = _ref_session(sk, cl, am, mk, td)
+                ref.bench_pose(h, 1, 1000, True)
+                out["single_core_us_per_instance"] = {"pose_only": round(1e6 / ref.bench_pose(h, 1, 10000, False), 2),
+                                                      "full_tick": round(1e6 / ref.bench_pose(h, 1, 10000, True), 2)}
+    except Exception:
+        pass
+    try:
+        out["host_cpu"] = [l.split(":", 1)[1].strip() for l in open("/proc/cpuinfo") if l.startswith("model name")][0]
+    except Exception:
+        pass
+    return out
 
 
 def run_reference(args):

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -64,6 +65,7 @@ struct ConstOwner
     int      skel = -1;
 };
 static ConstOwner g_const_owner[PCL_STATIC_MAX_DEVICES];
+static std::mutex g_const_mu; // contexts on one device may be driven from different threads; the bank is shared
 
 struct pcl_ctx
 {
@@ -284,8 +286,11 @@ extern "C"
             return PCL_ERR_INVALID;
         cudaSetDevice(c->device);
         cudaDeviceSynchronize();
-        if (c->device < PCL_STATIC_MAX_DEVICES && g_const_owner[c->device].ctx == c)
-            g_const_owner[c->device] = ConstOwner();
+        {
+            std::lock_guard<std::mutex> lk(g_const_mu);
+            if (c->device < PCL_STATIC_MAX_DEVICES && g_const_owner[c->device].ctx == c)
+                g_const_owner[c->device] = ConstOwner();
+        }
         for (auto& s : c->skels)
             cudaFree(s.d_steps), cudaFree(s.d_masks);
         for (auto& cl : c->clips)
@@ -918,8 +923,11 @@ extern "C"
             wpb = std::min(wpb, POSE_S_THREADS / 32);
         const size_t   smem = per_warp * wpb;
         const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
+        // the bank's contents must stay put from the upload until this launch is enqueued
+        std::unique_lock<std::mutex> bank_lock(g_const_mu, std::defer_lock);
         if (simple)
         {
+            bank_lock.lock();
             ConstOwner& own = g_const_owner[c->device];
             if (own.ctx != c || own.skel != b->skel)
             {
