@@ -204,6 +204,16 @@ class RefLib:
         self.lib.ref_tick(h, n_ticks, C.c_float(dt), _f(ph), _f(mats), _f(phases))
         return mats, phases
 
+    def blend_weights(self, skeleton_url, clip_url, map_url, mask0_url, mask1_url, w0, w1, J):
+        out = np.zeros((2, J), np.float32)
+        self.lib.ref_blend_weights.argtypes = [C.c_char_p] * 5 + [C.c_float, C.c_float, _fp]
+        self.lib.ref_set_asset_root(self.root.encode())
+        n = self.lib.ref_blend_weights(skeleton_url.encode(), clip_url.encode(), map_url.encode(), mask0_url.encode(), mask1_url.encode(),
+                                       C.c_float(w0), C.c_float(w1), _f(out))
+        if n != J:
+            raise RuntimeError("ref_blend_weights failed")
+        return out
+
     def bench_pose(self, h, n_threads, per_thread, full_tick=True):
         return float(self.lib.ref_bench_pose(h, n_threads, per_thread, int(full_tick), None))
 

@@ -189,6 +189,29 @@ extern "C"
         return (double)n_threads * per_thread / worst;
     }
 
+    // The per-bone normalised blend weights AnimationManager::getBlendStateWithClipData computes every tick
+    // (animation_system.cpp:117-149) for a two-clip blend state with two different masks.  out: [2][J].
+    int ref_blend_weights(const char* skeleton_url, const char* clip_url, const char* map_url, const char* mask0_url,
+                          const char* mask1_url, float w0, float w1, float* out)
+    {
+        BlendState bs;
+        bs.clip_count               = 2;
+        bs.blend_clip_file_path     = {clip_url, clip_url};
+        bs.blend_clip_file_length   = {1.f, 1.f};
+        bs.blend_anim_skel_map_path = {map_url, map_url};
+        bs.blend_weight             = {w0, w1};
+        bs.blend_mask_file_path     = {mask0_url, mask1_url};
+        bs.blend_ratio              = {0.f, 0.f};
+        auto skel = AnimationManager::tryLoadSkeleton(skeleton_url); // the masks name it by this very url
+        BlendStateWithClipData r = AnimationManager::getBlendStateWithClipData(bs);
+        size_t J = skel->bones_map.size();
+        if (r.blend_weight.size() != 2 || r.blend_weight[0].blend_weight.size() != J)
+            return -1;
+        for (int c = 0; c < 2; c++)
+            std::memcpy(out + c * J, r.blend_weight[c].blend_weight.data(), J * sizeof(float));
+        return (int)J;
+    }
+
     // ---- skinning: mesh.vert:72-111 with the reference's CPU matrix operators -----------------
     // palette16: n_slots row-major 4x4 (slot 0 = identity, slot b+1 = bone b; mesh_component.cpp:72-79).
     // w4_raw is renormalised exactly like render_resource.cpp:714-725 before use.

@@ -84,6 +84,30 @@ static int cmd_load(int argc, char** argv)
     return 0;
 }
 
+// AnimationManager::getBlendStateWithClipData of a two-clip, two-mask blend state: the per-bone weights
+static int cmd_weights(int argc, char** argv)
+{
+    if (argc < 11)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    BlendState bs;
+    bs.clip_count               = 2;
+    bs.blend_clip_file_path     = {argv[4], argv[4]};
+    bs.blend_clip_file_length   = {1.f, 1.f};
+    bs.blend_anim_skel_map_path = {argv[5], argv[5]};
+    bs.blend_weight             = {(float)std::atof(argv[8]), (float)std::atof(argv[9])};
+    bs.blend_mask_file_path     = {argv[6], argv[7]};
+    bs.blend_ratio              = {0.f, 0.f};
+    AnimationManager::tryLoadSkeleton(argv[3]);
+    BlendStateWithClipData r = AnimationManager::getBlendStateWithClipData(bs);
+    g_out                    = fopen(argv[10], "wb");
+    for (auto& w : r.blend_weight)
+        putf(1, w.blend_weight);
+    puti(2, {(int32_t)r.blend_clip.size(), (int32_t)r.blend_anim_skel_map.size(), r.clip_count, (int32_t)r.blend_clip[0].node_channels.size()});
+    fclose(g_out);
+    return 0;
+}
+
 // AnimationComponent as GObject::load + n x GObject::tick would drive it
 static int cmd_tick(int argc, char** argv)
 {
@@ -190,6 +214,8 @@ int main(int argc, char** argv)
         return 2;
     if (!std::strcmp(argv[1], "load"))
         return cmd_load(argc, argv);
+    if (!std::strcmp(argv[1], "weights"))
+        return cmd_weights(argc, argv);
     if (!std::strcmp(argv[1], "tick"))
         return cmd_tick(argc, argv);
     if (!std::strcmp(argv[1], "batch"))

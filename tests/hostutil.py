@@ -30,7 +30,10 @@ def read_dump(path):
         o += 8
         is_int = bool(tag & 0x40000000)
         tag = int(tag & 0x3FFFFFFF)
-        out["%d%s" % (tag, "i" if is_int else "")] = np.frombuffer(raw, np.int32 if is_int else np.float32, int(n), o).copy()
+        key = "%d%s" % (tag, "i" if is_int else "")
+        while key in out:  # a tag written several times: "1", "1'", "1''", ...
+            key += "'"
+        out[key] = np.frombuffer(raw, np.int32 if is_int else np.float32, int(n), o).copy()
         o += 4 * int(n)
     return out
 

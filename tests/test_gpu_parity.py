@@ -435,6 +435,35 @@ def test_lbs_full_size_config3_properties(ctx, oracle, player):
         x.close()
 
 
+def test_async_palette_download_overlapping_skin_and_next_pose(ctx, player_dev, player):
+    """The end-to-end path of bench.py: palette download on the copy stream into pinned memory while the compute stream
+    skins, then the next pose must wait for the export to have read the palette."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    mesh = A.make_player_mesh(player[0], V=4096, seed=2)
+    mh = ctx.upload_mesh(mesh, 58)
+    N = 5000
+    b = ctx.batch(skel, N, 1)
+    sb = ctx.skinbuf(mh, mesh.V, N, capi.PCL_SKIN_POS)
+    pinned = ctx.pinned((N, 58, 16), np.float32)
+    ph = np.random.default_rng(9).uniform(0, 1, (3, N)).astype(np.float32)
+    want = []
+    for r in range(3):  # reference results, fully synchronous
+        b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph[r])
+        b.pose()
+        want.append(b.download_palette())
+    for r in range(3):
+        b.set(phase=ph[r])
+        b.pose()
+        b.download_palette(out=pinned, asynchronous=True)
+        b.skin(mh, sb)
+        b.set(phase=ph[(r + 1) % 3])  # next frame's inputs and pose are enqueued before the download has been waited for
+        b.pose()
+        ctx.sync()
+        assert np.array_equal(pinned, want[r]), "async download saw the next frame's palette (round %d)" % r
+    sb.close(), b.close()
+
+
 def test_render_handoff_layout(ctx, player_dev):
     """joint_matrices[1024 * instance_in_draw + slot], 64 instances per draw, slot 0 = identity, only J+1 slots touched
     (main_camera_pass.cpp:2284-2298; mesh_component.cpp:72-79)."""

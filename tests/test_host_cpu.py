@@ -58,3 +58,28 @@ def test_component_is_inert_without_a_gpu(player, tmp_path):
     assert "bones=0" in r.stdout and "ctx=none" in r.stdout and "no CPU path" in r.stderr
     d = H.read_dump(out)
     assert d["100"].size == 0 and len(d["1"]) == 3  # phases still advance, results stay empty (like m_bones == nullptr)
+
+
+def test_blend_weights_match_reference_and_oracle(player, oracle, tmp_path):
+    """A2: AnimationManager::getBlendStateWithClipData's per-bone normalised weights (animation_system.cpp:117-149) -
+    host mirror == oracle, and == the reference's own code when oracle/_ref can run here."""
+    sk, cl, am, mk = player
+    urls = H.write_player_tree(str(tmp_path), player)
+    rng = np.random.default_rng(4)
+    m0, m1 = (rng.uniform(size=sk.J) < 0.7).astype(np.int32), (rng.uniform(size=sk.J) < 0.5).astype(np.int32)
+    m0[:3], m1[:3] = [1, 0, 1], [1, 1, 0]
+    for name, m in (("m0", m0), ("m1", m1)):
+        A.write_json(A.mask_to_json(A.BoneBlendMask(urls["skeleton"], m)), os.path.join(str(tmp_path), H.DATA + name + ".json"))
+    w = (np.float32(0.3), np.float32(0.9))
+    out = tmp_path / "w.bin"
+    r = H.run(["weights", tmp_path, urls["skeleton"], urls["clip"], urls["map"], H.DATA + "m0.json", H.DATA + "m1.json", w[0], w[1], out])
+    assert r.returncode == 0, r.stderr
+    d = H.read_dump(out)
+    got = np.stack([d["1"], d["1'"]])
+    want = oracle.blend_weights(np.float32(w), np.stack([m0, m1]))
+    both_off = (m0 == 0) & (m1 == 0)  # the reference divides 0/0 there only on paper: disabled slots are written as 0
+    assert np.array_equal(got, want) and not got[:, both_off].any()
+    assert d["2i"].tolist() == [2, 2, 2, cl.C]  # clips and maps are handed over by value, like the reference
+    if O.RefLib.available() and os.path.isdir(O.REFERENCE_ROOT):
+        ref = O.RefLib(str(tmp_path)).blend_weights(urls["skeleton"], urls["clip"], urls["map"], H.DATA + "m0.json", H.DATA + "m1.json", w[0], w[1], sk.J)
+        assert np.array_equal(ref, want)
