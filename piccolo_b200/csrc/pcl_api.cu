@@ -47,7 +47,8 @@ namespace
         float * d_pos = nullptr, *d_nrm = nullptr, *d_tan = nullptr;
         int4*   d_idx = nullptr;
         float4* d_w   = nullptr;
-        VRec*   d_vrec = nullptr; // lane = instance form: slot-stable influences, see lbs_inst_kernel
+        VRec*   d_vrec = nullptr;     // lane = instance form: slot-stable influences, see lbs_inst_kernel
+        VRec*   d_vrec_cta = nullptr; // the same packed along lbs_cta_kernel's visiting order
     };
 } // namespace
 
@@ -115,6 +116,8 @@ struct pcl_skinbuf
     long long capacity;
     int32_t   flags, V, Vp;
     float *   d_pos = nullptr, *d_nt = nullptr;
+    bool        has_tmaps = false; // tensor maps of the two streams for lbs_cta_kernel's TMA stores
+    CUtensorMap tm_pos, tm_nt;
 };
 
 namespace
@@ -213,6 +216,35 @@ namespace
 
     bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size(); }
 
+    // 2-D tensor map over a skinned stream [capacity][row_floats], box = 32 rows x 32 floats (128 B), 128-byte swizzle.
+    // The encoder lives in the driver; it is fetched through the runtime so that the library has no link-time
+    // dependency on libcuda (it must load on machines without a GPU).
+    bool make_stream_tmap(CUtensorMap* tm, float* base, long long capacity, long long row_floats)
+    {
+        typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                      const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        static encode_fn encode = nullptr;
+        if (!encode)
+        {
+            void*                           fn = nullptr;
+            cudaDriverEntryPointQueryResult qr;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn)
+            {
+                (void)cudaGetLastError();
+                return false;
+            }
+            encode = (encode_fn)fn;
+        }
+        if (row_floats >= (1LL << 32) || capacity >= (1LL << 32))
+            return false;
+        const cuuint64_t dims[2]    = {(cuuint64_t)row_floats, (cuuint64_t)capacity};
+        const cuuint64_t strides[1] = {(cuuint64_t)row_floats * 4};
+        const cuuint32_t box[2]     = {32, 32};
+        const cuuint32_t estr[2]    = {1, 1};
+        return encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                      CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    }
+
     int ensure_smem(pcl_ctx* c, const void* func, size_t bytes)
     {
         size_t& have = c->smem_attr[func];
@@ -296,7 +328,7 @@ extern "C"
         for (auto& cl : c->clips)
             cudaFree(cl.d_blob);
         for (auto& m : c->meshes)
-            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec);
+            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec), cudaFree(m.d_vrec_cta);
         cudaFree(c->d_clips);
         cudaEventDestroy(c->ev_pose), cudaEventDestroy(c->ev_copy), cudaEventDestroy(c->t0), cudaEventDestroy(c->t1);
         cudaStreamDestroy(c->compute), cudaStreamDestroy(c->copy);
@@ -364,7 +396,7 @@ extern "C"
             c->opt_pose_wpb = v;
         else if (k == "pose_generic" && (v == 0 || v == 1))
             c->opt_pose_generic = v;
-        else if (k == "lbs_variant" && v >= -1 && v <= 2)
+        else if (k == "lbs_variant" && v >= -1 && v <= 3)
             c->opt_lbs_variant = v;
         else if (k == "lbs_warps" && (v == 0 || v == 8 || v == 12))
             c->opt_lbs_warps = v;
@@ -686,62 +718,78 @@ extern "C"
             hi[v] = make_int4(id[0], id[1], id[2], id[3]);
             hw[v] = make_float4(w[0], w[1], w[2], w[3]);
         }
-        // lane = instance form.  Each vertex's (gated) influences are packed into four register slots so that
-        // a bone that was already resident for the previous vertex keeps its slot; unused slots keep the
+        // lane = instance forms.  Each vertex's (gated) influences are packed into four register slots so that
+        // a bone that was already resident for the previously VISITED vertex keeps its slot; unused slots keep the
         // resident bone with weight 0 (an exact zero contribution).  The blend is then summed in slot order,
         // which differs from the shader's x,y,z,w order only by a permutation of the same four products.
+        //   hv  : visiting order 0,1,2,...                       (lbs_inst_kernel: a warp walks a contiguous run)
+        //   hvc : eight interleaved visiting orders, sequence w = vertices 32 s + 4 w + {0..3}, s = 0,1,...
+        //         (lbs_cta_kernel: warp w owns that slice of every superchunk)
+        const size_t      n_sc = ((size_t)m.Vp + LBS_C_SC - 1) / LBS_C_SC;
         std::vector<VRec> hv((size_t)m.Vt + LBS_I_SCH * LBS_I_CHUNK); // tail padding: a record stage may overrun the last chunk
+        std::vector<VRec> hvc((n_sc + LBS_C_RSC) * LBS_C_SC);
         std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
+        std::memset(hvc.data(), 0, hvc.size() * sizeof(VRec));
         if (max_slot * 3 <= 0xffff)
         {
-            int cur[4] = {0, 0, 0, 0};
-            for (int v = 0; v < V; v++)
-            {
-                const int   src_i[4] = {hi[v].x, hi[v].y, hi[v].z, hi[v].w};
-                const float src_w[4] = {hw[v].x, hw[v].y, hw[v].z, hw[v].w};
-                int         slot_i[4];
-                float       slot_w[4] = {0.f, 0.f, 0.f, 0.f};
-                bool        taken[4] = {false, false, false, false}, placed[4] = {false, false, false, false};
-                for (int k = 0; k < 4; k++) // keep resident bones where they are
-                    if (src_w[k] != 0.f)
-                        for (int sl = 0; sl < 4; sl++)
-                            if (!taken[sl] && cur[sl] == src_i[k])
-                            {
-                                taken[sl] = true, placed[k] = true, slot_w[sl] = src_w[k];
-                                break;
-                            }
-                for (int k = 0; k < 4; k++) // newcomers go to the free slots
-                    if (src_w[k] != 0.f && !placed[k])
-                        for (int sl = 0; sl < 4; sl++)
-                            if (!taken[sl])
-                            {
-                                taken[sl] = true, cur[sl] = src_i[k], slot_w[sl] = src_w[k];
-                                break;
-                            }
-                uint32_t mask = 0;
-                for (int sl = 0; sl < 4; sl++)
+            auto slot_of = [](const VRec& r, int sl) { return ((sl < 2 ? (r.i01 >> (16 * sl)) : (r.i23 >> (16 * (sl - 2)))) & 0xffffu); };
+            // pack vertex v (or padding when v >= V) given the resident bones `cur` and the previously visited record
+            auto pack = [&](VRec& r, size_t v, int cur[4], const VRec* prev) {
+                float slot_w[4] = {0.f, 0.f, 0.f, 0.f};
+                if (v < (size_t)V)
                 {
-                    slot_i[sl] = cur[sl];
-                    if (v == 0 || (uint32_t)slot_i[sl] * 3u != ((sl < 2 ? (hv[v - 1].i01 >> (16 * sl)) : (hv[v - 1].i23 >> (16 * (sl - 2)))) & 0xffffu))
-                        mask |= 1u << sl;
+                    const int   src_i[4] = {hi[v].x, hi[v].y, hi[v].z, hi[v].w};
+                    const float src_w[4] = {hw[v].x, hw[v].y, hw[v].z, hw[v].w};
+                    bool        taken[4] = {false, false, false, false}, placed[4] = {false, false, false, false};
+                    for (int k = 0; k < 4; k++) // keep resident bones where they are
+                        if (src_w[k] != 0.f)
+                            for (int sl = 0; sl < 4; sl++)
+                                if (!taken[sl] && cur[sl] == src_i[k])
+                                {
+                                    taken[sl] = true, placed[k] = true, slot_w[sl] = src_w[k];
+                                    break;
+                                }
+                    for (int k = 0; k < 4; k++) // newcomers go to the free slots
+                        if (src_w[k] != 0.f && !placed[k])
+                            for (int sl = 0; sl < 4; sl++)
+                                if (!taken[sl])
+                                {
+                                    taken[sl] = true, cur[sl] = src_i[k], slot_w[sl] = src_w[k];
+                                    break;
+                                }
+                    r.px = hp[3 * v], r.py = hp[3 * v + 1], r.pz = hp[3 * v + 2];
+                    r.nx = hn[3 * v], r.ny = hn[3 * v + 1], r.nz = hn[3 * v + 2];
+                    r.tx = ht[3 * v], r.ty = ht[3 * v + 1], r.tz = ht[3 * v + 2];
                 }
-                VRec& r = hv[v];
-                r.px = hp[3 * (size_t)v], r.py = hp[3 * (size_t)v + 1], r.pz = hp[3 * (size_t)v + 2], r.w0 = slot_w[0];
-                r.nx = hn[3 * (size_t)v], r.ny = hn[3 * (size_t)v + 1], r.nz = hn[3 * (size_t)v + 2], r.w1 = slot_w[1];
-                r.tx = ht[3 * (size_t)v], r.ty = ht[3 * (size_t)v + 1], r.tz = ht[3 * (size_t)v + 2], r.w2 = slot_w[2];
-                r.w3   = slot_w[3];
-                r.i01  = (uint32_t)slot_i[0] * 3u | (((uint32_t)slot_i[1] * 3u) << 16);
-                r.i23  = (uint32_t)slot_i[2] * 3u | (((uint32_t)slot_i[3] * 3u) << 16);
-                r.mask = mask;
+                r.w0 = slot_w[0], r.w1 = slot_w[1], r.w2 = slot_w[2], r.w3 = slot_w[3];
+                r.i01  = (uint32_t)cur[0] * 3u | (((uint32_t)cur[1] * 3u) << 16);
+                r.i23  = (uint32_t)cur[2] * 3u | (((uint32_t)cur[3] * 3u) << 16);
+                r.mask = 0;
+                for (int sl = 0; sl < 4; sl++)
+                    if (!prev || slot_of(r, sl) != slot_of(*prev, sl))
+                        r.mask |= 1u << sl;
+            };
+            int cur[4] = {0, 0, 0, 0};
+            for (size_t v = 0; v < hv.size(); v++)
+                pack(hv[v], v, cur, v ? &hv[v - 1] : nullptr);
+            for (int w = 0; w < LBS_C_WARPS; w++)
+            {
+                int         cw[4] = {0, 0, 0, 0};
+                const VRec* prev  = nullptr;
+                for (size_t sc = 0; sc < n_sc + LBS_C_RSC; sc++)
+                    for (int j = 0; j < LBS_C_VPW; j++)
+                    {
+                        const size_t v = sc * LBS_C_SC + (size_t)w * LBS_C_VPW + j;
+                        pack(hvc[v], v, cw, prev);
+                        prev = &hvc[v];
+                    }
             }
-            for (size_t v = V; v < hv.size(); v++) // padding keeps the last real vertex's slots resident
-                hv[v].i01 = hv[V - 1].i01, hv[v].i23 = hv[V - 1].i23;
         }
         int rc;
         if ((rc = upload(c, &m.d_pos, hp)) || (rc = upload(c, &m.d_nrm, hn)) || (rc = upload(c, &m.d_tan, ht)) ||
             (rc = upload(c, &m.d_idx, hi)) || (rc = upload(c, &m.d_w, hw)))
             return rc;
-        if (max_slot * 3 <= 0xffff && (rc = upload(c, &m.d_vrec, hv)))
+        if (max_slot * 3 <= 0xffff && ((rc = upload(c, &m.d_vrec, hv)) || (rc = upload(c, &m.d_vrec_cta, hvc))))
             return rc;
         c->meshes.push_back(m);
         *out = (pcl_mesh)c->meshes.size() - 1;
@@ -1013,6 +1061,10 @@ extern "C"
             (void)cudaGetLastError();
             return fail(c, PCL_ERR_OOM, std::string("pcl_skinbuf_create: ") + cudaGetErrorString(e));
         }
+        s->has_tmaps = make_stream_tmap(&s->tm_pos, s->d_pos, capacity, (long long)s->Vp * 3) &&
+                       (!s->d_nt || make_stream_tmap(&s->tm_nt, s->d_nt, capacity, (long long)s->Vp * 6));
+        if (!s->d_nt)
+            s->tm_nt = s->tm_pos;
         *out = s;
         return PCL_OK;
     }
@@ -1060,7 +1112,55 @@ extern "C"
             if (var == 2 && !fits)
                 return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 2 needs 32 palettes in shared memory");
             if (var < 0)
-                var = (fits && count >= 24) ? 2 : 0;
+            {
+                const bool fits3 = m.d_vrec_cta && out->has_tmaps && lbs_c_smem_bytes(prow, nt) <= (size_t)c->max_smem_optin;
+                var = (fits3 && count >= 32) ? 3 : ((fits && count >= 24) ? 2 : 0);
+            }
+            if (var == 3)
+            {
+                const size_t smem_c = lbs_c_smem_bytes(prow, nt);
+                if (!m.d_vrec_cta || !out->has_tmaps || smem_c > (size_t)c->max_smem_optin)
+                    return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 3 needs 32 palettes in shared memory and tensor maps");
+                const long long full = count / 32; // whole 32-instance tiles; a ragged remainder goes to lbs_inst_kernel below
+                if (full > 0)
+                {
+                    LbsCParams q {};
+                    q.vrec = m.d_vrec_cta, q.palette = b->d_palette;
+                    q.first = first, q.slot_first = slot_first, q.n_tiles = (int32_t)full;
+                    q.Vp = m.Vp, q.n_sc = (m.Vp + LBS_C_SC - 1) / LBS_C_SC, q.pitch = s.pitch, q.prow = prow;
+                    int vs = c->opt_lbs_vsplit;
+                    if (vs == 0)
+                    {
+                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_sc / 32));
+                        double    best   = -1.0;
+                        for (int cand = 1; cand <= max_vs; cand++)
+                        {
+                            const double waves = (double)(full * cand) / c->sm_count;
+                            const double eff   = waves / std::ceil(waves);
+                            if (eff > best + 0.02)
+                                best = eff, vs = cand;
+                        }
+                    }
+                    q.vsplit = std::max(1, std::min(vs, q.n_sc));
+                    const unsigned grid = (unsigned)(full * q.vsplit);
+                    if (nt)
+                    {
+                        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<true>, smem_c); if (rc__) return rc__; }
+                        lbs_cta_kernel<true><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos, out->tm_nt);
+                    }
+                    else
+                    {
+                        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<false>, smem_c); if (rc__) return rc__; }
+                        lbs_cta_kernel<false><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos, out->tm_nt);
+                    }
+                    c->launches++;
+                    PCL_CK(c, cudaGetLastError());
+                }
+                if (count == full * 32)
+                    return PCL_OK;
+                first += full * 32, slot_first += full * 32, count -= full * 32;
+                var = 2;
+            }
             if (var == 2)
             {
                 LbsIParams q {};

@@ -7,6 +7,8 @@
 #pragma once
 #include "pcl_math.cuh"
 
+#include <cuda.h> // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include <cstdint>
 
 namespace pcl
@@ -1234,6 +1236,245 @@ namespace pcl
                     lbs_i_flush12<false, LBS_I_NTROW>(snt, s_nt0, s_nt2, g_nt0, g_nt2, rowstep_nt, chunk_nt, lane, ni);
             }
             __syncwarp();
+        }
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // K5, crowd form with a TMA store pipeline (warp-specialised).
+    //
+    // lbs_inst_kernel moves every result through shared memory twice with LSU instructions (column stores,
+    // row loads, global stores: ~29 of its ~40 shared/global wavefronts per warp-vertex) and ends up bound by
+    // the L1/TEX pipe.  Here the read-back half is handed to the TMA engine: the CTA's 8 compute warps work on
+    // the SAME 32 instances and on the same 32-vertex "superchunk" (warp w owns vertices 4w..4w+3 of it) and
+    // write their results into one CTA-wide staging tile; a ninth warp then issues NINE tensor-map bulk stores
+    // per superchunk (cp.async.bulk.tensor.2d, SASS UTMASTG: boxes of 32 instances x 128 bytes; 3 for the
+    // positions, 6 for normal+tangent).  The tile uses the TMA 128-byte swizzle, which is exactly what makes the
+    // lane = instance 128-bit column stores bank-conflict free (16-byte unit u of row r lives at unit u ^ (r & 7)).
+    // (1-D bulk stores of the per-instance runs were tried first: 64 per superchunk, 2.0 TB/s - the non-tensor
+    // bulk path moves only ~14 GB/s per SM.)  Two tiles and named barriers (full/empty) decouple the two sides;
+    // the store warp also refills the CTA-wide vertex-record ring (TMA bulk loads, complete_tx on mbarriers).
+    // Bone matrices stay in registers exactly as in lbs_inst_kernel; because a warp now visits vertices
+    // 4w..4w+3 of every superchunk, the upload packs the influence slots along that visiting order (`vrec_cta`).
+    // Whole 32-instance tiles only (the boxes are not clipped in the instance dimension by `count`): the
+    // launcher hands a ragged remainder to lbs_inst_kernel.
+    // -------------------------------------------------------------------------------------------
+    constexpr int LBS_C_WARPS   = 8;                       // compute warps
+    constexpr int LBS_C_THREADS = (LBS_C_WARPS + 1) * 32;  // + 1 store / load warp
+    constexpr int LBS_C_SC      = 32;                      // vertices per superchunk
+    constexpr int LBS_C_VPW     = LBS_C_SC / LBS_C_WARPS;  // 4 vertices per warp per superchunk
+    constexpr int LBS_C_RSC     = 4;                       // superchunks per vertex-record stage
+    constexpr int LBS_C_RSTAGES = 3;
+    constexpr int LBS_C_SUB     = 32 * 128;                // one swizzled sub-tile: 32 instances x 128 bytes
+    constexpr int LBS_C_POS_SUBS = 3, LBS_C_NT_SUBS = 6;   // 384 B and 768 B per instance and superchunk
+
+    __host__ __device__ inline size_t lbs_c_tile_bytes(bool nt) { return (size_t)(LBS_C_POS_SUBS + (nt ? LBS_C_NT_SUBS : 0)) * LBS_C_SUB; }
+    __host__ __device__ inline size_t lbs_c_smem_bytes(int prow, bool nt)
+    {
+        return 2 * lbs_c_tile_bytes(nt)                                                // two staging tiles (1024-byte aligned, first)
+               + (size_t)32 * prow * 16                                                // palettes
+               + (size_t)LBS_C_RSTAGES * LBS_C_RSC * LBS_C_SC * sizeof(VRec)           // vertex-record ring
+               + 8 * (1 + LBS_C_RSTAGES) + 64;                                         // mbarriers
+    }
+
+    __device__ __forceinline__ void named_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+    __device__ __forceinline__ void named_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+    // 2-D tensor-map store shared -> global (SASS UTMASTG); c0 = innermost coordinate (floats), c1 = instance slot
+    __device__ __forceinline__ void tma_store_2d(const void* tmap, int c0, int c1, const void* src)
+    {
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(src))
+                     : "memory");
+    }
+
+    struct LbsCParams
+    {
+        const VRec*   vrec;    // packed along the warp visiting order, padded to whole record stages
+        const float4* palette; // [N][pitch][3]
+        long long     first, slot_first;
+        int32_t       n_tiles, Vp, n_sc, pitch, prow, vsplit;
+    };
+
+    template<bool NT>
+    __global__ void __launch_bounds__(LBS_C_THREADS, 1)
+        lbs_cta_kernel(const LbsCParams par, const __grid_constant__ CUtensorMap tm_pos, const __grid_constant__ CUtensorMap tm_nt)
+    {
+        extern __shared__ __align__(1024) unsigned char lsm[];
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        const int tile  = blockIdx.x / par.vsplit;
+        const int split = blockIdx.x - tile * par.vsplit;
+        const long long i0 = (long long)tile * 32;
+
+        const size_t   TILE  = lbs_c_tile_bytes(NT);
+        unsigned char* tiles = lsm;
+        float4*        pal_s = reinterpret_cast<float4*>(lsm + 2 * TILE);
+        VRec*          vring = reinterpret_cast<VRec*>(lsm + 2 * TILE + (size_t)32 * par.prow * 16);
+        uint64_t*      bars  = reinterpret_cast<uint64_t*>(vring + LBS_C_RSTAGES * LBS_C_RSC * LBS_C_SC);
+        uint64_t*      rbar  = bars + 1;
+
+        // this CTA's run of superchunks
+        const int per  = (par.n_sc + par.vsplit - 1) / par.vsplit;
+        const int s_lo = split * per, s_hi = min(par.n_sc, s_lo + per);
+        if (s_lo >= s_hi)
+            return;
+        const int n_steps = s_hi - s_lo;
+        constexpr uint32_t RSTAGE_BYTES = LBS_C_RSC * LBS_C_SC * sizeof(VRec);
+        // named barriers: 1,2 = tile b full (compute arrives, store warp syncs); 3,4 = tile b empty (store arrives, compute syncs)
+
+        if (tid == 0)
+        {
+            mbar_init(&bars[0], 1);
+            for (int i = 0; i < LBS_C_RSTAGES; i++)
+                mbar_init(&rbar[i], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+
+        if (warp == LBS_C_WARPS)
+        {
+            // ---------------- store / load warp ----------------
+            if (lane == 0)
+            {
+                const uint32_t row_bytes = (uint32_t)par.pitch * 48;
+                mbar_expect_tx(&bars[0], row_bytes * 32);
+                for (int i = 0; i < 32; i++)
+                    tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + i0 + i) * par.pitch * 3, row_bytes, &bars[0]);
+                for (int st = 0; st < LBS_C_RSTAGES && st * LBS_C_RSC < n_steps; st++)
+                {
+                    mbar_expect_tx(&rbar[st], RSTAGE_BYTES);
+                    tma_load(vring + st * LBS_C_RSC * LBS_C_SC, par.vrec + (size_t)(s_lo + st * LBS_C_RSC) * LBS_C_SC, RSTAGE_BYTES, &rbar[st]);
+                }
+            }
+            const int row0 = (int)(par.slot_first + i0);
+            for (int s = 0; s < n_steps; s++)
+            {
+                const int b = s & 1;
+                named_sync(1 + b, LBS_C_THREADS); // all compute warps have written (and fenced) tile b
+                const int v0 = (s_lo + s) * LBS_C_SC;
+                if (lane < LBS_C_POS_SUBS)
+                    tma_store_2d(&tm_pos, v0 * 3 + lane * 32, row0, tiles + b * TILE + lane * LBS_C_SUB);
+                else if (NT && lane < LBS_C_POS_SUBS + LBS_C_NT_SUBS)
+                    tma_store_2d(&tm_nt, v0 * 6 + (lane - LBS_C_POS_SUBS) * 32, row0, tiles + b * TILE + lane * LBS_C_SUB);
+                tma_commit();
+                // the records of superchunk s are consumed by everybody: refill the stage when its last superchunk is done
+                if (lane == 0 && (s % LBS_C_RSC) == LBS_C_RSC - 1)
+                {
+                    const int nxt = s / LBS_C_RSC + LBS_C_RSTAGES; // stage index to fetch into the slot just freed
+                    if (nxt * LBS_C_RSC < n_steps)
+                    {
+                        const int st = (s / LBS_C_RSC) % LBS_C_RSTAGES;
+                        mbar_expect_tx(&rbar[st], RSTAGE_BYTES);
+                        tma_load(vring + st * LBS_C_RSC * LBS_C_SC, par.vrec + (size_t)(s_lo + nxt * LBS_C_RSC) * LBS_C_SC, RSTAGE_BYTES, &rbar[st]);
+                    }
+                }
+                if (s >= 1)
+                {
+                    tma_wait_read<1>();                        // the stores issued for superchunk s-1 have read tile b^1
+                    __syncwarp();
+                    named_arrive(3 + (b ^ 1), LBS_C_THREADS);  // ... which the compute warps may now overwrite (superchunk s+1)
+                }
+            }
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); // the stores themselves, not only their reads of the tiles
+            return;
+        }
+
+        // ---------------- compute warps ----------------
+        mbar_wait(&bars[0], 0);
+        const float4* prow = pal_s + (size_t)lane * par.prow;
+        float4 m[4][3];
+        {
+            const uint4 d = __ldg(reinterpret_cast<const uint4*>(&par.vrec[(size_t)s_lo * LBS_C_SC + warp * LBS_C_VPW].w3));
+            lbs_i_load(m[0], prow, d.y & 0xffffu), lbs_i_load(m[1], prow, d.y >> 16);
+            lbs_i_load(m[2], prow, d.z & 0xffffu), lbs_i_load(m[3], prow, d.z >> 16);
+        }
+        // swizzled staging offsets of this lane (row = instance) for the 16-byte units this warp owns:
+        // positions: units 3w..3w+2 of 24, normal+tangent: units 6w..6w+5 of 48; unit U -> sub-tile U >> 3, chunk (U & 7) ^ (row & 7)
+        uint32_t off_p[3], off_n[6];
+#pragma unroll
+        for (int q = 0; q < 3; q++)
+        {
+            const int U = warp * 3 + q;
+            off_p[q]    = (U >> 3) * LBS_C_SUB + lane * 128 + (((U & 7) ^ (lane & 7)) << 4);
+        }
+#pragma unroll
+        for (int q = 0; q < 6; q++)
+        {
+            const int U = warp * 6 + q;
+            off_n[q]    = (LBS_C_POS_SUBS + (U >> 3)) * LBS_C_SUB + lane * 128 + (((U & 7) ^ (lane & 7)) << 4);
+        }
+        for (int s = 0; s < n_steps; s++)
+        {
+            const int b = s & 1;
+            const int ridx = s / LBS_C_RSC, rsub = s - ridx * LBS_C_RSC, rst = ridx % LBS_C_RSTAGES;
+            if (rsub == 0)
+                mbar_wait(&rbar[rst], (uint32_t)(ridx / LBS_C_RSTAGES) & 1);
+            const VRec* vr = vring + (rst * LBS_C_RSC + rsub) * LBS_C_SC + warp * LBS_C_VPW;
+            float4 op[3], on[6];
+            float* opf = reinterpret_cast<float*>(op);
+            float* onf = reinterpret_cast<float*>(on);
+            float4 na = *reinterpret_cast<const float4*>(&vr[0].px), nb = *reinterpret_cast<const float4*>(&vr[0].nx);
+            float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].tx);
+            uint4  nd = *reinterpret_cast<const uint4*>(&vr[0].w3);
+#pragma unroll
+            for (int j = 0; j < LBS_C_VPW; j++)
+            {
+                const float4 a = na, bb = nb, t = nt_;
+                const uint4  d = nd;
+                if (j + 1 < LBS_C_VPW)
+                {
+                    na  = *reinterpret_cast<const float4*>(&vr[j + 1].px);
+                    nb  = *reinterpret_cast<const float4*>(&vr[j + 1].nx);
+                    nt_ = *reinterpret_cast<const float4*>(&vr[j + 1].tx);
+                    nd  = *reinterpret_cast<const uint4*>(&vr[j + 1].w3);
+                }
+                if (d.w)
+                {
+                    if (d.w & 1) lbs_i_load(m[0], prow, d.y & 0xffffu);
+                    if (d.w & 2) lbs_i_load(m[1], prow, d.y >> 16);
+                    if (d.w & 4) lbs_i_load(m[2], prow, d.z & 0xffffu);
+                    if (d.w & 8) lbs_i_load(m[3], prow, d.z >> 16);
+                }
+                const float w0 = a.w, w1 = bb.w, w2 = t.w, w3 = __uint_as_float(d.x);
+                float4 B[3];
+                {
+                    const unsigned long long ww0 = pack2(w0, w0), ww1 = pack2(w1, w1), ww2 = pack2(w2, w2), ww3 = pack2(w3, w3);
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+                    {
+                        unsigned long long lo = mul2(pack2(m[0][r].x, m[0][r].y), ww0), hi = mul2(pack2(m[0][r].z, m[0][r].w), ww0);
+                        lo = fma2(pack2(m[1][r].x, m[1][r].y), ww1, lo), hi = fma2(pack2(m[1][r].z, m[1][r].w), ww1, hi);
+                        lo = fma2(pack2(m[2][r].x, m[2][r].y), ww2, lo), hi = fma2(pack2(m[2][r].z, m[2][r].w), ww2, hi);
+                        lo = fma2(pack2(m[3][r].x, m[3][r].y), ww3, lo), hi = fma2(pack2(m[3][r].z, m[3][r].w), ww3, hi);
+                        unpack2(lo, B[r].x, B[r].y), unpack2(hi, B[r].z, B[r].w);
+                    }
+                }
+                opf[j * 3 + 0] = B[0].x * a.x + B[0].y * a.y + B[0].z * a.z + B[0].w; // mesh.vert:104
+                opf[j * 3 + 1] = B[1].x * a.x + B[1].y * a.y + B[1].z * a.z + B[1].w;
+                opf[j * 3 + 2] = B[2].x * a.x + B[2].y * a.y + B[2].z * a.z + B[2].w;
+                if (NT)
+                {
+                    const float nx = B[0].x * bb.x + B[0].y * bb.y + B[0].z * bb.z, ny = B[1].x * bb.x + B[1].y * bb.y + B[1].z * bb.z,
+                                nz = B[2].x * bb.x + B[2].y * bb.y + B[2].z * bb.z;
+                    const float tx = B[0].x * t.x + B[0].y * t.y + B[0].z * t.z, ty = B[1].x * t.x + B[1].y * t.y + B[1].z * t.z,
+                                tz = B[2].x * t.x + B[2].y * t.y + B[2].z * t.z;
+                    const float rn = rsqrt_ftz(nx * nx + ny * ny + nz * nz);
+                    const float rt = rsqrt_ftz(tx * tx + ty * ty + tz * tz);
+                    onf[j * 6 + 0] = nx * rn, onf[j * 6 + 1] = ny * rn, onf[j * 6 + 2] = nz * rn;
+                    onf[j * 6 + 3] = tx * rt, onf[j * 6 + 4] = ty * rt, onf[j * 6 + 5] = tz * rt;
+                }
+            }
+            if (s >= 2)
+                named_sync(3 + b, LBS_C_THREADS); // the tensor stores of superchunk s-2 have read tile b
+            unsigned char* tb = tiles + b * TILE;
+#pragma unroll
+            for (int q = 0; q < 3; q++)
+                *reinterpret_cast<float4*>(tb + off_p[q]) = op[q];
+            if (NT)
+            {
+#pragma unroll
+                for (int q = 0; q < 6; q++)
+                    *reinterpret_cast<float4*>(tb + off_n[q]) = on[q];
+            }
+            fence_async_smem();
+            named_arrive(1 + b, LBS_C_THREADS);
         }
     }
 } // namespace pcl

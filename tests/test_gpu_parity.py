@@ -301,7 +301,7 @@ def _check_skin(oracle, mesh, pal, pos, nt):
             assert np.all(np.isnan(nt[i][~ok]).any(axis=1))  # normalize(0) stays NaN like the shader
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
 def test_lbs_reference_golden(ctx, player_dev, variant):
     """mesh.vert restated with the reference's Matrix4x4/Vector4 operators (oracle/_ref) on 2048 vertices."""
     from piccolo_b200 import capi
@@ -318,7 +318,7 @@ def test_lbs_reference_golden(ctx, player_dev, variant):
     assert np.all(pos[0][5] == 0) and np.all(np.isnan(nt[0][5]))  # vertex with zero total weight
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
 @pytest.mark.parametrize("V,N", [(16380, 37), (1001, 5), (255, 3), (4, 1), (513, 70)])
 def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
     from piccolo_b200 import capi
@@ -336,7 +336,7 @@ def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
     ctx.set_option("lbs_warps", 0)
 
 
-@pytest.mark.parametrize("variant", [0, 1, -1, 2])
+@pytest.mark.parametrize("variant", [0, 1, -1, 2, 3])
 def test_lbs_config5_synthetic(ctx, oracle, variant):
     """257 palette slots: 32 palettes do not fit in shared memory, so auto (-1) must fall back to the lane-per-vertex
     kernel and forcing the crowd kernel (2) must be refused, not silently mis-skinned."""
@@ -349,7 +349,7 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     mh = ctx.upload_mesh(mesh, 256)
     N = 40
     ph = np.linspace(0.05, 0.95, N, dtype=np.float32)
-    if variant == 2:
+    if variant >= 2:
         with pytest.raises(capi.PclError) as e:
             _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
         assert e.value.code == -3
@@ -359,7 +359,7 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     _check_skin(oracle, mesh, pal[::5], pos[::5], nt[::5])
 
 
-@pytest.mark.parametrize("variant", [0, 2])
+@pytest.mark.parametrize("variant", [0, 2, 3])
 def test_lbs_ring_slots_and_linearity(ctx, player_dev, player, variant):
     """Ring addressing + a size-independent property: skinning is linear in the vertex position stream."""
     from piccolo_b200 import capi
@@ -367,34 +367,36 @@ def test_lbs_ring_slots_and_linearity(ctx, player_dev, player, variant):
     mesh = A.make_player_mesh(player[0], V=16380, seed=1)
     m2 = A.MeshData(mesh.pos * np.float32(2.0), mesh.nrm, mesh.tan, mesh.uv, mesh.index_buffer, mesh.bind_idx, mesh.bind_w)
     h1, h2 = ctx.upload_mesh(mesh, 58), ctx.upload_mesh(m2, 58)
-    N = 64
+    N, C = 160, 32  # variant 3 works on whole 32-instance tiles (a ragged remainder is handed to the variant-2 kernel)
     b = ctx.batch(skel, N, 1)
     b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=np.linspace(0, 1, N, dtype=np.float32))
     b.pose()
     ctx.set_option("lbs_variant", variant)
-    s1, s2 = ctx.skinbuf(h1, 16380, 16, capi.PCL_SKIN_POS), ctx.skinbuf(h2, 16380, 16, capi.PCL_SKIN_POS)
-    b.skin(h1, s1, first=40, count=8, slot_first=4)
-    b.skin(h2, s2, first=40, count=8, slot_first=4)
+    s1, s2 = ctx.skinbuf(h1, 16380, 3 * C, capi.PCL_SKIN_POS), ctx.skinbuf(h2, 16380, 3 * C, capi.PCL_SKIN_POS)
+    b.skin(h1, s1, first=96, count=C, slot_first=C)
+    b.skin(h2, s2, first=96, count=C, slot_first=C)
     b.skin(h1, s1, first=0, count=4, slot_first=0)
-    p1, _ = s1.download(4, 8)
-    p2, _ = s2.download(4, 8)
-    pal = b.download_palette(40, 8)
+    p1, _ = s1.download(C, C)
+    p2, _ = s2.download(C, C)
+    pal = b.download_palette(96, C)
     t = pal[:, :, [3, 7, 11]]  # translations; p(2x) - 2 p(x) = -sum_k w_k t_k : bounded by max |t|
     assert np.abs(p2 - 2 * p1).max() <= np.abs(t).max() * 1.0001 + 1e-4
     full = ctx.skinbuf(h1, 16380, N, capi.PCL_SKIN_POS)
     b.skin(h1, full)
     pf, _ = full.download()
     ctx.set_option("lbs_vsplit", 5)
-    b.skin(h1, s1, first=40, count=8, slot_first=8)
+    b.skin(h1, s1, first=96, count=C, slot_first=2 * C)
     ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_variant", -1)
-    assert np.array_equal(pf[40:48], p1)  # same instances through a different slot / tile position: bit-identical
-    assert np.array_equal(pf[0:4], s1.download(0, 4)[0])
-    assert np.array_equal(s1.download(8, 8)[0], p1)  # and through a different vertex split
-    for x in (s1, s2, full, b):
-        x.close()
+    assert np.array_equal(pf[96:96 + C], p1)  # same instances through a different slot / tile position: bit-identical
+    assert np.array_equal(s1.download(2 * C, C)[0], p1)  # and through a different vertex split
+    small = s1.download(0, 4)[0]  # 4 instances: variant 3 hands them to the variant-2 kernel (another summation order)
+    assert np.array_equal(pf[0:4], small) if variant != 3 else np.abs(pf[0:4] - small).max() <= 1e-5
+    for x_ in (s1, s2, full, b):
+        x_.close()
 
 
-def test_lbs_full_size_config3_properties(ctx, oracle, player):
+@pytest.mark.parametrize("variant", [2, 3])
+def test_lbs_full_size_config3_properties(ctx, oracle, player, variant):
     """BASELINE.json config 3 at full size (100 000 instances, 2-clip blend, 16 380 vertices, 25 000-slot ring): sampled
     instances match the oracle, and an instance's skinned streams do not depend on the launch it was part of."""
     from piccolo_b200 import capi
@@ -414,7 +416,7 @@ def test_lbs_full_size_config3_properties(ctx, oracle, player):
     b.pose()
     sb = ctx.skinbuf(mh, mesh.V, ring, capi.PCL_SKIN_POS_NRM_TAN)
     small = ctx.skinbuf(mh, mesh.V, 64, capi.PCL_SKIN_POS_NRM_TAN)
-    ctx.set_option("lbs_variant", 2)
+    ctx.set_option("lbs_variant", variant)
     orc_clips = [oracle.clip(cl, am), oracle.clip(run, am)]
     sv = oracle.skeleton(sk)
     for chunk in (0, 3):
@@ -426,10 +428,16 @@ def test_lbs_full_size_config3_properties(ctx, oracle, player):
             rp, rn, rt = oracle.lbs(mesh, oracle.palette_slots(ref[0]))
             assert np.abs(pos[0] - rp).max() <= POS_TOL * max(1.0, np.abs(rp).max())
             assert np.abs(nt[0][:, :3] - rn).max() <= 1e-4 and np.abs(nt[0][:, 3:] - rt).max() <= 1e-4
-            lo = max(0, min(inst - 7, N - 64))  # the same instance inside a different 64-instance launch, other tile lane
+            lo = min(max(inst // 32 * 32 - 32, 0), N - 64)  # the same instance inside another 64-instance launch ...
+            if variant != 3 and lo + 67 <= N and inst >= lo + 3:
+                lo += 3  # ... and, where the kernel allows ragged tiles, in another lane of its tile
             b.skin(mh, small, first=lo, count=64, slot_first=0)
             p2, n2 = small.download(inst - lo, 1)
-            assert np.array_equal(p2, pos) and np.array_equal(n2, nt)
+            if variant == 3 and slot >= ring // 32 * 32:
+                # the ragged tail of the 25 000-instance launch was skinned by the variant-2 kernel (other summation order)
+                assert np.abs(p2 - pos).max() <= 1e-5 and np.abs(n2 - nt).max() <= 1e-5
+            else:
+                assert np.array_equal(p2, pos) and np.array_equal(n2, nt)
     ctx.set_option("lbs_variant", -1)
     for x in (sb, small, b):
         x.close()
