@@ -6,7 +6,7 @@ Workload "config3" (BASELINE.json configs[2]) PER GPU:
   crouch-walk clip + a seeded 17-frame synthetic "run" variant -- the reference ships one clip) with
   weights (w, 1-w), then 4-weight linear-blend skinning of a 16 380-vertex synthetic player mesh
   (robot.mesh_bind.json is a missing blob) to positions + normals + tangents (36 B / vertex) into a
-  device ring of 25 000 instance slots (14.7 GB; the consumer -- a renderer -- would drain it).
+  device ring of 25 024 instance slots (14.8 GB; the consumer -- a renderer -- would drain it).
 A "step" = one pcl_batch_tick (phase advance + sample + blend + hierarchy + palette) + the LBS launches
 that skin all instances (4 ring chunks).  Instances shard across GPUs with no collective (weak scaling).
 
@@ -39,7 +39,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 V_PLAYER = 16380
-RING_SLOTS = 25000
+RING_SLOTS = 25024  # 782 whole 32-instance tiles; 100 000 = 3 x 25 024 + 24 928 (779 tiles)
 DT = 1.0 / 60.0
 CLIP_LEN = 0.76666998863220215
 
@@ -278,7 +278,7 @@ def run_ours(args):
     per_launch = np.mean([lbs_algorithmic_bytes(n, mesh.V, sk.J, 36) for _, n in chunks])
     achieved = per_launch / (lbs_ms * 1e-3) / 1e9
     pose_bytes = N * (2 * 12 + 60 * 48)
-    roofline = {"bound": "hbm", "kernel": "lbs_inst_kernel<NT=1>" if (args.lbs_variant in (None, -1, 2)) else "lbs_kernel<NT=1>", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": {None: "lbs_cta_kernel<NT=1>", -1: "lbs_cta_kernel<NT=1>", 3: "lbs_cta_kernel<NT=1>", 2: "lbs_inst_kernel<NT=1>"}.get(args.lbs_variant, "lbs_kernel<NT=1>"), "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(per_launch), "launch_ms": round(lbs_ms, 4),
                 "frac_of_nominal_8000": round(achieved / 8000.0, 4),

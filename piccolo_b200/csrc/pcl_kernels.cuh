@@ -1263,14 +1263,18 @@ namespace pcl
     constexpr int LBS_C_SC      = 32;                      // vertices per superchunk
     constexpr int LBS_C_VPW     = LBS_C_SC / LBS_C_WARPS;  // 4 vertices per warp per superchunk
     constexpr int LBS_C_RSC     = 4;                       // superchunks per vertex-record stage
-    constexpr int LBS_C_RSTAGES = 3;
+#ifndef PCL_LBS_C_TILES
+#define PCL_LBS_C_TILES 3
+#endif
+    constexpr int LBS_C_TILES   = PCL_LBS_C_TILES;         // staging tiles in flight between the compute warps and the TMA stores
+    constexpr int LBS_C_RSTAGES = LBS_C_TILES >= 3 ? 2 : 3;
     constexpr int LBS_C_SUB     = 32 * 128;                // one swizzled sub-tile: 32 instances x 128 bytes
     constexpr int LBS_C_POS_SUBS = 3, LBS_C_NT_SUBS = 6;   // 384 B and 768 B per instance and superchunk
 
     __host__ __device__ inline size_t lbs_c_tile_bytes(bool nt) { return (size_t)(LBS_C_POS_SUBS + (nt ? LBS_C_NT_SUBS : 0)) * LBS_C_SUB; }
     __host__ __device__ inline size_t lbs_c_smem_bytes(int prow, bool nt)
     {
-        return 2 * lbs_c_tile_bytes(nt)                                                // two staging tiles (1024-byte aligned, first)
+        return LBS_C_TILES * lbs_c_tile_bytes(nt)                                      // staging tiles (1024-byte aligned, first)
                + (size_t)32 * prow * 16                                                // palettes
                + (size_t)LBS_C_RSTAGES * LBS_C_RSC * LBS_C_SC * sizeof(VRec)           // vertex-record ring
                + 8 * (1 + LBS_C_RSTAGES) + 64;                                         // mbarriers
@@ -1305,8 +1309,8 @@ namespace pcl
 
         const size_t   TILE  = lbs_c_tile_bytes(NT);
         unsigned char* tiles = lsm;
-        float4*        pal_s = reinterpret_cast<float4*>(lsm + 2 * TILE);
-        VRec*          vring = reinterpret_cast<VRec*>(lsm + 2 * TILE + (size_t)32 * par.prow * 16);
+        float4*        pal_s = reinterpret_cast<float4*>(lsm + LBS_C_TILES * TILE);
+        VRec*          vring = reinterpret_cast<VRec*>(lsm + LBS_C_TILES * TILE + (size_t)32 * par.prow * 16);
         uint64_t*      bars  = reinterpret_cast<uint64_t*>(vring + LBS_C_RSTAGES * LBS_C_RSC * LBS_C_SC);
         uint64_t*      rbar  = bars + 1;
 
@@ -1317,7 +1321,7 @@ namespace pcl
             return;
         const int n_steps = s_hi - s_lo;
         constexpr uint32_t RSTAGE_BYTES = LBS_C_RSC * LBS_C_SC * sizeof(VRec);
-        // named barriers: 1,2 = tile b full (compute arrives, store warp syncs); 3,4 = tile b empty (store arrives, compute syncs)
+        // named barriers: 1 + b = tile b full (compute arrives, store warp syncs); 1 + TILES + b = tile b empty (store arrives, compute syncs)
 
         if (tid == 0)
         {
@@ -1346,7 +1350,7 @@ namespace pcl
             const int row0 = (int)(par.slot_first + i0);
             for (int s = 0; s < n_steps; s++)
             {
-                const int b = s & 1;
+                const int b = s % LBS_C_TILES;
                 named_sync(1 + b, LBS_C_THREADS); // all compute warps have written (and fenced) tile b
                 const int v0 = (s_lo + s) * LBS_C_SC;
                 if (lane < LBS_C_POS_SUBS)
@@ -1365,11 +1369,11 @@ namespace pcl
                         tma_load(vring + st * LBS_C_RSC * LBS_C_SC, par.vrec + (size_t)(s_lo + nxt * LBS_C_RSC) * LBS_C_SC, RSTAGE_BYTES, &rbar[st]);
                     }
                 }
-                if (s >= 1)
+                if (s >= LBS_C_TILES - 1)
                 {
-                    tma_wait_read<1>();                        // the stores issued for superchunk s-1 have read tile b^1
+                    tma_wait_read<LBS_C_TILES - 1>(); // the stores issued for superchunk s-(TILES-1) have read their tile ...
                     __syncwarp();
-                    named_arrive(3 + (b ^ 1), LBS_C_THREADS);  // ... which the compute warps may now overwrite (superchunk s+1)
+                    named_arrive(1 + LBS_C_TILES + (s + 1) % LBS_C_TILES, LBS_C_THREADS); // ... which superchunk s+1 may now overwrite
                 }
             }
             asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); // the stores themselves, not only their reads of the tiles
@@ -1402,7 +1406,7 @@ namespace pcl
         }
         for (int s = 0; s < n_steps; s++)
         {
-            const int b = s & 1;
+            const int b = s % LBS_C_TILES;
             const int ridx = s / LBS_C_RSC, rsub = s - ridx * LBS_C_RSC, rst = ridx % LBS_C_RSTAGES;
             if (rsub == 0)
                 mbar_wait(&rbar[rst], (uint32_t)(ridx / LBS_C_RSTAGES) & 1);
@@ -1461,8 +1465,8 @@ namespace pcl
                     onf[j * 6 + 3] = tx * rt, onf[j * 6 + 4] = ty * rt, onf[j * 6 + 5] = tz * rt;
                 }
             }
-            if (s >= 2)
-                named_sync(3 + b, LBS_C_THREADS); // the tensor stores of superchunk s-2 have read tile b
+            if (s >= LBS_C_TILES)
+                named_sync(1 + LBS_C_TILES + b, LBS_C_THREADS); // the tensor stores of superchunk s-TILES have read tile b
             unsigned char* tb = tiles + b * TILE;
 #pragma unroll
             for (int q = 0; q < 3; q++)
