@@ -224,6 +224,8 @@ def run_ours(args):
         ctx.set_option("lbs_variant", args.lbs_variant)
     if args.lbs_warps:
         ctx.set_option("lbs_warps", args.lbs_warps)
+    if args.lbs_vsplit:
+        ctx.set_option("lbs_vsplit", args.lbs_vsplit)
 
     def skin_all():
         for f, n in chunks:
@@ -445,6 +447,7 @@ def main():
     ap.add_argument("--instances", type=int, default=100000, help="instances per GPU")
     ap.add_argument("--lbs-variant", type=int, default=None)
     ap.add_argument("--lbs-warps", type=int, default=0)
+    ap.add_argument("--lbs-vsplit", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-configs", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=16.0)
