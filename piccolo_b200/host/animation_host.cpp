@@ -111,6 +111,40 @@ namespace Piccolo
     }
 
     // ---------------------------------------------------------------------------------------------
+    // asset-side conventions
+    // ---------------------------------------------------------------------------------------------
+    int find_index_by_name(const SkeletonData& skeleton, const std::string& name)
+    {
+        for (const RawBone& b : skeleton.bones_map)
+            if (b.name == name)
+                return b.index;
+        return std::numeric_limits<int>::max();
+    }
+    AnimSkelMap buildAnimSkelMap(const AnimNodeMap& anim, const SkeletonData& skeleton)
+    {
+        AnimSkelMap m;
+        for (const std::string& n : anim.convert)
+            m.convert.push_back(find_index_by_name(skeleton, n));
+        return m;
+    }
+    bool addBoneBind(MeshData& mesh_bind, size_t bone_index, size_t vertex_index, float weight)
+    {
+        if (vertex_index >= mesh_bind.bind.size())
+            return false;
+        SkeletonBinding& b   = mesh_bind.bind[vertex_index];
+        int*             idx[4] = {&b.index0, &b.index1, &b.index2, &b.index3};
+        float*           w[4]   = {&b.weight0, &b.weight1, &b.weight2, &b.weight3};
+        for (int k = 0; k < 4; k++)
+            if (*idx[k] == 0) // 0 = empty slot, which is why stored indices are bone_index + 1
+            {
+                *idx[k] = (int)bone_index + 1;
+                *w[k]   = weight;
+                return true;
+            }
+        return false;
+    }
+
+    // ---------------------------------------------------------------------------------------------
     // AnimationManager (function/animation/animation_system.cpp)
     // ---------------------------------------------------------------------------------------------
     std::map<std::string, std::shared_ptr<SkeletonData>>  AnimationManager::m_skeleton_definition_cache;

@@ -344,6 +344,15 @@ namespace Piccolo
         std::vector<int32_t> m_index;
     };
 
+    // ---- asset-side conventions (function/animation/utilities.cpp:46-53, animation_loader.cpp:30-71) -------------
+    // The reference keeps these in an anonymous namespace of its offline converter and never calls them at run time;
+    // they are what produced the bundled anim.skeleton_map.json / robot.mesh_bind.json and are provided so that new
+    // clips and meshes can be bound the same way.
+    int         find_index_by_name(const SkeletonData& skeleton, const std::string& name); // INT_MAX when absent
+    AnimSkelMap buildAnimSkelMap(const AnimNodeMap& anim, const SkeletonData& skeleton);    // channel name -> bone index
+    // first free of the vertex's four slots gets (bone_index + 1, weight); returns false when all four are taken
+    bool addBoneBind(MeshData& mesh_bind, size_t bone_index, size_t vertex_index, float weight);
+
     // RawBone arrays for pcl_upload_skeleton (shared by Skeleton and AnimationBatch)
     pcl_skel uploadSkeleton(const SkeletonData& def);
     pcl_mesh uploadMesh(const MeshData& mesh, int32_t max_slot);

@@ -84,6 +84,32 @@ static int cmd_load(int argc, char** argv)
     return 0;
 }
 
+// offline-converter conventions: name -> index map and the first-free-of-four binding rule
+static int cmd_bind(int argc, char** argv)
+{
+    if (argc < 6)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    auto            sk = AnimationLoader().loadSkeletonData(argv[3]);
+    AnimNodeMap     nm;
+    // channel names = the clip's node_channels names, which is what AnimationAsset.node_map.convert lists
+    auto cl = AnimationLoader().loadAnimationClipData(argv[4]);
+    for (auto& ch : cl->node_channels)
+        nm.convert.push_back(ch.name);
+    nm.convert.push_back("no such bone");
+    AnimSkelMap m = buildAnimSkelMap(nm, *sk);
+    g_out         = fopen(argv[5], "wb");
+    puti(1, std::vector<int32_t>(m.convert.begin(), m.convert.end()));
+    MeshData md;
+    md.bind.resize(3);
+    bool ok[6] = {addBoneBind(md, 4, 0, 0.5f), addBoneBind(md, 9, 0, 0.25f), addBoneBind(md, 0, 0, 0.125f), addBoneBind(md, 57, 0, 0.0625f),
+                  addBoneBind(md, 3, 0, 1.f), addBoneBind(md, 3, 7, 1.f)};
+    puti(2, {md.bind[0].index0, md.bind[0].index1, md.bind[0].index2, md.bind[0].index3, ok[0], ok[1], ok[2], ok[3], ok[4], ok[5], md.bind[1].index0});
+    putf(3, {md.bind[0].weight0, md.bind[0].weight1, md.bind[0].weight2, md.bind[0].weight3});
+    fclose(g_out);
+    return 0;
+}
+
 // AnimationManager::getBlendStateWithClipData of a two-clip, two-mask blend state: the per-bone weights
 static int cmd_weights(int argc, char** argv)
 {
@@ -214,6 +240,8 @@ int main(int argc, char** argv)
         return 2;
     if (!std::strcmp(argv[1], "load"))
         return cmd_load(argc, argv);
+    if (!std::strcmp(argv[1], "bind"))
+        return cmd_bind(argc, argv);
     if (!std::strcmp(argv[1], "weights"))
         return cmd_weights(argc, argv);
     if (!std::strcmp(argv[1], "tick"))

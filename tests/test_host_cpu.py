@@ -83,3 +83,18 @@ def test_blend_weights_match_reference_and_oracle(player, oracle, tmp_path):
     if O.RefLib.available() and os.path.isdir(O.REFERENCE_ROOT):
         ref = O.RefLib(str(tmp_path)).blend_weights(urls["skeleton"], urls["clip"], urls["map"], H.DATA + "m0.json", H.DATA + "m1.json", w[0], w[1], sk.J)
         assert np.array_equal(ref, want)
+
+
+def test_offline_converter_conventions(player, tmp_path):
+    """buildAnimSkelMap / addBoneBind (animation_loader.cpp:30-71, utilities.cpp:46-53): the name->index map reproduces the
+    bundled anim.skeleton_map.json, bindings go to the first free of four slots as bone_index + 1."""
+    sk, cl, am, mk = player
+    urls = H.write_player_tree(str(tmp_path), player)
+    out = tmp_path / "bind.bin"
+    r = H.run(["bind", tmp_path, urls["skeleton"], urls["clip"], out])
+    assert r.returncode == 0, r.stderr
+    d = H.read_dump(out)
+    assert np.array_equal(d["1i"][:-1], am.convert)  # the bundled map IS the name map of the bundled clip onto the skeleton
+    assert d["1i"][-1] == 2147483647                 # unknown name -> INT_MAX (find_index_by_name)
+    assert d["2i"].tolist() == [5, 10, 1, 58, 1, 1, 1, 1, 0, 0, 0]  # 4 slots fill in order, 5th refused, bad vertex refused
+    assert d["3"].tolist() == [0.5, 0.25, 0.125, 0.0625]
