@@ -1114,7 +1114,9 @@ extern "C"
             if (var < 0)
             {
                 const bool fits3 = m.d_vrec_cta && out->has_tmaps && lbs_c_smem_bytes(prow, nt) <= (size_t)c->max_smem_optin;
-                var = (fits3 && count >= 32) ? 3 : ((fits && count >= 24) ? 2 : 0);
+                // measured on the player mesh (tools/lbs_sweep.py): below ~200 instances the long per-CTA vertex walk of the
+                // crowd kernels (a ~35 us floor) loses to the lane-per-vertex kernel, which spreads over many more CTAs
+                var = (fits3 && count >= 160) ? 3 : ((fits && !fits3 && count >= 160) ? 2 : 0);
             }
             if (var == 3)
             {
