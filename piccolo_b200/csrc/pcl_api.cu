@@ -1133,7 +1133,7 @@ extern "C"
                     int vs = c->opt_lbs_vsplit;
                     if (vs == 0)
                     {
-                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_sc / 32));
+                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_sc / 32)); // finer splits measured slower (palette reloads, pipeline fills)
                         double    best   = -1.0;
                         for (int cand = 1; cand <= max_vs; cand++)
                         {
