@@ -64,7 +64,8 @@ const char* pcl_last_error(const pcl_ctx* ctx); /* ctx == NULL: error of the las
 int         pcl_sync(pcl_ctx* ctx);
 /* number of this library's kernels launched on the context so far */
 int64_t     pcl_launch_count(const pcl_ctx* ctx);
-/* pinned host memory for the download / set calls (cudaHostAlloc); optional, any host memory works */
+/* pinned host memory for the download / set calls (cudaHostAlloc); optional, any host memory works.
+ * Blocks not freed with pcl_host_free are released by pcl_destroy. */
 int         pcl_host_alloc(pcl_ctx* ctx, size_t bytes, void** out);
 int         pcl_host_free(pcl_ctx* ctx, void* p);
 /* device timing on the context's compute stream: begin records an event, end waits for all the

@@ -85,6 +85,7 @@ struct pcl_ctx
     int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0;
     int          max_smem_optin = 0, sm_count = 0;
     std::map<const void*, size_t> smem_attr; // largest dynamic shared memory size already enabled per kernel
+    std::vector<void*> host_allocs;           // pcl_host_alloc blocks still alive (released by pcl_destroy at the latest)
 };
 
 struct pcl_batch
@@ -330,6 +331,8 @@ extern "C"
         for (auto& m : c->meshes)
             cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec), cudaFree(m.d_vrec_cta);
         cudaFree(c->d_clips);
+        for (void* p : c->host_allocs)
+            cudaFreeHost(p);
         cudaEventDestroy(c->ev_pose), cudaEventDestroy(c->ev_copy), cudaEventDestroy(c->t0), cudaEventDestroy(c->t1);
         cudaStreamDestroy(c->compute), cudaStreamDestroy(c->copy);
         delete c;
@@ -356,12 +359,17 @@ extern "C"
             return PCL_ERR_INVALID;
         PCL_CK(c, cudaSetDevice(c->device));
         PCL_CK(c, cudaHostAlloc(out, bytes, cudaHostAllocDefault));
+        c->host_allocs.push_back(*out);
         return PCL_OK;
     }
     int pcl_host_free(pcl_ctx* c, void* p)
     {
         if (!c)
             return PCL_ERR_INVALID;
+        auto it = std::find(c->host_allocs.begin(), c->host_allocs.end(), p);
+        if (it == c->host_allocs.end())
+            return fail(c, PCL_ERR_INVALID, "pcl_host_free: pointer was not returned by pcl_host_alloc of this context");
+        c->host_allocs.erase(it);
         PCL_CK(c, cudaFreeHost(p));
         return PCL_OK;
     }
