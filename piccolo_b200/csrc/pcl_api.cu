@@ -1121,14 +1121,15 @@ extern "C"
                 return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 2 needs 32 palettes in shared memory");
             if (var < 0)
             {
-                const bool fits3 = m.d_vrec_cta && out->has_tmaps && lbs_c_smem_bytes(prow, nt) <= (size_t)c->max_smem_optin;
+                const bool fits3 = m.d_vrec_cta && out->has_tmaps && lbs_c_smem_bytes(prow, nt, 2) <= (size_t)c->max_smem_optin;
                 // measured on the player mesh (tools/lbs_sweep.py): below ~200 instances the long per-CTA vertex walk of the
                 // crowd kernels (a ~35 us floor) loses to the lane-per-vertex kernel, which spreads over many more CTAs
                 var = (fits3 && count >= 160) ? 3 : ((fits && !fits3 && count >= 160) ? 2 : 0);
             }
             if (var == 3)
             {
-                const size_t smem_c = lbs_c_smem_bytes(prow, nt);
+                const int    ctiles = lbs_c_smem_bytes(prow, nt, 3) <= (size_t)c->max_smem_optin ? 3 : 2;
+                const size_t smem_c = lbs_c_smem_bytes(prow, nt, ctiles);
                 if (!m.d_vrec_cta || !out->has_tmaps || smem_c > (size_t)c->max_smem_optin)
                     return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 3 needs 32 palettes in shared memory and tensor maps");
                 const long long full = count / 32; // whole 32-instance tiles; a ragged remainder goes to lbs_inst_kernel below
@@ -1153,16 +1154,16 @@ extern "C"
                     }
                     q.vsplit = std::max(1, std::min(vs, q.n_sc));
                     const unsigned grid = (unsigned)(full * q.vsplit);
-                    if (nt)
-                    {
-                        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<true>, smem_c); if (rc__) return rc__; }
-                        lbs_cta_kernel<true><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos, out->tm_nt);
-                    }
-                    else
-                    {
-                        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<false>, smem_c); if (rc__) return rc__; }
-                        lbs_cta_kernel<false><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos, out->tm_nt);
-                    }
+#define PCL_LAUNCH_LBSC(NT_, T_)                                                                                            \
+    {                                                                                                                       \
+        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<NT_, T_>, smem_c); if (rc__) return rc__; }                 \
+        lbs_cta_kernel<NT_, T_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos, out->tm_nt);                   \
+    }
+                    if (nt && ctiles == 3) PCL_LAUNCH_LBSC(true, 3)
+                    else if (nt) PCL_LAUNCH_LBSC(true, 2)
+                    else if (ctiles == 3) PCL_LAUNCH_LBSC(false, 3)
+                    else PCL_LAUNCH_LBSC(false, 2)
+#undef PCL_LAUNCH_LBSC
                     c->launches++;
                     PCL_CK(c, cudaGetLastError());
                 }

@@ -1263,21 +1263,19 @@ namespace pcl
     constexpr int LBS_C_SC      = 32;                      // vertices per superchunk
     constexpr int LBS_C_VPW     = LBS_C_SC / LBS_C_WARPS;  // 4 vertices per warp per superchunk
     constexpr int LBS_C_RSC     = 4;                       // superchunks per vertex-record stage
-#ifndef PCL_LBS_C_TILES
-#define PCL_LBS_C_TILES 3
-#endif
-    constexpr int LBS_C_TILES   = PCL_LBS_C_TILES;         // staging tiles in flight between the compute warps and the TMA stores
-    constexpr int LBS_C_RSTAGES = LBS_C_TILES >= 3 ? 2 : 3;
+    // staging tiles in flight between the compute warps and the TMA stores: 3 when the palettes leave room (J <= 63),
+    // else 2 (J <= 82); the vertex-record ring gets the stage the third tile gives up
+    __host__ __device__ constexpr int lbs_c_rstages(int tiles) { return tiles >= 3 ? 2 : 3; }
     constexpr int LBS_C_SUB     = 32 * 128;                // one swizzled sub-tile: 32 instances x 128 bytes
     constexpr int LBS_C_POS_SUBS = 3, LBS_C_NT_SUBS = 6;   // 384 B and 768 B per instance and superchunk
 
     __host__ __device__ inline size_t lbs_c_tile_bytes(bool nt) { return (size_t)(LBS_C_POS_SUBS + (nt ? LBS_C_NT_SUBS : 0)) * LBS_C_SUB; }
-    __host__ __device__ inline size_t lbs_c_smem_bytes(int prow, bool nt)
+    __host__ __device__ inline size_t lbs_c_smem_bytes(int prow, bool nt, int tiles)
     {
-        return LBS_C_TILES * lbs_c_tile_bytes(nt)                                      // staging tiles (1024-byte aligned, first)
+        return tiles * lbs_c_tile_bytes(nt)                                            // staging tiles (1024-byte aligned, first)
                + (size_t)32 * prow * 16                                                // palettes
-               + (size_t)LBS_C_RSTAGES * LBS_C_RSC * LBS_C_SC * sizeof(VRec)           // vertex-record ring
-               + 8 * (1 + LBS_C_RSTAGES) + 64;                                         // mbarriers
+               + (size_t)lbs_c_rstages(tiles) * LBS_C_RSC * LBS_C_SC * sizeof(VRec)    // vertex-record ring
+               + 8 * (1 + lbs_c_rstages(tiles)) + 64;                                  // mbarriers
     }
 
     __device__ __forceinline__ void named_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
@@ -1297,10 +1295,11 @@ namespace pcl
         int32_t       n_tiles, Vp, n_sc, pitch, prow, vsplit;
     };
 
-    template<bool NT>
+    template<bool NT, int LBS_C_TILES>
     __global__ void __launch_bounds__(LBS_C_THREADS, 1)
         lbs_cta_kernel(const LbsCParams par, const __grid_constant__ CUtensorMap tm_pos, const __grid_constant__ CUtensorMap tm_nt)
     {
+        constexpr int LBS_C_RSTAGES = lbs_c_rstages(LBS_C_TILES);
         extern __shared__ __align__(1024) unsigned char lsm[];
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int tile  = blockIdx.x / par.vsplit;

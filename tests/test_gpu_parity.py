@@ -359,6 +359,29 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     _check_skin(oracle, mesh, pal[::5], pos[::5], nt[::5])
 
 
+@pytest.mark.parametrize("J,variant", [(75, 3), (75, 2), (82, 3), (83, 2), (83, -1), (60, 3)])
+def test_lbs_crowd_kernels_on_mid_sized_skeletons(ctx, oracle, J, variant):
+    """The crowd kernels keep 32 palettes in shared memory: 3 staging tiles up to 63 bones, 2 up to 82 (TMA-store kernel),
+    the LSU-flush kernel up to 82 as well; beyond that they must refuse (explicit variant) or fall back (auto)."""
+    from piccolo_b200 import capi
+    sk = A.make_synthetic_skeleton(J, branching=2, seed=J)
+    cl, am = A.make_synthetic_clip(sk, 12, seed=J + 1)
+    mesh = A.make_player_mesh(sk, V=3000, seed=J)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    mh = ctx.upload_mesh(mesh, J)
+    N = 192
+    ph = np.random.default_rng(J).uniform(0, 1, N).astype(np.float32)
+    if J > 82 and variant in (2, 3):
+        with pytest.raises(capi.PclError) as e:
+            _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
+        assert e.value.code == -3
+        ctx.set_option("lbs_variant", -1)
+        return
+    pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
+    _check_skin(oracle, mesh, pal[::37], pos[::37], nt[::37])
+
+
 @pytest.mark.parametrize("variant", [0, 2, 3])
 def test_lbs_ring_slots_and_linearity(ctx, player_dev, player, variant):
     """Ring addressing + a size-independent property: skinning is linear in the vertex position stream."""
