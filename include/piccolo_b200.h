@@ -213,7 +213,8 @@ int pcl_renderbuf_download(pcl_renderbuf* r, int64_t draw, float* host /*[64][10
  * coalesced 128-bit stores, 1 = same with TMA bulk stores, 2 = lane-per-instance crowd kernel, 3 = crowd kernel with a
  * warp-specialised TMA store pipeline);
  * "lbs_warps" (0 = auto, 8, 12: resident warps per SM of the crowd kernel); "lbs_vsplit" (0 = auto);
- * "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only).
+ * "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only); "lbs_cta_tile" (0 = auto, 32, 16, 8: instances per
+ * CTA of variant 3 - auto takes the largest whose palettes fit in shared memory: 32 up to 82 bones, 16 up to ~165, 8 up to ~340).
  * PCL_ERR_INVALID for unknown keys. */
 int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
 

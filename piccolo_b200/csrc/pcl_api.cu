@@ -47,8 +47,12 @@ namespace
         float * d_pos = nullptr, *d_nrm = nullptr, *d_tan = nullptr;
         int4*   d_idx = nullptr;
         float4* d_w   = nullptr;
-        VRec*   d_vrec = nullptr;     // lane = instance form: slot-stable influences, see lbs_inst_kernel
-        VRec*   d_vrec_cta = nullptr; // the same packed along lbs_cta_kernel's visiting order
+        VRec*   d_vrec = nullptr;        // lane = instance form: slot-stable influences, see lbs_inst_kernel
+        VRec*   d_vrec_cta[3] = {nullptr, nullptr, nullptr}; // the same packed along lbs_cta_kernel's visiting order for S = 1, 2, 4
+                                         // vertex streams per warp (built on first use: which S runs depends on the skeleton)
+        std::vector<float>  h_pos, h_nrm, h_tan; // gated, padded host copies the record streams are packed from
+        std::vector<int4>   h_idx;
+        std::vector<float4> h_w;
     };
 } // namespace
 
@@ -82,7 +86,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0;
     int          max_smem_optin = 0, sm_count = 0;
     std::map<const void*, size_t> smem_attr; // largest dynamic shared memory size already enabled per kernel
     std::vector<void*> host_allocs;           // pcl_host_alloc blocks still alive (released by pcl_destroy at the latest)
@@ -117,8 +121,8 @@ struct pcl_skinbuf
     long long capacity;
     int32_t   flags, V, Vp;
     float *   d_pos = nullptr, *d_nt = nullptr;
-    bool        has_tmaps = false; // tensor maps of the two streams for lbs_cta_kernel's TMA stores
-    CUtensorMap tm_pos, tm_nt;
+    bool        has_tmaps = false; // tensor maps of the two streams for lbs_cta_kernel's TMA stores, boxes of 32 / 16 / 8 instances
+    CUtensorMap tm_pos[3], tm_nt[3];
 };
 
 namespace
@@ -215,12 +219,80 @@ namespace
         }
     }
 
+    // Slot-stable packing of vertex v (or padding when v >= V): influences whose bone is already resident keep their
+    // slot, newcomers take free slots, unused slots keep the resident bone with weight 0; the mask says which slots
+    // differ from the previously VISITED record.
+    void pack_vrec(const MeshRec& m, VRec& r, size_t v, int cur[4], const VRec* prev)
+    {
+        auto  slot_of = [](const VRec& x, int sl) { return ((sl < 2 ? (x.i01 >> (16 * sl)) : (x.i23 >> (16 * (sl - 2)))) & 0xffffu); };
+        float slot_w[4] = {0.f, 0.f, 0.f, 0.f};
+        if (v < (size_t)m.V)
+        {
+            const int   src_i[4] = {m.h_idx[v].x, m.h_idx[v].y, m.h_idx[v].z, m.h_idx[v].w};
+            const float src_w[4] = {m.h_w[v].x, m.h_w[v].y, m.h_w[v].z, m.h_w[v].w};
+            bool        taken[4] = {false, false, false, false}, placed[4] = {false, false, false, false};
+            for (int k = 0; k < 4; k++)
+                if (src_w[k] != 0.f)
+                    for (int sl = 0; sl < 4; sl++)
+                        if (!taken[sl] && cur[sl] == src_i[k])
+                        {
+                            taken[sl] = true, placed[k] = true, slot_w[sl] = src_w[k];
+                            break;
+                        }
+            for (int k = 0; k < 4; k++)
+                if (src_w[k] != 0.f && !placed[k])
+                    for (int sl = 0; sl < 4; sl++)
+                        if (!taken[sl])
+                        {
+                            taken[sl] = true, cur[sl] = src_i[k], slot_w[sl] = src_w[k];
+                            break;
+                        }
+            r.px = m.h_pos[3 * v], r.py = m.h_pos[3 * v + 1], r.pz = m.h_pos[3 * v + 2];
+            r.nx = m.h_nrm[3 * v], r.ny = m.h_nrm[3 * v + 1], r.nz = m.h_nrm[3 * v + 2];
+            r.tx = m.h_tan[3 * v], r.ty = m.h_tan[3 * v + 1], r.tz = m.h_tan[3 * v + 2];
+        }
+        r.w0 = slot_w[0], r.w1 = slot_w[1], r.w2 = slot_w[2], r.w3 = slot_w[3];
+        r.i01  = (uint32_t)cur[0] * 3u | (((uint32_t)cur[1] * 3u) << 16);
+        r.i23  = (uint32_t)cur[2] * 3u | (((uint32_t)cur[3] * 3u) << 16);
+        r.mask = 0;
+        for (int sl = 0; sl < 4; sl++)
+            if (!prev || slot_of(r, sl) != slot_of(*prev, sl))
+                r.mask |= 1u << sl;
+    }
+
+    // lbs_cta_kernel's record stream for T = 32 / 16 / 8 instances per tile (S = 1 / 2 / 4 vertex streams per warp):
+    // 8 S interleaved visiting orders, sequence vw = vertices scv * s + 4 vw + {0..3}, s = 0, 1, ...
+    int ensure_vrec_cta(pcl_ctx* c, MeshRec& m, int T)
+    {
+        const int si = T == 32 ? 0 : (T == 16 ? 1 : 2);
+        if (m.d_vrec_cta[si])
+            return PCL_OK;
+        const size_t      scv  = (size_t)lbs_c_scv(T);
+        const size_t      n_sc = ((size_t)m.Vp + scv - 1) / scv;
+        const size_t      pad  = (size_t)lbs_c_rsc(T); // a record stage may overrun the last superchunk
+        std::vector<VRec> hvc((n_sc + pad) * scv);
+        std::memset(hvc.data(), 0, hvc.size() * sizeof(VRec));
+        for (size_t vw = 0; vw < scv / LBS_C_VPW; vw++)
+        {
+            int         cw[4] = {0, 0, 0, 0};
+            const VRec* prev  = nullptr;
+            for (size_t sc = 0; sc < n_sc + pad; sc++)
+                for (int j = 0; j < LBS_C_VPW; j++)
+                {
+                    const size_t v = sc * scv + vw * LBS_C_VPW + j;
+                    pack_vrec(m, hvc[v], v, cw, prev);
+                    prev = &hvc[v];
+                }
+        }
+        return upload(c, &m.d_vrec_cta[si], hvc);
+    }
+
     bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size(); }
 
     // 2-D tensor map over a skinned stream [capacity][row_floats], box = 32 rows x 32 floats (128 B), 128-byte swizzle.
     // The encoder lives in the driver; it is fetched through the runtime so that the library has no link-time
     // dependency on libcuda (it must load on machines without a GPU).
-    bool make_stream_tmap(CUtensorMap* tm, float* base, long long capacity, long long row_floats)
+    bool make_stream_tmap(CUtensorMap* tm, float* base, long long capacity, long long row_floats, unsigned box_rows)
     {
         typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                       const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -240,7 +312,7 @@ namespace
             return false;
         const cuuint64_t dims[2]    = {(cuuint64_t)row_floats, (cuuint64_t)capacity};
         const cuuint64_t strides[1] = {(cuuint64_t)row_floats * 4};
-        const cuuint32_t box[2]     = {32, 32};
+        const cuuint32_t box[2]     = {32, box_rows};
         const cuuint32_t estr[2]    = {1, 1};
         return encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -329,7 +401,7 @@ extern "C"
         for (auto& cl : c->clips)
             cudaFree(cl.d_blob);
         for (auto& m : c->meshes)
-            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec), cudaFree(m.d_vrec_cta);
+            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec), cudaFree(m.d_vrec_cta[0]), cudaFree(m.d_vrec_cta[1]), cudaFree(m.d_vrec_cta[2]);
         cudaFree(c->d_clips);
         for (void* p : c->host_allocs)
             cudaFreeHost(p);
@@ -412,6 +484,8 @@ extern "C"
             c->opt_lbs_vsplit = v;
         else if (k == "lbs_inst_tile" && v >= 0 && v <= 16)
             c->opt_lbs_inst_tile = v;
+        else if (k == "lbs_cta_tile" && (v == 0 || v == 8 || v == 16 || v == 32))
+            c->opt_lbs_cta_tile = v;
         else
             return fail(c, PCL_ERR_INVALID, "pcl_set_option: unknown key or bad value: " + k);
         return PCL_OK;
@@ -730,75 +804,23 @@ extern "C"
         // a bone that was already resident for the previously VISITED vertex keeps its slot; unused slots keep the
         // resident bone with weight 0 (an exact zero contribution).  The blend is then summed in slot order,
         // which differs from the shader's x,y,z,w order only by a permutation of the same four products.
-        //   hv  : visiting order 0,1,2,...                       (lbs_inst_kernel: a warp walks a contiguous run)
-        //   hvc : eight interleaved visiting orders, sequence w = vertices 32 s + 4 w + {0..3}, s = 0,1,...
-        //         (lbs_cta_kernel: warp w owns that slice of every superchunk)
-        const size_t      n_sc = ((size_t)m.Vp + LBS_C_SC - 1) / LBS_C_SC;
-        std::vector<VRec> hv((size_t)m.Vt + LBS_I_SCH * LBS_I_CHUNK); // tail padding: a record stage may overrun the last chunk
-        std::vector<VRec> hvc((n_sc + LBS_C_RSC) * LBS_C_SC);
-        std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
-        std::memset(hvc.data(), 0, hvc.size() * sizeof(VRec));
-        if (max_slot * 3 <= 0xffff)
-        {
-            auto slot_of = [](const VRec& r, int sl) { return ((sl < 2 ? (r.i01 >> (16 * sl)) : (r.i23 >> (16 * (sl - 2)))) & 0xffffu); };
-            // pack vertex v (or padding when v >= V) given the resident bones `cur` and the previously visited record
-            auto pack = [&](VRec& r, size_t v, int cur[4], const VRec* prev) {
-                float slot_w[4] = {0.f, 0.f, 0.f, 0.f};
-                if (v < (size_t)V)
-                {
-                    const int   src_i[4] = {hi[v].x, hi[v].y, hi[v].z, hi[v].w};
-                    const float src_w[4] = {hw[v].x, hw[v].y, hw[v].z, hw[v].w};
-                    bool        taken[4] = {false, false, false, false}, placed[4] = {false, false, false, false};
-                    for (int k = 0; k < 4; k++) // keep resident bones where they are
-                        if (src_w[k] != 0.f)
-                            for (int sl = 0; sl < 4; sl++)
-                                if (!taken[sl] && cur[sl] == src_i[k])
-                                {
-                                    taken[sl] = true, placed[k] = true, slot_w[sl] = src_w[k];
-                                    break;
-                                }
-                    for (int k = 0; k < 4; k++) // newcomers go to the free slots
-                        if (src_w[k] != 0.f && !placed[k])
-                            for (int sl = 0; sl < 4; sl++)
-                                if (!taken[sl])
-                                {
-                                    taken[sl] = true, cur[sl] = src_i[k], slot_w[sl] = src_w[k];
-                                    break;
-                                }
-                    r.px = hp[3 * v], r.py = hp[3 * v + 1], r.pz = hp[3 * v + 2];
-                    r.nx = hn[3 * v], r.ny = hn[3 * v + 1], r.nz = hn[3 * v + 2];
-                    r.tx = ht[3 * v], r.ty = ht[3 * v + 1], r.tz = ht[3 * v + 2];
-                }
-                r.w0 = slot_w[0], r.w1 = slot_w[1], r.w2 = slot_w[2], r.w3 = slot_w[3];
-                r.i01  = (uint32_t)cur[0] * 3u | (((uint32_t)cur[1] * 3u) << 16);
-                r.i23  = (uint32_t)cur[2] * 3u | (((uint32_t)cur[3] * 3u) << 16);
-                r.mask = 0;
-                for (int sl = 0; sl < 4; sl++)
-                    if (!prev || slot_of(r, sl) != slot_of(*prev, sl))
-                        r.mask |= 1u << sl;
-            };
-            int cur[4] = {0, 0, 0, 0};
-            for (size_t v = 0; v < hv.size(); v++)
-                pack(hv[v], v, cur, v ? &hv[v - 1] : nullptr);
-            for (int w = 0; w < LBS_C_WARPS; w++)
-            {
-                int         cw[4] = {0, 0, 0, 0};
-                const VRec* prev  = nullptr;
-                for (size_t sc = 0; sc < n_sc + LBS_C_RSC; sc++)
-                    for (int j = 0; j < LBS_C_VPW; j++)
-                    {
-                        const size_t v = sc * LBS_C_SC + (size_t)w * LBS_C_VPW + j;
-                        pack(hvc[v], v, cw, prev);
-                        prev = &hvc[v];
-                    }
-            }
-        }
+        // d_vrec: visiting order 0,1,2,... (lbs_inst_kernel: a warp walks a contiguous run); the interleaved streams of
+        // lbs_cta_kernel are packed by ensure_vrec_cta on first use.
         int rc;
         if ((rc = upload(c, &m.d_pos, hp)) || (rc = upload(c, &m.d_nrm, hn)) || (rc = upload(c, &m.d_tan, ht)) ||
             (rc = upload(c, &m.d_idx, hi)) || (rc = upload(c, &m.d_w, hw)))
             return rc;
-        if (max_slot * 3 <= 0xffff && ((rc = upload(c, &m.d_vrec, hv)) || (rc = upload(c, &m.d_vrec_cta, hvc))))
-            return rc;
+        m.h_pos = std::move(hp), m.h_nrm = std::move(hn), m.h_tan = std::move(ht), m.h_idx = std::move(hi), m.h_w = std::move(hw);
+        if (max_slot * 3 <= 0xffff)
+        {
+            std::vector<VRec> hv((size_t)m.Vt + LBS_I_SCH * LBS_I_CHUNK); // tail padding: a record stage may overrun the last chunk
+            std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
+            int cur[4] = {0, 0, 0, 0};
+            for (size_t v = 0; v < hv.size(); v++)
+                pack_vrec(m, hv[v], v, cur, v ? &hv[v - 1] : nullptr);
+            if ((rc = upload(c, &m.d_vrec, hv)))
+                return rc;
+        }
         c->meshes.push_back(m);
         *out = (pcl_mesh)c->meshes.size() - 1;
         return PCL_OK;
@@ -1069,10 +1091,15 @@ extern "C"
             (void)cudaGetLastError();
             return fail(c, PCL_ERR_OOM, std::string("pcl_skinbuf_create: ") + cudaGetErrorString(e));
         }
-        s->has_tmaps = make_stream_tmap(&s->tm_pos, s->d_pos, capacity, (long long)s->Vp * 3) &&
-                       (!s->d_nt || make_stream_tmap(&s->tm_nt, s->d_nt, capacity, (long long)s->Vp * 6));
-        if (!s->d_nt)
-            s->tm_nt = s->tm_pos;
+        s->has_tmaps = true;
+        for (int i = 0; i < 3; i++)
+        {
+            const unsigned rows = 32u >> i;
+            s->has_tmaps = s->has_tmaps && make_stream_tmap(&s->tm_pos[i], s->d_pos, capacity, (long long)s->Vp * 3, rows) &&
+                           (!s->d_nt || make_stream_tmap(&s->tm_nt[i], s->d_nt, capacity, (long long)s->Vp * 6, rows));
+            if (!s->d_nt)
+                s->tm_nt[i] = s->tm_pos[i];
+        }
         *out = s;
         return PCL_OK;
     }
@@ -1119,30 +1146,39 @@ extern "C"
             int          var    = c->opt_lbs_variant;
             if (var == 2 && !fits)
                 return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 2 needs 32 palettes in shared memory");
+            // lbs_cta_kernel: the largest instance tile (32, 16, 8) whose palettes leave room for two staging tiles
+            int cT = 0;
+            for (int cand = 32; cand >= 8 && !cT; cand >>= 1)
+                if ((c->opt_lbs_cta_tile == 0 || c->opt_lbs_cta_tile == cand) && lbs_c_smem_bytes(prow, nt, 2, cand) <= (size_t)c->max_smem_optin)
+                    cT = cand;
+            const bool fits3 = cT && m.max_slot * 3 <= 0xffff && out->has_tmaps;
             if (var < 0)
             {
-                const bool fits3 = m.d_vrec_cta && out->has_tmaps && lbs_c_smem_bytes(prow, nt, 2) <= (size_t)c->max_smem_optin;
                 // measured on the player mesh (tools/lbs_sweep.py): below ~200 instances the long per-CTA vertex walk of the
                 // crowd kernels (a ~35 us floor) loses to the lane-per-vertex kernel, which spreads over many more CTAs
                 var = (fits3 && count >= 160) ? 3 : ((fits && !fits3 && count >= 160) ? 2 : 0);
             }
             if (var == 3)
             {
-                const int    ctiles = lbs_c_smem_bytes(prow, nt, 3) <= (size_t)c->max_smem_optin ? 3 : 2;
-                const size_t smem_c = lbs_c_smem_bytes(prow, nt, ctiles);
-                if (!m.d_vrec_cta || !out->has_tmaps || smem_c > (size_t)c->max_smem_optin)
-                    return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 3 needs 32 palettes in shared memory and tensor maps");
-                const long long full = count / 32; // whole 32-instance tiles; a ragged remainder goes to lbs_inst_kernel below
+                if (!fits3)
+                    return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 3 needs 8 palettes in shared memory and tensor maps");
+                const int    ctiles = lbs_c_smem_bytes(prow, nt, 3, cT) <= (size_t)c->max_smem_optin ? 3 : 2;
+                const size_t smem_c = lbs_c_smem_bytes(prow, nt, ctiles, cT);
+                const int    ti     = cT == 32 ? 0 : (cT == 16 ? 1 : 2);
+                const long long full = count / cT; // whole tiles; a ragged remainder goes to lbs_inst_kernel / lbs_kernel below
                 if (full > 0)
                 {
+                    MeshRec& mm = c->meshes[mesh];
+                    { int rc__ = ensure_vrec_cta(c, mm, cT); if (rc__) return rc__; }
                     LbsCParams q {};
-                    q.vrec = m.d_vrec_cta, q.palette = b->d_palette;
+                    q.vrec = mm.d_vrec_cta[ti], q.palette = b->d_palette;
                     q.first = first, q.slot_first = slot_first, q.n_tiles = (int32_t)full;
-                    q.Vp = m.Vp, q.n_sc = (m.Vp + LBS_C_SC - 1) / LBS_C_SC, q.pitch = s.pitch, q.prow = prow;
+                    q.Vp = m.Vp, q.n_sc = (m.Vp + lbs_c_scv(cT) - 1) / lbs_c_scv(cT), q.pitch = s.pitch, q.prow = prow;
                     int vs = c->opt_lbs_vsplit;
                     if (vs == 0)
                     {
-                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_sc / 32)); // finer splits measured slower (palette reloads, pipeline fills)
+                        // at least 32 superchunks per CTA: finer splits measured slower (palette reloads, pipeline fills)
+                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_sc / 32));
                         double    best   = -1.0;
                         for (int cand = 1; cand <= max_vs; cand++)
                         {
@@ -1154,23 +1190,30 @@ extern "C"
                     }
                     q.vsplit = std::max(1, std::min(vs, q.n_sc));
                     const unsigned grid = (unsigned)(full * q.vsplit);
-#define PCL_LAUNCH_LBSC(NT_, T_)                                                                                            \
+#define PCL_LAUNCH_LBSC(NT_, TL_, T_)                                                                                        \
     {                                                                                                                       \
-        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<NT_, T_>, smem_c); if (rc__) return rc__; }                 \
-        lbs_cta_kernel<NT_, T_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos, out->tm_nt);                   \
+        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<NT_, TL_, T_>, smem_c); if (rc__) return rc__; }             \
+        lbs_cta_kernel<NT_, TL_, T_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos[ti], out->tm_nt[ti]);       \
     }
-                    if (nt && ctiles == 3) PCL_LAUNCH_LBSC(true, 3)
-                    else if (nt) PCL_LAUNCH_LBSC(true, 2)
-                    else if (ctiles == 3) PCL_LAUNCH_LBSC(false, 3)
-                    else PCL_LAUNCH_LBSC(false, 2)
+#define PCL_LAUNCH_LBSC_T(T_)                                                                                               \
+    {                                                                                                                       \
+        if (nt && ctiles == 3) PCL_LAUNCH_LBSC(true, 3, T_)                                                                 \
+        else if (nt) PCL_LAUNCH_LBSC(true, 2, T_)                                                                           \
+        else if (ctiles == 3) PCL_LAUNCH_LBSC(false, 3, T_)                                                                 \
+        else PCL_LAUNCH_LBSC(false, 2, T_)                                                                                  \
+    }
+                    if (cT == 32) PCL_LAUNCH_LBSC_T(32)
+                    else if (cT == 16) PCL_LAUNCH_LBSC_T(16)
+                    else PCL_LAUNCH_LBSC_T(8)
+#undef PCL_LAUNCH_LBSC_T
 #undef PCL_LAUNCH_LBSC
                     c->launches++;
                     PCL_CK(c, cudaGetLastError());
                 }
-                if (count == full * 32)
+                if (count == full * cT)
                     return PCL_OK;
-                first += full * 32, slot_first += full * 32, count -= full * 32;
-                var = 2;
+                first += full * cT, slot_first += full * cT, count -= full * cT;
+                var = fits ? 2 : 0;
             }
             if (var == 2)
             {

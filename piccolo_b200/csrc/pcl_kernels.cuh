@@ -1260,21 +1260,26 @@ namespace pcl
     // -------------------------------------------------------------------------------------------
     constexpr int LBS_C_WARPS   = 8;                       // compute warps
     constexpr int LBS_C_THREADS = (LBS_C_WARPS + 1) * 32;  // + 1 store / load warp
-    constexpr int LBS_C_SC      = 32;                      // vertices per superchunk
-    constexpr int LBS_C_VPW     = LBS_C_SC / LBS_C_WARPS;  // 4 vertices per warp per superchunk
-    constexpr int LBS_C_RSC     = 4;                       // superchunks per vertex-record stage
-    // staging tiles in flight between the compute warps and the TMA stores: 3 when the palettes leave room (J <= 63),
-    // else 2 (J <= 82); the vertex-record ring gets the stage the third tile gives up
+    constexpr int LBS_C_VPW     = 4;                       // consecutive vertices a (warp, stream) owns in every superchunk
+    constexpr int LBS_C_TILE_BYTES_POS = 3 * 32 * 128;     // per staging tile: 32 lanes x 4 vertices x 8 warps x 12 B
+    constexpr int LBS_C_TILE_BYTES_NT  = 6 * 32 * 128;
+    constexpr int LBS_C_RSTAGE_BYTES   = 8192;             // one vertex-record stage (128 records)
+    // A tile holds T = 32, 16 or 8 INSTANCES; a warp then carries S = 32 / T vertex streams side by side (lanes
+    // [st*T, st*T+T) = the T instances of stream st), which is what lets skeletons whose 32 palettes do not fit in shared
+    // memory (more than 82 bones) still use this kernel: 16 palettes fit up to ~165 bones, 8 up to ~340.
+    // Superchunk = 32 S vertices; "virtual warp" vw = warp * S + st owns vertices 4 vw .. 4 vw + 3 of it.
+    __host__ __device__ constexpr int lbs_c_scv(int T) { return 32 * (32 / T); }                  // vertices per superchunk
+    __host__ __device__ constexpr int lbs_c_rsc(int T) { return LBS_C_RSTAGE_BYTES / (lbs_c_scv(T) * 64); } // superchunks per record stage
+    // staging tiles in flight between the compute warps and the TMA stores: 3 when the palettes leave room, else 2;
+    // the vertex-record ring gets the stage the third tile gives up
     __host__ __device__ constexpr int lbs_c_rstages(int tiles) { return tiles >= 3 ? 2 : 3; }
-    constexpr int LBS_C_SUB     = 32 * 128;                // one swizzled sub-tile: 32 instances x 128 bytes
-    constexpr int LBS_C_POS_SUBS = 3, LBS_C_NT_SUBS = 6;   // 384 B and 768 B per instance and superchunk
 
-    __host__ __device__ inline size_t lbs_c_tile_bytes(bool nt) { return (size_t)(LBS_C_POS_SUBS + (nt ? LBS_C_NT_SUBS : 0)) * LBS_C_SUB; }
-    __host__ __device__ inline size_t lbs_c_smem_bytes(int prow, bool nt, int tiles)
+    __host__ __device__ inline size_t lbs_c_tile_bytes(bool nt) { return (size_t)LBS_C_TILE_BYTES_POS + (nt ? LBS_C_TILE_BYTES_NT : 0); }
+    __host__ __device__ inline size_t lbs_c_smem_bytes(int prow, bool nt, int tiles, int T)
     {
         return tiles * lbs_c_tile_bytes(nt)                                            // staging tiles (1024-byte aligned, first)
-               + (size_t)32 * prow * 16                                                // palettes
-               + (size_t)lbs_c_rstages(tiles) * LBS_C_RSC * LBS_C_SC * sizeof(VRec)    // vertex-record ring
+               + (size_t)T * prow * 16                                                 // palettes
+               + (size_t)lbs_c_rstages(tiles) * LBS_C_RSTAGE_BYTES                     // vertex-record ring
                + 8 * (1 + lbs_c_rstages(tiles)) + 64;                                  // mbarriers
     }
 
@@ -1289,28 +1294,33 @@ namespace pcl
 
     struct LbsCParams
     {
-        const VRec*   vrec;    // packed along the warp visiting order, padded to whole record stages
+        const VRec*   vrec;    // packed along the (warp, stream) visiting order for this T, padded to whole record stages
         const float4* palette; // [N][pitch][3]
         long long     first, slot_first;
         int32_t       n_tiles, Vp, n_sc, pitch, prow, vsplit;
     };
 
-    template<bool NT, int LBS_C_TILES>
+    template<bool NT, int LBS_C_TILES, int T>
     __global__ void __launch_bounds__(LBS_C_THREADS, 1)
         lbs_cta_kernel(const LbsCParams par, const __grid_constant__ CUtensorMap tm_pos, const __grid_constant__ CUtensorMap tm_nt)
     {
+        constexpr int S             = 32 / T;               // vertex streams per warp
+        constexpr int SCV           = lbs_c_scv(T);         // vertices per superchunk
+        constexpr int RSC           = lbs_c_rsc(T);         // superchunks per record stage
         constexpr int LBS_C_RSTAGES = lbs_c_rstages(LBS_C_TILES);
+        constexpr int SUB           = T * 128;              // one swizzled sub-tile: T instances x 128 bytes
+        constexpr int POS_SUBS = 3 * S, NT_SUBS = 6 * S;    // 384 S and 768 S bytes per instance and superchunk
         extern __shared__ __align__(1024) unsigned char lsm[];
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int tile  = blockIdx.x / par.vsplit;
         const int split = blockIdx.x - tile * par.vsplit;
-        const long long i0 = (long long)tile * 32;
+        const long long i0 = (long long)tile * T;
 
         const size_t   TILE  = lbs_c_tile_bytes(NT);
         unsigned char* tiles = lsm;
         float4*        pal_s = reinterpret_cast<float4*>(lsm + LBS_C_TILES * TILE);
-        VRec*          vring = reinterpret_cast<VRec*>(lsm + LBS_C_TILES * TILE + (size_t)32 * par.prow * 16);
-        uint64_t*      bars  = reinterpret_cast<uint64_t*>(vring + LBS_C_RSTAGES * LBS_C_RSC * LBS_C_SC);
+        VRec*          vring = reinterpret_cast<VRec*>(lsm + LBS_C_TILES * TILE + (size_t)T * par.prow * 16);
+        uint64_t*      bars  = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(vring) + LBS_C_RSTAGES * LBS_C_RSTAGE_BYTES);
         uint64_t*      rbar  = bars + 1;
 
         // this CTA's run of superchunks
@@ -1319,7 +1329,6 @@ namespace pcl
         if (s_lo >= s_hi)
             return;
         const int n_steps = s_hi - s_lo;
-        constexpr uint32_t RSTAGE_BYTES = LBS_C_RSC * LBS_C_SC * sizeof(VRec);
         // named barriers: 1 + b = tile b full (compute arrives, store warp syncs); 1 + TILES + b = tile b empty (store arrives, compute syncs)
 
         if (tid == 0)
@@ -1337,13 +1346,14 @@ namespace pcl
             if (lane == 0)
             {
                 const uint32_t row_bytes = (uint32_t)par.pitch * 48;
-                mbar_expect_tx(&bars[0], row_bytes * 32);
-                for (int i = 0; i < 32; i++)
+                mbar_expect_tx(&bars[0], row_bytes * T);
+                for (int i = 0; i < T; i++)
                     tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + i0 + i) * par.pitch * 3, row_bytes, &bars[0]);
-                for (int st = 0; st < LBS_C_RSTAGES && st * LBS_C_RSC < n_steps; st++)
+                for (int st = 0; st < LBS_C_RSTAGES && st * RSC < n_steps; st++)
                 {
-                    mbar_expect_tx(&rbar[st], RSTAGE_BYTES);
-                    tma_load(vring + st * LBS_C_RSC * LBS_C_SC, par.vrec + (size_t)(s_lo + st * LBS_C_RSC) * LBS_C_SC, RSTAGE_BYTES, &rbar[st]);
+                    mbar_expect_tx(&rbar[st], LBS_C_RSTAGE_BYTES);
+                    tma_load(reinterpret_cast<unsigned char*>(vring) + st * LBS_C_RSTAGE_BYTES, par.vrec + (size_t)(s_lo + st * RSC) * SCV,
+                             LBS_C_RSTAGE_BYTES, &rbar[st]);
                 }
             }
             const int row0 = (int)(par.slot_first + i0);
@@ -1351,21 +1361,25 @@ namespace pcl
             {
                 const int b = s % LBS_C_TILES;
                 named_sync(1 + b, LBS_C_THREADS); // all compute warps have written (and fenced) tile b
-                const int v0 = (s_lo + s) * LBS_C_SC;
-                if (lane < LBS_C_POS_SUBS)
-                    tma_store_2d(&tm_pos, v0 * 3 + lane * 32, row0, tiles + b * TILE + lane * LBS_C_SUB);
-                else if (NT && lane < LBS_C_POS_SUBS + LBS_C_NT_SUBS)
-                    tma_store_2d(&tm_nt, v0 * 6 + (lane - LBS_C_POS_SUBS) * 32, row0, tiles + b * TILE + lane * LBS_C_SUB);
+                const int v0 = (s_lo + s) * SCV;
+                for (int op = lane; op < POS_SUBS + (NT ? NT_SUBS : 0); op += 32)
+                {
+                    if (op < POS_SUBS)
+                        tma_store_2d(&tm_pos, v0 * 3 + op * 32, row0, tiles + b * TILE + op * SUB);
+                    else
+                        tma_store_2d(&tm_nt, v0 * 6 + (op - POS_SUBS) * 32, row0, tiles + b * TILE + op * SUB);
+                }
                 tma_commit();
                 // the records of superchunk s are consumed by everybody: refill the stage when its last superchunk is done
-                if (lane == 0 && (s % LBS_C_RSC) == LBS_C_RSC - 1)
+                if (lane == 0 && (s % RSC) == RSC - 1)
                 {
-                    const int nxt = s / LBS_C_RSC + LBS_C_RSTAGES; // stage index to fetch into the slot just freed
-                    if (nxt * LBS_C_RSC < n_steps)
+                    const int nxt = s / RSC + LBS_C_RSTAGES; // stage index to fetch into the slot just freed
+                    if (nxt * RSC < n_steps)
                     {
-                        const int st = (s / LBS_C_RSC) % LBS_C_RSTAGES;
-                        mbar_expect_tx(&rbar[st], RSTAGE_BYTES);
-                        tma_load(vring + st * LBS_C_RSC * LBS_C_SC, par.vrec + (size_t)(s_lo + nxt * LBS_C_RSC) * LBS_C_SC, RSTAGE_BYTES, &rbar[st]);
+                        const int st = (s / RSC) % LBS_C_RSTAGES;
+                        mbar_expect_tx(&rbar[st], LBS_C_RSTAGE_BYTES);
+                        tma_load(reinterpret_cast<unsigned char*>(vring) + st * LBS_C_RSTAGE_BYTES, par.vrec + (size_t)(s_lo + nxt * RSC) * SCV,
+                                 LBS_C_RSTAGE_BYTES, &rbar[st]);
                     }
                 }
                 if (s >= LBS_C_TILES - 1)
@@ -1381,35 +1395,37 @@ namespace pcl
 
         // ---------------- compute warps ----------------
         mbar_wait(&bars[0], 0);
-        const float4* prow = pal_s + (size_t)lane * par.prow;
+        const int     row  = lane % T;          // instance within the tile
+        const int     vw   = warp * S + lane / T; // virtual warp: which 4 vertices of every superchunk
+        const float4* prow = pal_s + (size_t)row * par.prow;
         float4 m[4][3];
         {
-            const uint4 d = __ldg(reinterpret_cast<const uint4*>(&par.vrec[(size_t)s_lo * LBS_C_SC + warp * LBS_C_VPW].w3));
+            const uint4 d = __ldg(reinterpret_cast<const uint4*>(&par.vrec[(size_t)s_lo * SCV + vw * LBS_C_VPW].w3));
             lbs_i_load(m[0], prow, d.y & 0xffffu), lbs_i_load(m[1], prow, d.y >> 16);
             lbs_i_load(m[2], prow, d.z & 0xffffu), lbs_i_load(m[3], prow, d.z >> 16);
         }
-        // swizzled staging offsets of this lane (row = instance) for the 16-byte units this warp owns:
-        // positions: units 3w..3w+2 of 24, normal+tangent: units 6w..6w+5 of 48; unit U -> sub-tile U >> 3, chunk (U & 7) ^ (row & 7)
+        // swizzled staging offsets of this lane for the 16-byte units its virtual warp owns: positions: units 3 vw .. 3 vw + 2,
+        // normal+tangent: units 6 vw .. 6 vw + 5; unit U -> sub-tile U >> 3, chunk (U & 7) ^ (row & 7)
         uint32_t off_p[3], off_n[6];
 #pragma unroll
         for (int q = 0; q < 3; q++)
         {
-            const int U = warp * 3 + q;
-            off_p[q]    = (U >> 3) * LBS_C_SUB + lane * 128 + (((U & 7) ^ (lane & 7)) << 4);
+            const int U = vw * 3 + q;
+            off_p[q]    = (U >> 3) * SUB + row * 128 + (((U & 7) ^ (row & 7)) << 4);
         }
 #pragma unroll
         for (int q = 0; q < 6; q++)
         {
-            const int U = warp * 6 + q;
-            off_n[q]    = (LBS_C_POS_SUBS + (U >> 3)) * LBS_C_SUB + lane * 128 + (((U & 7) ^ (lane & 7)) << 4);
+            const int U = vw * 6 + q;
+            off_n[q]    = (POS_SUBS + (U >> 3)) * SUB + row * 128 + (((U & 7) ^ (row & 7)) << 4);
         }
         for (int s = 0; s < n_steps; s++)
         {
             const int b = s % LBS_C_TILES;
-            const int ridx = s / LBS_C_RSC, rsub = s - ridx * LBS_C_RSC, rst = ridx % LBS_C_RSTAGES;
+            const int ridx = s / RSC, rsub = s - ridx * RSC, rst = ridx % LBS_C_RSTAGES;
             if (rsub == 0)
                 mbar_wait(&rbar[rst], (uint32_t)(ridx / LBS_C_RSTAGES) & 1);
-            const VRec* vr = vring + (rst * LBS_C_RSC + rsub) * LBS_C_SC + warp * LBS_C_VPW;
+            const VRec* vr = reinterpret_cast<const VRec*>(reinterpret_cast<const unsigned char*>(vring) + rst * LBS_C_RSTAGE_BYTES) + rsub * SCV + vw * LBS_C_VPW;
             float4 op[3], on[6];
             float* opf = reinterpret_cast<float*>(op);
             float* onf = reinterpret_cast<float*>(on);

@@ -273,10 +273,19 @@ def test_pose_is_independent_of_batch_composition(ctx, player_dev):
 # ------------------------------------------------------------------------------------------------
 # skinning
 # ------------------------------------------------------------------------------------------------
-def _skin(ctx, skel, clip, mesh_h, V, N, ph, flags, variant, vsplit=0, inst_tile=0, K=1):
+def _skin(ctx, skel, clip, mesh_h, V, N, ph, flags, variant, vsplit=0, inst_tile=0, K=1, cta_tile=0):
     ctx.set_option("lbs_variant", variant)
     ctx.set_option("lbs_vsplit", vsplit)
     ctx.set_option("lbs_inst_tile", inst_tile)
+    ctx.set_option("lbs_cta_tile", cta_tile)
+    try:
+        return _skin_body(ctx, skel, clip, mesh_h, V, N, ph, flags)
+    finally:
+        ctx.set_option("lbs_variant", -1), ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_inst_tile", 0)
+        ctx.set_option("lbs_cta_tile", 0)
+
+
+def _skin_body(ctx, skel, clip, mesh_h, V, N, ph, flags):
     b = ctx.batch(skel, N, 1)
     b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph)
     b.pose()
@@ -285,7 +294,6 @@ def _skin(ctx, skel, clip, mesh_h, V, N, ph, flags, variant, vsplit=0, inst_tile
     pos, nt = sb.download()
     pal = b.download_palette()
     sb.close(), b.close()
-    ctx.set_option("lbs_variant", -1), ctx.set_option("lbs_vsplit", 0), ctx.set_option("lbs_inst_tile", 0)
     return pos, nt, pal
 
 
@@ -338,8 +346,9 @@ def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
 
 @pytest.mark.parametrize("variant", [0, 1, -1, 2, 3])
 def test_lbs_config5_synthetic(ctx, oracle, variant):
-    """257 palette slots: 32 palettes do not fit in shared memory, so auto (-1) must fall back to the lane-per-vertex
-    kernel and forcing the crowd kernel (2) must be refused, not silently mis-skinned."""
+    """257 palette slots: 32 palettes do not fit in shared memory.  The TMA-store crowd kernel (3) drops to 8 instances per
+    CTA (4 vertex streams per warp) and handles the ragged 3-instance remainder with the lane-per-vertex kernel; forcing the
+    LSU crowd kernel (2), which only exists for 32 palettes, must be refused, not silently mis-skinned."""
     from piccolo_b200 import capi
     sk = A.make_synthetic_skeleton(256)
     cl, am = A.make_synthetic_clip(sk, 32)
@@ -347,9 +356,9 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     skel = ctx.upload_skeleton(sk)
     clip = ctx.upload_clip(skel, cl, am)
     mh = ctx.upload_mesh(mesh, 256)
-    N = 40
+    N = 43
     ph = np.linspace(0.05, 0.95, N, dtype=np.float32)
-    if variant >= 2:
+    if variant == 2:
         with pytest.raises(capi.PclError) as e:
             _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
         assert e.value.code == -3
@@ -359,10 +368,12 @@ def test_lbs_config5_synthetic(ctx, oracle, variant):
     _check_skin(oracle, mesh, pal[::5], pos[::5], nt[::5])
 
 
-@pytest.mark.parametrize("J,variant", [(75, 3), (75, 2), (82, 3), (83, 2), (83, -1), (60, 3)])
+@pytest.mark.parametrize("J,variant", [(75, 3), (75, 2), (82, 3), (83, 2), (83, -1), (60, 3), (83, 3), (120, 3), (165, 3),
+                                       (166, 3), (200, -1), (340, 3), (400, 3)])
 def test_lbs_crowd_kernels_on_mid_sized_skeletons(ctx, oracle, J, variant):
-    """The crowd kernels keep 32 palettes in shared memory: 3 staging tiles up to 63 bones, 2 up to 82 (TMA-store kernel),
-    the LSU-flush kernel up to 82 as well; beyond that they must refuse (explicit variant) or fall back (auto)."""
+    """The TMA-store crowd kernel keeps 32 palettes in shared memory up to 82 bones (3 staging tiles up to 63), 16 palettes
+    up to ~165 bones and 8 up to ~340; the LSU-flush kernel exists for 32 palettes only.  Beyond their limits they must
+    refuse (explicit variant) or fall back (auto)."""
     from piccolo_b200 import capi
     sk = A.make_synthetic_skeleton(J, branching=2, seed=J)
     cl, am = A.make_synthetic_clip(sk, 12, seed=J + 1)
@@ -370,9 +381,9 @@ def test_lbs_crowd_kernels_on_mid_sized_skeletons(ctx, oracle, J, variant):
     skel = ctx.upload_skeleton(sk)
     clip = ctx.upload_clip(skel, cl, am)
     mh = ctx.upload_mesh(mesh, J)
-    N = 192
+    N = 192 + (J % 7)  # ragged against 32 / 16 / 8 for some J
     ph = np.random.default_rng(J).uniform(0, 1, N).astype(np.float32)
-    if J > 82 and variant in (2, 3):
+    if (J > 82 and variant == 2) or J >= 400:
         with pytest.raises(capi.PclError) as e:
             _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
         assert e.value.code == -3
@@ -380,6 +391,28 @@ def test_lbs_crowd_kernels_on_mid_sized_skeletons(ctx, oracle, J, variant):
         return
     pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
     _check_skin(oracle, mesh, pal[::37], pos[::37], nt[::37])
+
+
+@pytest.mark.parametrize("cta_tile", [16, 8])
+@pytest.mark.parametrize("flags_nt", [True, False])
+def test_lbs_tma_store_kernel_smaller_instance_tiles_on_player(ctx, player_dev, oracle, player, cta_tile, flags_nt):
+    """16 and 8 instances per CTA (2 and 4 vertex streams per warp) forced on the player, whose 32 palettes would fit:
+    same results as the oracle, and the 32-instance form's up to the order of the four influence products (the slot packing
+    follows each form's own visiting order)."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    mesh = A.make_player_mesh(player[0], V=5000, seed=7)
+    mh = ctx.upload_mesh(mesh, 58)
+    N = 208  # a multiple of 16 and 8: no remainder kernel involved
+    ph = np.random.default_rng(cta_tile).uniform(0, 1, N).astype(np.float32)
+    flags = capi.PCL_SKIN_POS_NRM_TAN if flags_nt else capi.PCL_SKIN_POS
+    pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, flags, 3, cta_tile=cta_tile)
+    _check_skin(oracle, mesh, pal[::41], pos[::41], None if nt is None else nt[::41])
+    pos32, nt32, _ = _skin(ctx, skel, clip, mh, mesh.V, N - 16, ph[:N - 16], flags, 3, cta_tile=32)
+    assert np.abs(pos[:N - 16] - pos32).max() <= 4e-6 * max(1.0, float(np.abs(pos32).max()))
+    if flags_nt:
+        ok = np.isfinite(nt32)
+        assert np.array_equal(ok, np.isfinite(nt[:N - 16])) and np.abs(nt[:N - 16][ok] - nt32[ok]).max() <= 4e-6
 
 
 @pytest.mark.parametrize("variant", [0, 2, 3])

@@ -17,6 +17,7 @@ ap.add_argument("--steps", type=int, default=10)
 ap.add_argument("--inst-tile", type=int, default=0)
 ap.add_argument("--vsplit", type=int, default=0)
 ap.add_argument("--warps", type=int, default=0)
+ap.add_argument("--cta-tile", type=int, default=0)
 args = ap.parse_args()
 peak = 6540.2
 try:
@@ -34,6 +35,7 @@ ctx.set_option("lbs_variant", args.variant)
 ctx.set_option("lbs_inst_tile", args.inst_tile)
 ctx.set_option("lbs_vsplit", args.vsplit)
 ctx.set_option("lbs_warps", args.warps)
+ctx.set_option("lbs_cta_tile", args.cta_tile)
 for flags, O in ((capi.PCL_SKIN_POS, 12), (capi.PCL_SKIN_POS_NRM_TAN, 36)):
     for N in args.n:
         b = ctx.batch(skel, N, 1)
