@@ -86,9 +86,9 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1;
+    int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
     int          max_smem_optin = 0, sm_count = 0;
-    std::map<const void*, size_t> smem_attr; // largest dynamic shared memory size already enabled per kernel
     std::vector<void*> host_allocs;           // pcl_host_alloc blocks still alive (released by pcl_destroy at the latest)
 };
 
@@ -104,6 +104,8 @@ struct pcl_batch
     float*    d_derived = nullptr;
     float4*   d_export  = nullptr;
     long long export_cap = 0; // instances
+    int32_t*  d_order = nullptr;  // [N] frame-coherent visiting order of the pose kernel (allocated on first use)
+    int32_t*  d_ohist = nullptr;  // [2][ORDER_MAX_BUCKETS] histogram (kept zero between launches) and scatter cursors
     bool      posed = false;
 };
 
@@ -318,9 +320,14 @@ namespace
                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
     }
 
+    // The attribute belongs to the (device, kernel) pair, not to a context: two contexts on one device share it, and setting it
+    // is not monotone (a second context asking for less would shrink what the first one relies on).  One process-wide record.
     int ensure_smem(pcl_ctx* c, const void* func, size_t bytes)
     {
-        size_t& have = c->smem_attr[func];
+        static std::mutex                                        mu;
+        static std::map<std::pair<int, const void*>, size_t>     have_all;
+        std::lock_guard<std::mutex>                              lk(mu);
+        size_t& have = have_all[std::make_pair(c->device, func)];
         if (bytes > have)
         {
             PCL_CK(c, cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
@@ -476,6 +483,8 @@ extern "C"
             c->opt_pose_wpb = v;
         else if (k == "pose_generic" && (v == 0 || v == 1))
             c->opt_pose_generic = v;
+        else if (k == "pose_sort" && v >= -1 && v <= 1)
+            c->opt_pose_sort = v;
         else if (k == "lbs_variant" && v >= -1 && v <= 3)
             c->opt_lbs_variant = v;
         else if (k == "lbs_warps" && (v == 0 || v == 8 || v == 12))
@@ -713,6 +722,8 @@ extern "C"
         ch.rec.simple         = simple ? 1 : 0;
         ch.rec.keys_step      = simple ? (const float4*)d2 : nullptr;
         ch.rec.hic_step       = simple ? (const int32_t*)(d2 + up16(skb)) : nullptr;
+        ch.rec.bucket_base    = c->n_buckets;
+        c->n_buckets += total_frame; // lo = floor(phase * (total_frame - 1)) is one of total_frame values
         sk.n_clips++;
         sk.n_simple += simple ? 1 : 0;
         c->clips.push_back(ch);
@@ -770,6 +781,8 @@ extern "C"
         PCL_CK(c, cudaSetDevice(c->device));
         MeshRec m;
         m.V = V, m.Vp = (V + 7) & ~7, m.Vt = (V + LBS_VT - 1) / LBS_VT * LBS_VT, m.max_slot = max_slot;
+        // (Vp is also the row pitch of the skin buffers.  tools/tma_store_peak.cu shows the store stream alone gaining 3 % when the
+        // pitch is not a multiple of 4 KiB - 16 416 instead of 16 384 vertices - but the full kernel did not move, so no padding.)
         std::vector<float>  hp((size_t)m.Vt * 3, 0.f), hn((size_t)m.Vt * 3, 0.f), ht((size_t)m.Vt * 3, 0.f);
         std::vector<int4>   hi(m.Vt, make_int4(0, 0, 0, 0));
         std::vector<float4> hw(m.Vt, make_float4(0, 0, 0, 0));
@@ -813,7 +826,7 @@ extern "C"
         m.h_pos = std::move(hp), m.h_nrm = std::move(hn), m.h_tan = std::move(ht), m.h_idx = std::move(hi), m.h_w = std::move(hw);
         if (max_slot * 3 <= 0xffff)
         {
-            std::vector<VRec> hv((size_t)m.Vt + LBS_I_SCH * LBS_I_CHUNK); // tail padding: a record stage may overrun the last chunk
+            std::vector<VRec> hv((size_t)std::max(m.Vt, m.Vp) + LBS_I_SCH * LBS_I_CHUNK); // tail padding: a record stage may overrun the last chunk
             std::memset(hv.data(), 0, hv.size() * sizeof(VRec));
             int cur[4] = {0, 0, 0, 0};
             for (size_t v = 0; v < hv.size(); v++)
@@ -864,7 +877,7 @@ extern "C"
         cudaSetDevice(b->ctx->device);
         cudaStreamSynchronize(b->ctx->compute), cudaStreamSynchronize(b->ctx->copy);
         cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len);
-        cudaFree(b->d_palette), cudaFree(b->d_derived), cudaFree(b->d_export);
+        cudaFree(b->d_palette), cudaFree(b->d_derived), cudaFree(b->d_export), cudaFree(b->d_order), cudaFree(b->d_ohist);
         delete b;
         return PCL_OK;
     }
@@ -1015,12 +1028,44 @@ extern "C"
                 own.ctx = c, own.skel = b->skel;
             }
         }
+        // frame-coherent visiting order: worth three small launches (~45 us) once the crowd is large; measured with
+        // tools/pose_bench.py: 1 M instances 1.63 -> 1.51 ms (K = 1), 2.43 -> 2.18 ms (K = 2); 100 k instances, K = 2: 0.27 -> 0.30 ms
+        bool sorted = simple && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
+                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= 262144));
+        if (sorted)
+        {
+            if (!b->d_order)
+            {
+                PCL_CK(c, cudaMalloc((void**)&b->d_order, (size_t)b->N * 4));
+                PCL_CK(c, cudaMalloc((void**)&b->d_ohist, (size_t)2 * ORDER_MAX_BUCKETS * 4));
+                PCL_CK(c, cudaMemsetAsync(b->d_ohist, 0, (size_t)2 * ORDER_MAX_BUCKETS * 4, c->compute));
+            }
+            OrderParams q {};
+            q.clips = c->d_clips, q.clip_ids = b->d_clip_ids, q.phase = b->d_phase, q.clip_len = b->d_len;
+            q.hist = b->d_ohist, q.cursor = b->d_ohist + ORDER_MAX_BUCKETS, q.order = b->d_order;
+            q.N = b->N, q.nb = c->n_buckets, q.dt = dt, q.advance = advance;
+            q.levels = (b->K >= 2 && (long long)c->n_buckets * c->n_buckets <= ORDER_MAX_BUCKETS) ? 2 : 1;
+            q.nbk    = q.levels == 2 ? c->n_buckets * c->n_buckets : c->n_buckets;
+            const unsigned ogrid = (unsigned)((b->N + ORDER_THREADS * ORDER_PER_THREAD - 1) / (ORDER_THREADS * ORDER_PER_THREAD));
+            order_hist_kernel<<<ogrid, ORDER_THREADS, (size_t)q.nbk * 4, c->compute>>>(q);
+            order_scan_kernel<<<1, 1024, 0, c->compute>>>(q);
+            { int rc__ = ensure_smem(c, (const void*)order_scatter_kernel, (size_t)q.nbk * 8); if (rc__) return rc__; }
+            order_scatter_kernel<<<ogrid, ORDER_THREADS, (size_t)q.nbk * 8, c->compute>>>(q);
+            c->launches += 3;
+            PCL_CK(c, cudaGetLastError());
+            p.order = b->d_order;
+        }
 #define PCL_LAUNCH_POSE(KK)                                                                                                 \
     {                                                                                                                       \
-        if (simple)                                                                                                         \
+        if (simple && sorted)                                                                                               \
         {                                                                                                                   \
-            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK>, smem); if (rc__) return rc__; } \
-            pose_simple_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                \
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, true>, smem); if (rc__) return rc__; }         \
+            pose_simple_kernel<KK, true><<<grid, wpb * 32, smem, c->compute>>>(p);                                          \
+        }                                                                                                                   \
+        else if (simple)                                                                                                    \
+        {                                                                                                                   \
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, false>, smem); if (rc__) return rc__; }        \
+            pose_simple_kernel<KK, false><<<grid, wpb * 32, smem, c->compute>>>(p);                                         \
         }                                                                                                                   \
         else                                                                                                                \
         {                                                                                                                   \

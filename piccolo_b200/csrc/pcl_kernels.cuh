@@ -45,6 +45,8 @@ namespace pcl
         // channel drives, so a key's address depends only on (step, frame) - no dependent loads on the hot path
         const float4*  keys_step;  // [Jp][F][3]
         const int32_t* hic_step;   // [Jp]  hi_clamp of the step's channel (>= 0), or -F for an identity track (clamp F-1)
+        int32_t        bucket_base; // first (clip, frame) bucket of this clip in the context-wide numbering (order_* kernels)
+        int32_t        pad_[3];
     };
 
     struct PoseParams
@@ -59,6 +61,7 @@ namespace pcl
         const int32_t* mask_ids; // [K][N]  (-1 = all enabled)
         float4*        palette;  // [N][pitch][3]
         float*         derived;  // [N][J][10] or nullptr
+        const int32_t* order;    // [N] visiting order (frame-coherent, see order_* kernels) or nullptr = 0, 1, 2, ...
         long long      N;
         int32_t        J, pitch, nslot, n_steps_padded;
         float          dt;
@@ -372,7 +375,11 @@ namespace pcl
     // few spilled registers: measured at N = 1 M, K = 1: 8 warps/SM 2.38 ms, 12 warps 2.10 ms, 16 warps 1.78 ms.
     constexpr int POSE_S_THREADS = 128;
     __host__ __device__ constexpr int pose_s_minblocks(int K) { return K == 1 ? 4 : (K == 2 ? 3 : 2); }
-    template<int K>
+    // SORTED: lane l of warp w works on instance order[32 w + l] instead of 32 w + l.  The order groups instances by the
+    // (clip, frame) their phase falls in, so the 32 key gathers of a warp collapse onto one or two addresses (broadcast)
+    // instead of up to 32 cache lines; every instance is still computed by exactly the same instruction sequence and
+    // written to its own palette row, so the result does not depend on the order.
+    template<int K, bool SORTED>
     __global__ void __launch_bounds__(POSE_S_THREADS, pose_s_minblocks(K)) pose_simple_kernel(const PoseParams par)
     {
         extern __shared__ __align__(16) float smem[];
@@ -382,8 +389,10 @@ namespace pcl
         const long long inst0 = wglob * 32;
         if (inst0 >= par.N)
             return;
-        const long long inst   = min(inst0 + lane, par.N - 1);
         const bool      active = (inst0 + lane) < par.N;
+        const long long visit  = min(inst0 + lane, par.N - 1);
+        const long long inst   = SORTED ? (long long)__ldg(par.order + visit) : visit;
+        const int       inst32 = (int)inst;
         const int       ni     = (int)min(32LL, par.N - inst0);
         float*          slots  = smem + (size_t)wib * pose_smem_floats_per_warp(par.nslot);
         float*          stage  = slots + (size_t)par.nslot * 10 * 32;
@@ -421,6 +430,7 @@ namespace pcl
         float4*   g_f0 = par.palette + (size_t)(inst0 + fa) * par.pitch * 3 + fb;
         float4*   g_f2 = par.palette + (size_t)(inst0 + fa + fc4) * par.pitch * 3 + 8 + fd;
         const size_t rowstep = (size_t)par.pitch * 3 * 4; // float4 per 4 instances
+        const size_t rowsz   = (size_t)par.pitch * 3;     // float4 per instance
 
         TRS prev;
         prev.p = make_float3(0, 0, 0), prev.q = Quat {1, 0, 0, 0}, prev.s = make_float3(1, 1, 1);
@@ -579,9 +589,22 @@ namespace pcl
 #pragma unroll
                 for (int gq = 0; gq < 4; gq++)
                 {
-                    g_f0[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW);
-                    g_f0[off + (2 * gq + 1) * rowstep] = *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW);
-                    g_f2[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW);
+                    if (SORTED)
+                    {
+                        // staging row r belongs to the instance lane r works on
+                        const size_t i0 = (size_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8);
+                        const size_t i1 = (size_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8 + 4);
+                        const size_t i2 = (size_t)__shfl_sync(0xffffffffu, inst32, fa + fc4 + gq * 8);
+                        par.palette[i0 * rowsz + off + fb]     = *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW);
+                        par.palette[i1 * rowsz + off + fb]     = *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW);
+                        par.palette[i2 * rowsz + off + 8 + fd] = *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW);
+                    }
+                    else
+                    {
+                        g_f0[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW);
+                        g_f0[off + (2 * gq + 1) * rowstep] = *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW);
+                        g_f2[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW);
+                    }
                 }
             }
             else
@@ -594,12 +617,129 @@ namespace pcl
                     const int rm = f % (POSE_G * 3);
                     const int g  = rm / 3;
                     const int s  = s0 + g;
+                    const size_t irow = SORTED ? (size_t)__shfl_sync(0xffffffffu, inst32, il & 31) : (size_t)(inst0 + il);
                     if (s < par.J && il < ni)
-                        par.palette[((size_t)(inst0 + il) * par.pitch + c_steps[s].joint + 1) * 3 + (rm - g * 3)] =
+                        par.palette[(irow * par.pitch + c_steps[s].joint + 1) * 3 + (rm - g * 3)] =
                             *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
                 }
             }
             __syncwarp();
+        }
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // frame-coherent visiting order (counting sort, three launches): histogram of the (clip, frame) buckets the
+    // instances' phases fall in -> exclusive scan -> scatter of the instance numbers.  Which instance lands where
+    // inside a bucket is decided by atomics and may differ from run to run; the pose does not depend on it.
+    // With two or more clips per instance and few enough buckets the key is the pair (bucket of clip 0, bucket of clip 1).
+    // -------------------------------------------------------------------------------------------
+    constexpr int ORDER_MAX_BUCKETS = 8192; // 32 KB of shared-memory counters per block
+    constexpr int ORDER_THREADS     = 512;
+    constexpr int ORDER_PER_THREAD  = 16;
+    struct OrderParams
+    {
+        const ClipRec* clips;
+        const int32_t* clip_ids;
+        const float*   phase;
+        const float*   clip_len;
+        int32_t*       hist;   // [nbk] zero on entry of order_hist_kernel; order_scan_kernel re-zeroes it
+        int32_t*       cursor; // [nbk]
+        int32_t*       order;  // [N]
+        long long      N;
+        int32_t        nb, nbk, levels, advance;
+        float          dt;
+    };
+    __device__ __forceinline__ int order_key(const OrderParams& p, long long i)
+    {
+        int key = 0;
+        for (int k = 0; k < p.levels; k++)
+        {
+            const size_t   o  = (size_t)k * p.N + i;
+            const ClipRec* cr = p.clips + __ldg(p.clip_ids + o);
+            const int      tf = __ldg(&cr->total_frame_m1);
+            float          ph = __ldg(p.phase + o);
+            if (p.advance == 2 || (p.advance == 1 && k == 0))
+            {
+                ph += p.dt / __ldg(p.clip_len + o); // what the pose kernel is about to do (animation_component.cpp:19-21)
+                ph -= floorf(ph);
+            }
+            const int lo = min(max((int)floorf(ph * (float)tf), 0), tf);
+            key          = key * p.nb + __ldg(&cr->bucket_base) + lo;
+        }
+        return key;
+    }
+    __global__ void __launch_bounds__(ORDER_THREADS) order_hist_kernel(const OrderParams p)
+    {
+        extern __shared__ int32_t osm[];
+        for (int b = threadIdx.x; b < p.nbk; b += ORDER_THREADS)
+            osm[b] = 0;
+        __syncthreads();
+        const long long base = (long long)blockIdx.x * (ORDER_THREADS * ORDER_PER_THREAD);
+#pragma unroll 4
+        for (int j = 0; j < ORDER_PER_THREAD; j++)
+        {
+            const long long i = base + (long long)j * ORDER_THREADS + threadIdx.x;
+            if (i < p.N)
+                atomicAdd(&osm[order_key(p, i)], 1);
+        }
+        __syncthreads();
+        for (int b = threadIdx.x; b < p.nbk; b += ORDER_THREADS)
+            if (osm[b])
+                atomicAdd(&p.hist[b], osm[b]);
+    }
+    __global__ void __launch_bounds__(1024) order_scan_kernel(const OrderParams p)
+    {
+        __shared__ int32_t part[1024];
+        const int per = (p.nbk + 1023) / 1024;
+        const int lo = threadIdx.x * per, hi = min(p.nbk, lo + per);
+        int sum = 0;
+        for (int b = lo; b < hi; b++)
+            sum += p.hist[b];
+        part[threadIdx.x] = sum;
+        __syncthreads();
+        for (int d = 1; d < 1024; d <<= 1) // Hillis-Steele inclusive scan of the 1024 partial sums
+        {
+            const int v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+            __syncthreads();
+            part[threadIdx.x] += v;
+            __syncthreads();
+        }
+        int run = part[threadIdx.x] - sum;
+        for (int b = lo; b < hi; b++)
+        {
+            const int h = p.hist[b];
+            p.cursor[b] = run, p.hist[b] = 0;
+            run += h;
+        }
+    }
+    __global__ void __launch_bounds__(ORDER_THREADS) order_scatter_kernel(const OrderParams p)
+    {
+        extern __shared__ int32_t osm[]; // [nbk] counters, then [nbk] this block's first position in each bucket
+        int32_t* cnt = osm;
+        int32_t* pos = osm + p.nbk;
+        for (int b = threadIdx.x; b < p.nbk; b += ORDER_THREADS)
+            cnt[b] = 0;
+        __syncthreads();
+        const long long base = (long long)blockIdx.x * (ORDER_THREADS * ORDER_PER_THREAD);
+        int keys[ORDER_PER_THREAD], rank[ORDER_PER_THREAD];
+#pragma unroll
+        for (int j = 0; j < ORDER_PER_THREAD; j++)
+        {
+            const long long i = base + (long long)j * ORDER_THREADS + threadIdx.x;
+            keys[j] = i < p.N ? order_key(p, i) : -1;
+            rank[j] = keys[j] >= 0 ? atomicAdd(&cnt[keys[j]], 1) : 0;
+        }
+        __syncthreads();
+        for (int b = threadIdx.x; b < p.nbk; b += ORDER_THREADS)
+            if (cnt[b])
+                pos[b] = atomicAdd(&p.cursor[b], cnt[b]);
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < ORDER_PER_THREAD; j++)
+        {
+            const long long i = base + (long long)j * ORDER_THREADS + threadIdx.x;
+            if (keys[j] >= 0)
+                p.order[pos[keys[j]] + rank[j]] = (int32_t)i;
         }
     }
 
@@ -1492,6 +1632,9 @@ namespace pcl
                 for (int q = 0; q < 6; q++)
                     *reinterpret_cast<float4*>(tb + off_n[q]) = on[q];
             }
+            // (handing the tile over one vertex later, so that the proxy fence finds the column stores already drained, was
+            // measured 3 % slower: the tensor stores start later and the compute warps wait longer for a free tile)
+            // (one proxy fence in the store warp after the barrier instead of one per compute warp: +0.8 %, not adopted)
             fence_async_smem();
             named_arrive(1 + b, LBS_C_THREADS);
         }

@@ -36,6 +36,11 @@ def player_dev(ctx, player):
     return skel, clip
 
 
+def capi_mod():
+    from piccolo_b200 import capi
+    return capi
+
+
 def assert_mats_close(got, ref, tol=MAT_TOL):
     got, ref = got.reshape(-1, 16), ref.reshape(-1, 16)
     scale = np.maximum(1.0, np.abs(ref).max(axis=1))
@@ -246,6 +251,62 @@ def test_pose_wide_and_deep_hierarchies(ctx, oracle):
         ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((100, 1), np.int32), ph)
         assert_mats_close(mats, ref, tol=5e-5)  # 63-deep chain of random rotations
         assert np.array_equal(ctx.skeleton_parents(skel), np.array([-1] + [parent_of(i) for i in range(1, 64)]))
+
+
+@pytest.mark.parametrize("K", [1, 2, 3])
+@pytest.mark.parametrize("N", [1, 37, 4097, 70001])
+def test_pose_frame_coherent_order_changes_nothing(ctx, player, K, N):
+    """pose_sort: the step-ordered kernel visits the instances grouped by (clip, frame) bucket (counting sort on the device).
+    Palettes, derived transforms and advanced phases must be bit-identical to the unsorted launch, for pose and for tick
+    (where the order is computed from the phase the kernel is about to advance to)."""
+    sk, cl, am, mk = player
+    c2 = capi_mod().Context(0)  # own context: own clip table, so bucket numbering starts at 0 and stays small enough for pair keys
+    try:
+        skel = c2.upload_skeleton(sk)
+        ids = np.asarray([c2.upload_clip(skel, c, am) for c in (cl, A.make_variant_clip(cl, 17, seed=3), A.make_variant_clip(cl, 29, seed=4))], np.int32)
+        rng = np.random.default_rng(N + K)
+        pick = ids[rng.integers(0, 3, (N, K))]
+        ph = rng.uniform(0, 1, (N, K)).astype(np.float32)
+        ph[0, 0] = 0.0
+        ph[-1, 0] = np.float32(1.0) - np.float32(2.0 ** -24)
+        w = rng.uniform(0.1, 1, (N, K)).astype(np.float32)
+        ln = rng.uniform(0.5, 2.0, (N, K)).astype(np.float32)
+        out = {}
+        for mode in (0, 1):
+            c2.set_option("pose_sort", mode)
+            b = c2.batch(skel, N, K)
+            b.set(clip_ids=pick, phase=ph, weight=w, clip_len=ln)
+            b.keep_derived(True)
+            b.pose()
+            r = [b.download_palette(), b.download_derived()]
+            b.tick(1.0 / 30.0, capi_mod().PCL_ADVANCE_ALL)
+            b.tick(0.0421, capi_mod().PCL_ADVANCE_FIRST_ONLY)
+            r += [b.download_palette(), b.phases()]
+            out[mode] = r
+            b.close()
+        for x, y in zip(out[0], out[1]):
+            assert np.array_equal(x, y)
+    finally:
+        c2.close()
+
+
+def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, player):
+    """The opt-in shared-memory size is a property of (device, kernel), not of a context: a second context that needs less
+    must not shrink what the first one launches with (regression: 'invalid argument' on the first context's next pose)."""
+    skel, clip = player_dev
+    sk, cl, am, mk = player
+    N = 50000
+    ph = np.linspace(0, 0.999, N, dtype=np.float32)
+    a = gpu_pose(ctx, skel, np.full((N, 1), clip), ph)          # 4 warps per block
+    c2 = capi_mod().Context(0)
+    try:
+        s2 = c2.upload_skeleton(sk)
+        k2 = c2.upload_clip(s2, cl, am)
+        small = gpu_pose(c2, s2, np.full((40, 1), k2), ph[:40])  # 1 warp per block: a quarter of the shared memory
+    finally:
+        c2.close()
+    b = gpu_pose(ctx, skel, np.full((N, 1), clip), ph)
+    assert np.array_equal(a, b) and np.array_equal(a[:40], small)
 
 
 def test_pose_is_independent_of_batch_composition(ctx, player_dev):
