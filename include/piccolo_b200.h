@@ -207,6 +207,37 @@ int pcl_batch_export_render(pcl_batch* b, int64_t first, int64_t count, pcl_rend
 int pcl_renderbuf_dev(pcl_renderbuf* r, const void** dptr);
 int pcl_renderbuf_download(pcl_renderbuf* r, int64_t draw, float* host /*[64][1024][16]*/);
 
+/* ---- palette pool: the crowd's joint palettes gathered on ONE GPU -----------------------
+ * The reference hands every animated object's AnimationResult to one consumer, the render system of the one GPU that
+ * draws the frame (MeshComponent::tick, function/framework/component/mesh/mesh_component.cpp:68-100 ->
+ * RenderSystem::processSwapData, function/render/render_system.cpp:302-310 -> the per-draw joint buffer,
+ * function/render/passes/main_camera_pass.cpp:2284-2298).  With the crowd sharded over GPUs that consumer needs the
+ * palettes of all shards.  A pool is one device buffer [capacity][pitch][3] float4 (the compact palette layout) on the
+ * consumer's GPU; a batch attached to rows [first, first + N) of it makes the pose kernel write its palettes THERE -
+ * straight over NVLink when the pool lives on another GPU (peer-to-peer stores from the kernel, no staging copy and no
+ * collective).  Same process, other context: pass the owner's pool (peer access is enabled on attach).  Other process:
+ * pcl_pool_export on the owner, carry the PCL_POOL_HANDLE_BYTES to the producer (torch.distributed broadcast, a pipe ...),
+ * pcl_pool_open there.  Ordering across GPUs is the caller's: producers pcl_sync() and signal (a barrier) before the
+ * consumer calls pcl_batch_adopt_palettes on its own batch attached to the same rows and skins / exports from it.
+ * A pool must outlive the batches attached to it (pcl_pool_destroy refuses while any is attached). */
+typedef struct pcl_pool pcl_pool;
+#define PCL_POOL_HANDLE_BYTES 64
+int pcl_pool_create(pcl_ctx* ctx, pcl_skel skel, int64_t capacity, pcl_pool** out);
+int pcl_pool_export(pcl_pool* pool, void* handle /*[PCL_POOL_HANDLE_BYTES]*/);
+int pcl_pool_open(pcl_ctx* ctx, pcl_skel skel, int64_t capacity, const void* handle, pcl_pool** out);
+int pcl_pool_destroy(pcl_pool* pool);
+/* The batch's own palette buffer is released; its palettes live at pool rows [first, first + N) from now on. */
+int pcl_batch_attach_pool(pcl_batch* b, pcl_pool* pool, int64_t first);
+/* Consumer side: declare the attached rows valid (they were written by other batches / other GPUs). */
+int pcl_batch_adopt_palettes(pcl_batch* b);
+/* The other way to fill a pool: the batch keeps its own palette buffer and this call copies it to pool rows
+ * [first, first + N) with the copy engine (cudaMemcpyAsync on the context's copy stream, ordered after the last pose;
+ * completes by pcl_sync).  Measured on two B200s (tools/pool_gather_check.py, 1 M remote instances = 2.88 GB): pose +
+ * push 6.6 ms (1.5 ms pose, then the copy engine at ~570 GB/s, which can overlap the next tick), pose with the pool
+ * attached 8.1 ms (the kernel's 128- and 64-byte store runs reach 355 GB/s over NVLink); 100 k remote instances: 0.72 vs
+ * 0.83 ms.  Attach when a second palette copy in HBM or the extra hop is unwelcome, push for the largest crowds. */
+int pcl_batch_push_to_pool(pcl_batch* b, pcl_pool* pool, int64_t first);
+
 /* ---- tuning knobs (benchmarks / tests; defaults are chosen by the library) --------------------- */
 /* key: "pose_warps_per_block" (0 = auto, 1,2,4,8); "pose_generic" (1 = always use the channel-ordered pose kernel,
  * 0 = use the step-ordered one whenever the skeleton's clips allow it); "pose_sort" (-1 = auto, 0 = never, 1 = always: let

@@ -68,7 +68,15 @@ SIGNATURES = {
     "pcl_renderbuf_dev": (C.c_int, [_vp, C.POINTER(_vp)]),
     "pcl_renderbuf_download": (C.c_int, [_vp, _i64, _fp]),
     "pcl_batch_download_palette_static": (C.c_int, [_vp, _i64, _i64, _fp]),
+    "pcl_pool_create": (C.c_int, [_vp, C.c_int32, _i64, C.POINTER(_vp)]),
+    "pcl_pool_export": (C.c_int, [_vp, C.c_char_p]),
+    "pcl_pool_open": (C.c_int, [_vp, C.c_int32, _i64, C.c_char_p, C.POINTER(_vp)]),
+    "pcl_pool_destroy": (C.c_int, [_vp]),
+    "pcl_batch_attach_pool": (C.c_int, [_vp, _vp, _i64]),
+    "pcl_batch_adopt_palettes": (C.c_int, [_vp]),
+    "pcl_batch_push_to_pool": (C.c_int, [_vp, _vp, _i64]),
 }
+PCL_POOL_HANDLE_BYTES = 64
 
 _lib = None
 
@@ -201,6 +209,9 @@ class Context:
     def batch(self, skel: int, N: int, K: int = 1) -> "Batch":
         return Batch(self, skel, N, K)
 
+    def pool(self, skel: int, capacity: int, handle: bytes = None) -> "Pool":
+        return Pool(self, skel, capacity, handle)
+
     def skinbuf(self, mesh: int, V: int, capacity: int, flags: int = PCL_SKIN_POS_NRM_TAN) -> "SkinBuf":
         return SkinBuf(self, mesh, V, capacity, flags)
 
@@ -243,6 +254,15 @@ class Batch:
     def tick(self, dt, mode=PCL_ADVANCE_FIRST_ONLY):
         self.ctx._ck(self.ctx.L.pcl_batch_tick(self.h, C.c_float(dt), mode))
 
+    def attach_pool(self, pool: "Pool", first: int = 0):
+        self.ctx._ck(self.ctx.L.pcl_batch_attach_pool(self.h, pool.h, int(first)))
+
+    def push_to_pool(self, pool: "Pool", first: int = 0):
+        self.ctx._ck(self.ctx.L.pcl_batch_push_to_pool(self.h, pool.h, int(first)))
+
+    def adopt_palettes(self):
+        self.ctx._ck(self.ctx.L.pcl_batch_adopt_palettes(self.h))
+
     def keep_derived(self, enable=True):
         self.ctx._ck(self.ctx.L.pcl_batch_keep_derived(self.h, int(enable)))
 
@@ -280,6 +300,30 @@ class Batch:
         p, pitch, fps = _vp(), C.c_int32(), C.c_int32()
         self.ctx._ck(self.ctx.L.pcl_batch_palette_dev(self.h, C.byref(p), C.byref(pitch), C.byref(fps)))
         return p.value, pitch.value, fps.value
+
+
+class Pool:
+    """Palette pool (pcl_pool_*): the palettes of several batches - on this or on other GPUs - gathered in one device buffer."""
+
+    def __init__(self, ctx: Context, skel: int, capacity: int, handle: bytes = None):
+        self.ctx, self.skel, self.capacity = ctx, skel, int(capacity)
+        h = _vp()
+        if handle is None:
+            ctx._ck(ctx.L.pcl_pool_create(ctx.h, skel, self.capacity, C.byref(h)))
+        else:
+            assert len(handle) == PCL_POOL_HANDLE_BYTES
+            ctx._ck(ctx.L.pcl_pool_open(ctx.h, skel, self.capacity, bytes(handle), C.byref(h)))
+        self.h = h
+
+    def export(self) -> bytes:
+        buf = C.create_string_buffer(PCL_POOL_HANDLE_BYTES)
+        self.ctx._ck(self.ctx.L.pcl_pool_export(self.h, buf))
+        return buf.raw
+
+    def close(self):
+        if self.h:
+            self.ctx._ck(self.ctx.L.pcl_pool_destroy(self.h))
+            self.h = None
 
 
 class SkinBuf:

@@ -104,9 +104,20 @@ struct pcl_batch
     float*    d_derived = nullptr;
     float4*   d_export  = nullptr;
     long long export_cap = 0; // instances
+    pcl_pool* pool = nullptr;     // d_palette points into this pool (not owned) when attached
     int32_t*  d_order = nullptr;  // [N] frame-coherent visiting order of the pose kernel (allocated on first use)
     int32_t*  d_ohist = nullptr;  // [2][ORDER_MAX_BUCKETS] histogram (kept zero between launches) and scatter cursors
     bool      posed = false;
+};
+
+struct pcl_pool
+{
+    pcl_ctx*  ctx;          // the context that created or opened it
+    long long capacity;     // instance rows
+    int32_t   pitch, J;     // slots per row / bones of the skeleton the rows are laid out for
+    float4*   base = nullptr;
+    bool      owner = true; // cudaMalloc'ed here; false: mapped from an IPC handle
+    int       attached = 0;
 };
 
 struct pcl_renderbuf
@@ -877,8 +888,146 @@ extern "C"
         cudaSetDevice(b->ctx->device);
         cudaStreamSynchronize(b->ctx->compute), cudaStreamSynchronize(b->ctx->copy);
         cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len);
-        cudaFree(b->d_palette), cudaFree(b->d_derived), cudaFree(b->d_export), cudaFree(b->d_order), cudaFree(b->d_ohist);
+        if (b->pool)
+            b->pool->attached--;
+        else
+            cudaFree(b->d_palette);
+        cudaFree(b->d_derived), cudaFree(b->d_export), cudaFree(b->d_order), cudaFree(b->d_ohist);
         delete b;
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // palette pool
+    // ------------------------------------------------------------------------------------------
+    static_assert(sizeof(cudaIpcMemHandle_t) == PCL_POOL_HANDLE_BYTES, "PCL_POOL_HANDLE_BYTES must match cudaIpcMemHandle_t");
+
+    int pcl_pool_create(pcl_ctx* c, pcl_skel skel, int64_t capacity, pcl_pool** out)
+    {
+        if (!valid_skel(c, skel) || !out || capacity < 1)
+            return fail(c, PCL_ERR_INVALID, "pcl_pool_create: bad argument");
+        PCL_CK(c, cudaSetDevice(c->device));
+        const SkelRec& s = c->skels[skel];
+        pcl_pool*      p = new pcl_pool();
+        p->ctx = c, p->capacity = capacity, p->pitch = s.pitch, p->J = s.J, p->owner = true;
+        const size_t bytes = (size_t)capacity * s.pitch * 48;
+        cudaError_t  e     = cudaMalloc((void**)&p->base, bytes);
+        if (e == cudaSuccess)
+            e = cudaMemset(p->base, 0, bytes);
+        if (e != cudaSuccess)
+        {
+            cudaFree(p->base);
+            delete p;
+            return fail(c, PCL_ERR_CUDA, std::string("pcl_pool_create: ") + cudaGetErrorString(e));
+        }
+        *out = p;
+        return PCL_OK;
+    }
+    int pcl_pool_export(pcl_pool* p, void* handle)
+    {
+        if (!p || !handle)
+            return PCL_ERR_INVALID;
+        pcl_ctx* c = p->ctx;
+        if (!p->owner)
+            return fail(c, PCL_ERR_INVALID, "pcl_pool_export: only the pool's owner can export it");
+        PCL_CK(c, cudaSetDevice(c->device));
+        cudaIpcMemHandle_t h;
+        PCL_CK(c, cudaIpcGetMemHandle(&h, p->base));
+        std::memcpy(handle, &h, sizeof(h));
+        return PCL_OK;
+    }
+    int pcl_pool_open(pcl_ctx* c, pcl_skel skel, int64_t capacity, const void* handle, pcl_pool** out)
+    {
+        if (!valid_skel(c, skel) || !out || !handle || capacity < 1)
+            return fail(c, PCL_ERR_INVALID, "pcl_pool_open: bad argument");
+        PCL_CK(c, cudaSetDevice(c->device));
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, sizeof(h));
+        void* base = nullptr;
+        PCL_CK(c, cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess)); // maps the owner's buffer, enabling peer access if it is another GPU
+        const SkelRec& s = c->skels[skel];
+        pcl_pool*      p = new pcl_pool();
+        p->ctx = c, p->capacity = capacity, p->pitch = s.pitch, p->J = s.J, p->owner = false, p->base = (float4*)base;
+        *out = p;
+        return PCL_OK;
+    }
+    int pcl_pool_destroy(pcl_pool* p)
+    {
+        if (!p)
+            return PCL_ERR_INVALID;
+        pcl_ctx* c = p->ctx;
+        if (p->attached > 0)
+            return fail(c, PCL_ERR_INVALID, "pcl_pool_destroy: batches are still attached to the pool");
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaDeviceSynchronize());
+        if (p->owner)
+            cudaFree(p->base);
+        else
+            cudaIpcCloseMemHandle(p->base);
+        delete p;
+        return PCL_OK;
+    }
+    int pcl_batch_attach_pool(pcl_batch* b, pcl_pool* p, int64_t first)
+    {
+        if (!b || !p)
+            return PCL_ERR_INVALID;
+        pcl_ctx*       c = b->ctx;
+        const SkelRec& s = c->skels[b->skel];
+        if (b->pool)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_attach_pool: the batch is already attached to a pool");
+        if (p->pitch != s.pitch || p->J != s.J)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_attach_pool: the pool was laid out for a skeleton with another bone count");
+        if (first < 0 || first + b->N > p->capacity)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_attach_pool: rows outside the pool");
+        PCL_CK(c, cudaSetDevice(c->device));
+        if (p->ctx->device != c->device) // same process, pool on another GPU: the pose kernel will store to it over NVLink / PCIe
+        {
+            int can = 0;
+            PCL_CK(c, cudaDeviceCanAccessPeer(&can, c->device, p->ctx->device));
+            if (!can)
+                return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_attach_pool: no peer access between the batch's GPU and the pool's GPU");
+            cudaError_t e = cudaDeviceEnablePeerAccess(p->ctx->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return fail(c, PCL_ERR_CUDA, std::string("pcl_batch_attach_pool: ") + cudaGetErrorString(e));
+            (void)cudaGetLastError();
+        }
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        PCL_CK(c, cudaStreamSynchronize(c->copy));
+        cudaFree(b->d_palette);
+        b->d_palette = p->base + (size_t)first * s.pitch * 3;
+        b->pool      = p;
+        b->posed     = false;
+        p->attached++;
+        return PCL_OK;
+    }
+    int pcl_batch_push_to_pool(pcl_batch* b, pcl_pool* p, int64_t first)
+    {
+        if (!b || !p)
+            return PCL_ERR_INVALID;
+        pcl_ctx*       c = b->ctx;
+        const SkelRec& s = c->skels[b->skel];
+        if (b->pool)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_push_to_pool: the batch is attached to a pool (its palettes are already there)");
+        if (!b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_push_to_pool: pcl_batch_pose / pcl_batch_tick has not run");
+        if (p->pitch != s.pitch || p->J != s.J)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_push_to_pool: the pool was laid out for a skeleton with another bone count");
+        if (first < 0 || first + b->N > p->capacity)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_push_to_pool: rows outside the pool");
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamWaitEvent(c->copy, c->ev_pose, 0));
+        PCL_CK(c, cudaMemcpyAsync(p->base + (size_t)first * s.pitch * 3, b->d_palette, (size_t)b->N * s.pitch * 48, cudaMemcpyDefault, c->copy));
+        PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy));
+        c->copy_pending = true; // the next pose must not overwrite the palette while the copy engine reads it
+        return PCL_OK;
+    }
+    int pcl_batch_adopt_palettes(pcl_batch* b)
+    {
+        if (!b)
+            return PCL_ERR_INVALID;
+        if (!b->pool)
+            return fail(b->ctx, PCL_ERR_INVALID, "pcl_batch_adopt_palettes: the batch is not attached to a pool");
+        b->posed = true;
         return PCL_OK;
     }
 
@@ -1030,8 +1179,11 @@ extern "C"
         }
         // frame-coherent visiting order: worth three small launches (~45 us) once the crowd is large; measured with
         // tools/pose_bench.py: 1 M instances 1.63 -> 1.51 ms (K = 1), 2.43 -> 2.18 ms (K = 2); 100 k instances, K = 2: 0.27 -> 0.30 ms
+        // (not when the palettes go to another GPU's pool: rows visited in random order over gigabytes of peer memory ran at
+        // 69 GB/s against 350 GB/s in instance order, tools/pool_gather_check.py on two B200s)
+        const bool remote = b->pool && (!b->pool->owner || b->pool->ctx->device != c->device);
         bool sorted = simple && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
-                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= 262144));
+                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= 262144 && !remote));
         if (sorted)
         {
             if (!b->d_order)

@@ -20,6 +20,22 @@ def env_rank():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
 
 
+def open_gathered_pool(group: "RankGroup", ctx, skel: int, n_total: int, consumer: int = 0):
+    """one palette pool of n_total rows on rank `consumer`'s GPU, opened on every other rank through CUDA
+    IPC.  Each rank then attaches its shard's batch at `shard_range(n_total, world, rank)[0]`, so that the pose kernel stores
+    its palettes straight into the consumer's memory over NVLink; torch.distributed only carries the 64-byte handle."""
+    from . import capi
+    if group.rank == consumer:
+        pool = ctx.pool(skel, n_total)
+        handle = pool.export()
+    else:
+        pool, handle = None, b"\0" * capi.PCL_POOL_HANDLE_BYTES
+    handle = group.broadcast_bytes(handle, capi.PCL_POOL_HANDLE_BYTES, src=consumer)
+    if pool is None:
+        pool = ctx.pool(skel, n_total, handle)
+    return pool
+
+
 class RankGroup:
     """Thin wrapper: barrier + max/sum over ranks; degenerates to a no-op for a single process."""
 
@@ -58,6 +74,19 @@ class RankGroup:
 
     def sum(self, x: float) -> float:
         return self._reduce(x, "SUM")
+
+    def broadcast_bytes(self, payload: bytes, nbytes: int, src: int = 0) -> bytes:
+        """`payload` (exactly nbytes long) of rank `src` on every rank - e.g. a palette pool's IPC handle."""
+        if self.dist is None:
+            return bytes(payload)
+        import torch
+        dev = self.device if self.device is not None else "cpu"
+        t = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        if self.rank == src:
+            assert len(payload) == nbytes
+            t.copy_(torch.frombuffer(bytearray(payload), dtype=torch.uint8))
+        self.dist.broadcast(t, src=src)
+        return bytes(t.cpu().numpy().tobytes())
 
     def close(self):
         if self.dist is not None:

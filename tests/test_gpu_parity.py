@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 from piccolo_b200 import assets as A
-from conftest import GOLDEN
+from conftest import GOLDEN, ROOT
 
 pytestmark = pytest.mark.gpu
 
@@ -647,3 +647,93 @@ def test_upload_errors(ctx, player):
     with pytest.raises(capi.PclError):
         b.download_palette()  # nothing posed yet
     b.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# palette pool: palettes of several batches gathered in one buffer
+# ------------------------------------------------------------------------------------------------
+def test_palette_pool_gathers_shards_for_one_consumer(ctx, player_dev, player, oracle):
+    """Two producer batches (the shards of a crowd) pose straight into one pool; a consumer batch attached to all rows adopts
+    them and downloads / skins exactly what one big batch produces.  On one GPU this exercises everything but the IPC mapping
+    (tools/pool_gather_check.py does that under torchrun on two GPUs)."""
+    from piccolo_b200 import capi
+    from piccolo_b200.sharding import shard_range
+    skel, clip = player_dev
+    N = 777
+    ph = np.random.default_rng(5).uniform(0, 1, N).astype(np.float32)
+    whole = ctx.batch(skel, N, 1)
+    whole.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph)
+    whole.pose()
+    ref = whole.download_palette()
+    mesh = A.make_player_mesh(player[0], V=2000, seed=3)
+    mh = ctx.upload_mesh(mesh, 58)
+    sb = ctx.skinbuf(mh, mesh.V, N, capi.PCL_SKIN_POS_NRM_TAN)
+    whole.skin(mh, sb)
+    ref_pos, ref_nt = sb.download()
+
+    pool = ctx.pool(skel, N)
+    shards = []
+    for r in range(2):
+        first, count = shard_range(N, 2, r)
+        b = ctx.batch(skel, count, 1)
+        b.attach_pool(pool, first)
+        b.set(clip_ids=np.full((count, 1), clip, np.int32), phase=ph[first:first + count])
+        b.pose()
+        assert np.array_equal(b.download_palette(), ref[first:first + count])  # a producer can still read its own rows
+        shards.append(b)
+    ctx.sync()
+    consumer = ctx.batch(skel, N, 1)
+    consumer.attach_pool(pool, 0)
+    with pytest.raises(capi.PclError):
+        consumer.download_palette()  # nothing adopted yet
+    consumer.adopt_palettes()
+    assert np.array_equal(consumer.download_palette(), ref)
+    consumer.skin(mh, sb)
+    pos, nt = sb.download()
+    assert np.array_equal(pos, ref_pos) and np.array_equal(nt, ref_nt, equal_nan=True)
+    # the copy-engine way of filling the same rows: an unattached batch pushes its palettes
+    pool2 = ctx.pool(skel, N + 3)
+    whole.push_to_pool(pool2, 3)
+    ctx.sync()
+    view = ctx.batch(skel, N, 1)
+    view.attach_pool(pool2, 3)
+    view.adopt_palettes()
+    assert np.array_equal(view.download_palette(), ref)
+    view.close()
+    pool2.close()
+    with pytest.raises(capi.PclError):
+        shards[0].push_to_pool(pool, 0)         # attached batches have nothing to push
+    # misuse is refused, not undefined
+    with pytest.raises(capi.PclError):
+        consumer.attach_pool(pool, 0)           # already attached
+    with pytest.raises(capi.PclError):
+        pool.close()                            # batches still attached
+    late = ctx.batch(skel, 10, 1)
+    with pytest.raises(capi.PclError):
+        late.attach_pool(pool, N - 5)           # rows outside the pool
+    other = ctx.upload_skeleton(A.make_synthetic_skeleton(20))
+    wrong = ctx.batch(other, 4, 1)
+    with pytest.raises(capi.PclError):
+        wrong.attach_pool(pool, 0)              # another skeleton's row layout
+    for b in shards + [consumer, late, wrong, whole]:
+        b.close()
+    sb.close()
+    pool.close()
+
+
+def test_palette_pool_across_two_gpus_under_torchrun(tmp_path):
+    """The real thing: rank 1's pose kernel stores its shard's palettes into rank 0's memory over NVLink (CUDA IPC mapping);
+    needs two GPUs, so the single-GPU round-end run skips it (run by hand with `gpurun --gpus 2`)."""
+    import socket, subprocess, sys, json
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tools", "pool_gather_check.py"), "--instances", "20000"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["identical"] is True and line["world"] == 2

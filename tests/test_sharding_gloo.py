@@ -43,6 +43,8 @@ WORKER = textwrap.dedent("""
     elapsed = time.perf_counter() - t0 + 0.01 * g.rank          # rank 1 is made the slow one
     g.barrier()
     worst, total = g.max(elapsed), g.sum(float(count))
+    handle = g.broadcast_bytes(bytes(range(64)) if g.rank == 0 else bytes(64), 64, src=0)   # how a palette pool's IPC handle travels
+    assert handle == bytes(range(64))
     np.save(os.path.join(%r, "shard%%d.npy" %% g.rank), mats)
     if g.rank == 0:
         print(json.dumps({"world": g.world, "total": total, "worst": worst, "mine": elapsed}))
