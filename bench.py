@@ -175,7 +175,7 @@ def other_configs(ctx, capi, sk, cl, am, skel, clip0, peak):
     ms = time_it(lambda: b.skin(m5, sb5), 10)
     gb = (n * (mesh5.V * 36 + 257 * 48) + mesh5.V * 68) / ms / 1e6
     out["config5_256j_50kv_lbs_N512"] = {"ms": round(ms, 4), "vertices_per_s": round(n * mesh5.V / ms * 1e3), "GBps": round(gb, 1), "frac": round(gb / peak, 4),
-                                         "note": "random 4-bone bindings (worst case for bone reuse); lane-per-vertex kernel"}
+                                         "note": "random 4-bone bindings (worst case for bone reuse); lbs_cta_kernel with 8-instance tiles (257 palette slots)"}
     sb5.close(), b.close()
     return out
 
@@ -280,7 +280,7 @@ def run_ours(args):
     per_launch = np.mean([lbs_algorithmic_bytes(n, mesh.V, sk.J, 36) for _, n in chunks])
     achieved = per_launch / (lbs_ms * 1e-3) / 1e9
     pose_bytes = N * (2 * 12 + 60 * 48)
-    roofline = {"bound": "hbm", "kernel": {None: "lbs_cta_kernel<NT=1>", -1: "lbs_cta_kernel<NT=1>", 3: "lbs_cta_kernel<NT=1>", 2: "lbs_inst_kernel<NT=1>"}.get(args.lbs_variant, "lbs_kernel<NT=1>"), "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": {None: "lbs_cta_kernel<NT=1,TILES=3,T=32>", -1: "lbs_cta_kernel<NT=1,TILES=3,T=32>", 3: "lbs_cta_kernel<NT=1,TILES=3,T=32>", 2: "lbs_inst_kernel<NT=1>"}.get(args.lbs_variant, "lbs_kernel<NT=1>"), "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(per_launch), "launch_ms": round(lbs_ms, 4),
                 "frac_of_nominal_8000": round(achieved / 8000.0, 4),
