@@ -153,8 +153,11 @@ namespace
     {                                                                                                                   \
         cudaError_t e__ = (call);                                                                                       \
         if (e__ != cudaSuccess)                                                                                         \
+        {                                                                                                               \
+            (void)cudaGetLastError(); /* a recoverable error must not resurface at the next launch check */             \
             return fail(ctx, e__ == cudaErrorMemoryAllocation ? PCL_ERR_OOM : PCL_ERR_CUDA,                             \
                         std::string(#call) + ": " + cudaGetErrorString(e__));                                           \
+        }                                                                                                               \
     } while (0)
 
     // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (device, kernel, size class) instead of on every launch
@@ -864,19 +867,31 @@ extern "C"
         b->ctx = c, b->skel = skel, b->N = N, b->K = K;
         const size_t   n = (size_t)N * K;
         const SkelRec& s = c->skels[skel];
-        PCL_CK(c, cudaMalloc((void**)&b->d_clip_ids, n * 4));
-        PCL_CK(c, cudaMalloc((void**)&b->d_mask_ids, n * 4));
-        PCL_CK(c, cudaMalloc((void**)&b->d_phase, n * 4));
-        PCL_CK(c, cudaMalloc((void**)&b->d_weight, n * 4));
-        PCL_CK(c, cudaMalloc((void**)&b->d_len, n * 4));
-        PCL_CK(c, cudaMalloc((void**)&b->d_palette, (size_t)N * s.pitch * 48));
         std::vector<float> ones(n, 1.f);
-        PCL_CK(c, cudaMemset(b->d_clip_ids, 0, n * 4));
-        PCL_CK(c, cudaMemset(b->d_mask_ids, 0xff, n * 4));
-        PCL_CK(c, cudaMemset(b->d_phase, 0, n * 4));
-        PCL_CK(c, cudaMemcpy(b->d_weight, ones.data(), n * 4, cudaMemcpyHostToDevice));
-        PCL_CK(c, cudaMemcpy(b->d_len, ones.data(), n * 4, cudaMemcpyHostToDevice));
-        PCL_CK(c, cudaMemset(b->d_palette, 0, (size_t)N * s.pitch * 48));
+        cudaError_t        e    = cudaSuccess;
+        auto               step = [&e](cudaError_t r) { if (e == cudaSuccess) e = r; };
+        step(cudaMalloc((void**)&b->d_clip_ids, n * 4));
+        step(cudaMalloc((void**)&b->d_mask_ids, n * 4));
+        step(cudaMalloc((void**)&b->d_phase, n * 4));
+        step(cudaMalloc((void**)&b->d_weight, n * 4));
+        step(cudaMalloc((void**)&b->d_len, n * 4));
+        step(cudaMalloc((void**)&b->d_palette, (size_t)N * s.pitch * 48));
+        if (e == cudaSuccess)
+        {
+            step(cudaMemset(b->d_clip_ids, 0, n * 4));
+            step(cudaMemset(b->d_mask_ids, 0xff, n * 4));
+            step(cudaMemset(b->d_phase, 0, n * 4));
+            step(cudaMemcpy(b->d_weight, ones.data(), n * 4, cudaMemcpyHostToDevice));
+            step(cudaMemcpy(b->d_len, ones.data(), n * 4, cudaMemcpyHostToDevice));
+            step(cudaMemset(b->d_palette, 0, (size_t)N * s.pitch * 48));
+        }
+        if (e != cudaSuccess) // a crowd too big for the GPU must leave nothing behind
+        {
+            (void)cudaGetLastError();
+            cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len), cudaFree(b->d_palette);
+            delete b;
+            return fail(c, e == cudaErrorMemoryAllocation ? PCL_ERR_OOM : PCL_ERR_CUDA, std::string("pcl_batch_create: ") + cudaGetErrorString(e));
+        }
         *out = b;
         return PCL_OK;
     }

@@ -290,6 +290,17 @@ def test_pose_frame_coherent_order_changes_nothing(ctx, player, K, N):
         c2.close()
 
 
+def test_crowd_too_big_for_the_gpu_is_refused_cleanly(ctx, player_dev):
+    """A batch whose palettes exceed HBM: PCL_ERR_OOM, nothing leaked, no stale CUDA error at the next launch."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    with pytest.raises(capi.PclError) as e:
+        ctx.batch(skel, 70_000_000, 1)  # 70 M x 2880 B = 200 GB of palettes
+    assert e.value.code == -4
+    mats = gpu_pose(ctx, skel, np.full((64, 1), clip), np.linspace(0, 0.9, 64, dtype=np.float32))
+    assert np.isfinite(mats).all()
+
+
 def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, player):
     """The opt-in shared-memory size is a property of (device, kernel), not of a context: a second context that needs less
     must not shrink what the first one launches with (regression: 'invalid argument' on the first context's next pose)."""

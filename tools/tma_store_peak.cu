@@ -118,5 +118,23 @@ int main()
                 if (run<3, 9>(tp, tn, rows, Vp, vsplit, bytes, stagger, pitch))
                     return 1;
     }
+    // sustained: the same stream for ~3 s (does the 1 kW power cap, which pulls the SM clock down under the full kernel, touch it?)
+    {
+        CUtensorMap tp, tn;
+        make_map((encode_fn)fn, &tp, dp, rows, (long long)16384 * 3), make_map((encode_fn)fn, &tn, dn, rows, (long long)16384 * 6);
+        const int smem = 200 * 1024;
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0), cudaEventCreate(&e1);
+        for (int r = 0; r < 1200; r++)
+            store_only<3, 9><<<2346, 32, smem>>>(tp, tn, Vp / 32, 3, 0);
+        cudaEventRecord(e0);
+        for (int r = 0; r < 100; r++)
+            store_only<3, 9><<<2346, 32, smem>>>(tp, tn, Vp / 32, 3, 0);
+        cudaEventRecord(e1);
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        cudaEventElapsedTime(&ms, e0, e1);
+        printf("sustained (after ~2.7 s of the same launches): %.3f ms per launch, %7.1f GB/s\n", ms / 100, 100.0 * bytes / ms / 1e6);
+    }
     return 0;
 }
