@@ -86,7 +86,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0;
     int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
     int          max_smem_optin = 0, sm_count = 0;
     std::vector<void*> host_allocs;           // pcl_host_alloc blocks still alive (released by pcl_destroy at the latest)
@@ -499,6 +499,8 @@ extern "C"
             c->opt_pose_generic = v;
         else if (k == "pose_sort" && v >= -1 && v <= 1)
             c->opt_pose_sort = v;
+        else if (k == "pose_min_blocks" && (v == 0 || (v >= 2 && v <= 4)))
+            c->opt_pose_min_blocks = v;
         else if (k == "lbs_variant" && v >= -1 && v <= 3)
             c->opt_lbs_variant = v;
         else if (k == "lbs_warps" && (v == 0 || v == 8 || v == 12))
@@ -1222,21 +1224,30 @@ extern "C"
             PCL_CK(c, cudaGetLastError());
             p.order = b->d_order;
         }
+        // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM, except two-clip crowds beyond ~300 k instances
+        int mb = c->opt_pose_min_blocks;
+        if (mb == 0)
+            mb = (b->K == 2 && b->N >= 300000) ? 3 : 2;
+        if (b->K > 2)
+            mb = 2;
+#define PCL_LAUNCH_POSE_S(KK, SS, MM)                                                                                       \
+    {                                                                                                                       \
+        { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, SS, MM>, smem); if (rc__) return rc__; }            \
+        pose_simple_kernel<KK, SS, MM><<<grid, wpb * 32, smem, c->compute>>>(p);                                            \
+    }
+#define PCL_LAUNCH_POSE_MB(KK, SS)                                                                                          \
+    {                                                                                                                       \
+        if (KK > 2 || mb == 2) PCL_LAUNCH_POSE_S(KK, SS, 2)                                                                 \
+        else if (mb == 3) PCL_LAUNCH_POSE_S((KK > 2 ? 1 : KK), SS, 3)                                                       \
+        else PCL_LAUNCH_POSE_S((KK > 2 ? 1 : KK), SS, 4)                                                                    \
+    }
 #define PCL_LAUNCH_POSE(KK)                                                                                                 \
     {                                                                                                                       \
-        if (simple && sorted)                                                                                               \
-        {                                                                                                                   \
-            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, true>, smem); if (rc__) return rc__; }         \
-            pose_simple_kernel<KK, true><<<grid, wpb * 32, smem, c->compute>>>(p);                                          \
-        }                                                                                                                   \
-        else if (simple)                                                                                                    \
-        {                                                                                                                   \
-            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, false>, smem); if (rc__) return rc__; }        \
-            pose_simple_kernel<KK, false><<<grid, wpb * 32, smem, c->compute>>>(p);                                         \
-        }                                                                                                                   \
+        if (simple && sorted) PCL_LAUNCH_POSE_MB(KK, true)                                                                  \
+        else if (simple) PCL_LAUNCH_POSE_MB(KK, false)                                                                      \
         else                                                                                                                \
         {                                                                                                                   \
-            { int rc__ = ensure_smem(c, (const void*)pose_kernel<KK>, smem); if (rc__) return rc__; }       \
+            { int rc__ = ensure_smem(c, (const void*)pose_kernel<KK>, smem); if (rc__) return rc__; }                       \
             pose_kernel<KK><<<grid, wpb * 32, smem, c->compute>>>(p);                                                       \
         }                                                                                                                   \
     }
@@ -1247,6 +1258,8 @@ extern "C"
             case 3: PCL_LAUNCH_POSE(3) break;
             default: PCL_LAUNCH_POSE(4) break;
         }
+#undef PCL_LAUNCH_POSE_S
+#undef PCL_LAUNCH_POSE_MB
 #undef PCL_LAUNCH_POSE
         c->launches++;
         PCL_CK(c, cudaGetLastError());

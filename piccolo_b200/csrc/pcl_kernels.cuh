@@ -371,16 +371,19 @@ namespace pcl
     __device__ __forceinline__ int pick4(const int4& v, int g) { return g == 0 ? v.x : (g == 1 ? v.y : (g == 2 ? v.z : v.w)); }
     __device__ __forceinline__ int hic_decode(int v) { return v < 0 ? -1 - v : v; } // identity tracks are stored as -F
 
-    // The kernel is latency-bound (dependent sqrt/div chains, key gathers), so resident warps matter more than a
-    // few spilled registers: measured at N = 1 M, K = 1: 8 warps/SM 2.38 ms, 12 warps 2.10 ms, 16 warps 1.78 ms.
+    // MB = resident blocks per SM the register allocation is made for (__launch_bounds__): 2 -> 255 registers, 3 -> 168, 4 -> 128.
+    // With IEEE sqrt / division in the normalisations (slow-path branches after every one of them) the kernel hid its latencies
+    // only through resident warps: at N = 1 M, K = 1, 8 / 12 / 16 warps per SM ran 2.38 / 2.10 / 1.78 ms.  With the branch-free
+    // normalise (pcl_math.cuh) ptxas schedules across whole bones and the registers are worth more than the warps:
+    // 1.36 / 1.40 / 1.44 ms, and 33 us instead of 50 us for 10 k instances.  Two clips per instance still prefer 12 warps for the
+    // largest crowds (2.04 vs 2.23 ms at 1 M) and 8 below (0.236 vs 0.254 ms at 100 k); the launcher picks.
     constexpr int POSE_S_THREADS = 128;
-    __host__ __device__ constexpr int pose_s_minblocks(int K) { return K == 1 ? 4 : (K == 2 ? 3 : 2); }
     // SORTED: lane l of warp w works on instance order[32 w + l] instead of 32 w + l.  The order groups instances by the
     // (clip, frame) their phase falls in, so the 32 key gathers of a warp collapse onto one or two addresses (broadcast)
     // instead of up to 32 cache lines; every instance is still computed by exactly the same instruction sequence and
     // written to its own palette row, so the result does not depend on the order.
-    template<int K, bool SORTED>
-    __global__ void __launch_bounds__(POSE_S_THREADS, pose_s_minblocks(K)) pose_simple_kernel(const PoseParams par)
+    template<int K, bool SORTED, int MB>
+    __global__ void __launch_bounds__(POSE_S_THREADS, MB) pose_simple_kernel(const PoseParams par)
     {
         extern __shared__ __align__(16) float smem[];
         const int       lane  = threadIdx.x & 31;

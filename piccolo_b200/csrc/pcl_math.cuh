@@ -43,10 +43,29 @@ namespace pcl
     __device__ __forceinline__ Quat  qscale(Quat a, float s) { return Quat {a.w * s, a.x * s, a.y * s, a.z * s}; }
     __device__ __forceinline__ float qdot(Quat a, Quat b) { return a.w * b.w + a.x * b.x + a.y * b.y + a.z * b.z; }
     // Quaternion::normalise, core/math/quaternion.h:131-135: factor = 1 / length; q = q * factor.
-    // IEEE sqrt and division (nvcc defaults -prec-sqrt=true -prec-div=true), like the reference.
+    // The reference's factor carries two roundings (sqrt, then the division).  IEEE sqrtf and division each compile to a fast
+    // path plus a branch to a slow-path subroutine; three normalisations per bone put six such branches into every bone of the
+    // pose kernels and cut their instruction streams into blocks ptxas cannot schedule across.  PCL_EXACT_NORMALISE = 0 (default)
+    // takes MUFU.RSQ and one Newton step instead: branch-free, within 1 ulp of 1/sqrt(x), i.e. within 2 ulp of the reference's
+    // factor - the same size as the FMA-contraction differences the parity tolerance (1e-5 scaled) already covers.
+#ifndef PCL_EXACT_NORMALISE
+#define PCL_EXACT_NORMALISE 0
+#endif
+    __device__ __forceinline__ float rsqrt_newton(float x)
+    {
+        float y;
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+        const float e = fmaf(-x * y, 0.5f * y, 0.5f); // 0.5 (1 - x y^2)
+        return fmaf(y, e, y);
+    }
     __device__ __forceinline__ Quat qnormalise(Quat a)
     {
-        float factor = 1.0f / sqrtf(a.w * a.w + a.x * a.x + a.y * a.y + a.z * a.z);
+        const float len2 = a.w * a.w + a.x * a.x + a.y * a.y + a.z * a.z;
+#if PCL_EXACT_NORMALISE
+        const float factor = 1.0f / sqrtf(len2);
+#else
+        const float factor = rsqrt_newton(len2);
+#endif
         return qscale(a, factor);
     }
     // Quaternion::nLerp(t, kp, kq, shortest_path = true), core/math/quaternion.cpp:391-405
