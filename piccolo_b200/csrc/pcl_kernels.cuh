@@ -520,7 +520,7 @@ namespace pcl
 #pragma unroll
                     for (int k = 0; k < K; k++)
                     {
-                        const float wn = en[k] ? st[k].w / wsum : 0.f;
+                        const float wn = en[k] ? (PCL_EXACT_NORMALISE ? st[k].w / wsum : fdiv_nobranch(st[k].w, wsum)) : 0.f; // animation_system.cpp:117-149
                         TRS         d; // an identity track samples to the identity delta, exactly
                         d.p = P[k], d.s = S[k], d.q = Q[k];
                         if (fabsf(wsum) >= 0.0001f && wn != 0.f)

@@ -58,6 +58,16 @@ namespace pcl
         const float e = fmaf(-x * y, 0.5f * y, 0.5f); // 0.5 (1 - x y^2)
         return fmaf(y, e, y);
     }
+    // a / b without the slow-path branch of the IEEE division: reciprocal estimate, one Newton step, one residual correction
+    // (correctly rounded for the blend weights it is used on: normal range, b >= 1e-4).
+    __device__ __forceinline__ float fdiv_nobranch(float a, float b)
+    {
+        float r;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+        r             = fmaf(fmaf(-b, r, 1.0f), r, r);
+        const float q = a * r;
+        return fmaf(fmaf(-b, q, a), r, q);
+    }
     __device__ __forceinline__ Quat qnormalise(Quat a)
     {
         const float len2 = a.w * a.w + a.x * a.x + a.y * a.y + a.z * a.z;
