@@ -301,6 +301,30 @@ def test_crowd_too_big_for_the_gpu_is_refused_cleanly(ctx, player_dev):
     assert np.isfinite(mats).all()
 
 
+@pytest.mark.parametrize("K", [1, 2])
+def test_pose_register_allocation_variants_agree(ctx, player_dev, oracle, player, K):
+    """pose_min_blocks: the step-ordered kernel compiled for 2, 3 and 4 resident blocks per SM (255 / 168 / 128 registers) is the
+    same arithmetic, so the palettes must be bit-identical - and right (oracle)."""
+    skel, clip = player_dev
+    sk, cl, am, mk = player
+    N = 3001
+    rng = np.random.default_rng(K)
+    ph = rng.uniform(0, 1, (N, K)).astype(np.float32)
+    w = rng.uniform(0.1, 1, (N, K)).astype(np.float32)
+    got = {}
+    try:
+        for mb in (2, 3, 4):
+            ctx.set_option("pose_min_blocks", mb)
+            got[mb] = gpu_pose(ctx, skel, np.full((N, K), clip), ph, weight=w)
+    finally:
+        ctx.set_option("pose_min_blocks", 0)
+    assert np.array_equal(got[2], got[3]) and np.array_equal(got[2], got[4])
+    osk, ocl = oracle.skeleton(sk), oracle.clip(cl, am)
+    ref = oracle.pose_batch(osk, [ocl], np.zeros((N, K), np.int32), ph, weight=w) if K > 1 else \
+        oracle.pose_batch(osk, [ocl], np.zeros((N, 1), np.int32), ph[:, 0])
+    assert_mats_close(got[2], ref, tol=MAT_TOL if K == 1 else 2e-5)
+
+
 def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, player):
     """The opt-in shared-memory size is a property of (device, kernel), not of a context: a second context that needs less
     must not shrink what the first one launches with (regression: 'invalid argument' on the first context's next pose)."""
