@@ -39,7 +39,7 @@ def build_host(force: bool = False) -> str:
     hdir = os.path.join(PKG, "host")
     if not os.path.isdir(hdir):
         return ""
-    srcs = [os.path.join(hdir, f) for f in sorted(os.listdir(hdir))]
+    srcs = [os.path.join(hdir, f) for f in sorted(os.listdir(hdir)) if f.endswith((".cpp", ".h"))]  # not the built test_host: it is newer than the library by construction
     cpps = [s for s in srcs if s.endswith(".cpp") and not os.path.basename(s).startswith("test_")]
     if not cpps:
         return ""

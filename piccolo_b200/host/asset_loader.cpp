@@ -18,9 +18,11 @@ namespace Piccolo
     {
         std::string g_root;
 
+        std::string fullPath(const std::string& url) { return g_root.empty() ? url : g_root + "/" + url; }
+
         bool loadJson(const std::string& url, Value& out)
         {
-            const std::string path = g_root.empty() ? url : g_root + "/" + url;
+            const std::string path = fullPath(url);
             std::string       err;
             if (!pcljson::parse_file(path, out, err))
             {
@@ -152,10 +154,13 @@ namespace Piccolo
     {
         SkeletonData data;
         Value        j;
+        if (detail::cacheLoad(fullPath(url), data))
+            return std::make_shared<SkeletonData>(std::move(data));
         if (loadJson(url, j))
         {
             rdArray(j, "bones_map", data.bones_map);
             rd(j, "is_flat", data.is_flat), rd(j, "root_index", data.root_index), rd(j, "in_topological_order", data.in_topological_order);
+            detail::cacheStore(fullPath(url), data);
         }
         return std::make_shared<SkeletonData>(data);
     }
@@ -165,6 +170,8 @@ namespace Piccolo
     {
         AnimationAsset asset;
         Value          j;
+        if (detail::cacheLoad(fullPath(url), asset.clip_data))
+            return std::make_shared<AnimationClip>(std::move(asset.clip_data));
         if (loadJson(url, j))
         {
             if (has(j, "node_map"))
@@ -176,6 +183,7 @@ namespace Piccolo
                 rdArray(c, "node_channels", asset.clip_data.node_channels);
             }
             rd(j, "skeleton_file_path", asset.skeleton_file_path);
+            detail::cacheStore(fullPath(url), asset.clip_data);
         }
         return std::make_shared<AnimationClip>(asset.clip_data);
     }
@@ -184,8 +192,13 @@ namespace Piccolo
     {
         AnimSkelMap data;
         Value       j;
+        if (detail::cacheLoad(fullPath(url), data))
+            return std::make_shared<AnimSkelMap>(std::move(data));
         if (loadJson(url, j))
+        {
             rdInts(j, "convert", data.convert);
+            detail::cacheStore(fullPath(url), data);
+        }
         return std::make_shared<AnimSkelMap>(data);
     }
 
@@ -193,10 +206,13 @@ namespace Piccolo
     {
         BoneBlendMask data;
         Value         j;
+        if (detail::cacheLoad(fullPath(url), data))
+            return std::make_shared<BoneBlendMask>(std::move(data));
         if (loadJson(url, j))
         {
             rd(j, "skeleton_file_path", data.skeleton_file_path);
             rdInts(j, "enabled", data.enabled);
+            detail::cacheStore(fullPath(url), data);
         }
         return std::make_shared<BoneBlendMask>(data);
     }
@@ -205,11 +221,14 @@ namespace Piccolo
     {
         MeshData data;
         Value    j;
+        if (detail::cacheLoad(fullPath(url), data))
+            return std::make_shared<MeshData>(std::move(data));
         if (loadJson(url, j))
         {
             rdArray(j, "vertex_buffer", data.vertex_buffer);
             rdInts(j, "index_buffer", data.index_buffer);
             rdArray(j, "bind", data.bind);
+            detail::cacheStore(fullPath(url), data);
         }
         return std::make_shared<MeshData>(data);
     }

@@ -170,7 +170,25 @@ namespace Piccolo
         // AssetManager::getFullPath stand-in: prefix joined in front of every url
         static void               setAssetRoot(const std::string& root);
         static const std::string& assetRoot();
+        // Binary cache of the parsed assets (asset_cache.cpp).  Empty (default) = off, like the reference.
+        // With a directory set, a load first looks for a flat image of the asset there (validated against the JSON file's
+        // size and modification time, and by a checksum) and writes one after parsing otherwise.
+        static void               setCacheDir(const std::string& dir);
+        static const std::string& cacheDir();
     };
+    namespace detail // asset_cache.cpp
+    {
+        bool cacheLoad(const std::string& full_path, SkeletonData& out);
+        bool cacheLoad(const std::string& full_path, AnimationClip& out);
+        bool cacheLoad(const std::string& full_path, AnimSkelMap& out);
+        bool cacheLoad(const std::string& full_path, BoneBlendMask& out);
+        bool cacheLoad(const std::string& full_path, MeshData& out);
+        void cacheStore(const std::string& full_path, const SkeletonData& v);
+        void cacheStore(const std::string& full_path, const AnimationClip& v);
+        void cacheStore(const std::string& full_path, const AnimSkelMap& v);
+        void cacheStore(const std::string& full_path, const BoneBlendMask& v);
+        void cacheStore(const std::string& full_path, const MeshData& v);
+    } // namespace detail
 
     // ---- function/animation/node.h (the read side LevelDebugger uses) -------------------------------
     class Node

@@ -43,6 +43,8 @@ static int cmd_load(int argc, char** argv)
     if (argc < 8)
         return 2;
     AnimationLoader::setAssetRoot(argv[2]);
+    if (argc > 8) // optional: binary asset cache directory
+        AnimationLoader::setCacheDir(argv[8]);
     AnimationLoader L;
     auto            sk = L.loadSkeletonData(argv[3]);
     auto            cl = L.loadAnimationClipData(argv[4]);

@@ -47,6 +47,55 @@ def test_loader_on_the_bundled_reference_json(player, tmp_path):
     _check_load(out, *player)
 
 
+def test_binary_asset_cache_returns_exactly_what_the_json_does(player, tmp_path):
+    """AnimationLoader::setCacheDir (SURVEY.md 8f.3): the first load parses the JSON and writes flat images, the second is served
+    from them, bit for bit; a stale (source touched), truncated or corrupted image is ignored and rewritten, never trusted."""
+    import time
+    urls = H.write_player_tree(str(tmp_path / "assets"), player, sparse=True)
+    cache = tmp_path / "cache"
+    cache.mkdir()
+    args = ["load", tmp_path / "assets", urls["skeleton"], urls["clip"], urls["map"], urls["mask"]]
+    dumps = []
+    times = []
+    for i in range(2):
+        out = tmp_path / ("load%d.bin" % i)
+        t0 = time.perf_counter()
+        r = H.run(args + [out, cache])
+        times.append(time.perf_counter() - t0)
+        assert r.returncode == 0, r.stderr
+        _check_load(out, *player)
+        dumps.append(open(out, "rb").read())
+    images = sorted(os.listdir(cache))
+    assert len(images) == 4 and all(f.endswith(".pclbin") for f in images)  # skeleton, clip, map, mask; nothing for the missing file
+    assert dumps[0] == dumps[1]
+    # served from the cache: make the JSON unparsable but keep its size and mtime - the load must still succeed
+    clip_json = tmp_path / "assets" / urls["clip"]
+    st = os.stat(clip_json)
+    raw = open(clip_json, "rb").read()
+    open(clip_json, "wb").write(b"!" * len(raw))
+    os.utime(clip_json, ns=(st.st_atime_ns, st.st_mtime_ns))
+    out = tmp_path / "load_cached.bin"
+    r = H.run(args + [out, cache])
+    assert r.returncode == 0 and open(out, "rb").read() == dumps[0]
+    # stale: restore the JSON with a new mtime -> the image no longer validates, the JSON is parsed again
+    open(clip_json, "wb").write(raw)
+    os.utime(clip_json, ns=(st.st_atime_ns, st.st_mtime_ns + 5_000_000_000))
+    # corrupted and truncated images of the other assets
+    for k, f in enumerate(images):
+        p = cache / f
+        b = bytearray(open(p, "rb").read())
+        if k % 2 == 0:
+            b[len(b) // 2] ^= 0x5a
+        else:
+            b = b[: len(b) // 2]
+        open(p, "wb").write(bytes(b))
+    out = tmp_path / "load_repaired.bin"
+    r = H.run(args + [out, cache])
+    assert r.returncode == 0, r.stderr
+    _check_load(out, *player)
+    assert open(out, "rb").read() == dumps[0]
+
+
 def test_component_is_inert_without_a_gpu(player, tmp_path):
     import torch
     if torch.cuda.is_available():
