@@ -8,6 +8,7 @@
 #include <climits>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -87,6 +88,7 @@ struct pcl_ctx
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
     int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0;
+    bool         debug_sync = false; // PICCOLO_B200_DEBUG_SYNC=1: synchronise after every launch
     int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
     int          max_smem_optin = 0, sm_count = 0;
     std::vector<void*> host_allocs;           // pcl_host_alloc blocks still alive (released by pcl_destroy at the latest)
@@ -160,15 +162,40 @@ namespace
         }                                                                                                               \
     } while (0)
 
+    // After every launch: the launch error, and - with PICCOLO_B200_DEBUG_SYNC=1 in the environment when the context is created -
+    // a synchronisation, so that an asynchronous fault is reported by the call that caused it, with the kernel's name.
+#define PCL_POST_LAUNCH(ctx, stream, name)                                                                                  \
+    do                                                                                                                      \
+    {                                                                                                                       \
+        cudaError_t e__ = cudaGetLastError();                                                                               \
+        if (e__ == cudaSuccess && (ctx)->debug_sync)                                                                        \
+            e__ = cudaStreamSynchronize(stream);                                                                            \
+        if (e__ != cudaSuccess)                                                                                             \
+        {                                                                                                                   \
+            (void)cudaGetLastError();                                                                                       \
+            return fail(ctx, PCL_ERR_CUDA, std::string(name) + ": " + cudaGetErrorString(e__));                             \
+        }                                                                                                                   \
+    } while (0)
+
     // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (device, kernel, size class) instead of on every launch
     int ensure_smem(pcl_ctx* c, const void* func, size_t bytes);
+
+    // Host -> device copies and memsets go through the context's COMPUTE stream, never the legacy default stream: the
+    // context's streams are non-blocking, so they are not ordered against legacy-stream work, and cudaMemcpy from pageable
+    // memory returns once the data is STAGED, not once it has reached the device - a kernel launched right after an upload
+    // (the record streams lbs_cta_kernel builds on first use) could read the buffer before its contents had arrived.
+    cudaError_t copy_h2d(pcl_ctx* c, void* dst, const void* src, size_t bytes)
+    {
+        cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->compute);
+        return e != cudaSuccess ? e : cudaStreamSynchronize(c->compute); // the host buffer may be freed when this returns
+    }
 
     template<typename T>
     int upload(pcl_ctx* c, T** dptr, const std::vector<T>& h)
     {
         PCL_CK(c, cudaMalloc((void**)dptr, std::max<size_t>(h.size(), 1) * sizeof(T)));
         if (!h.empty())
-            PCL_CK(c, cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+            PCL_CK(c, copy_h2d(c, *dptr, h.data(), h.size() * sizeof(T)));
         return PCL_OK;
     }
 
@@ -385,6 +412,8 @@ extern "C"
         c->device         = device;
         c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
         c->sm_count       = prop.multiProcessorCount;
+        const char* dbg   = std::getenv("PICCOLO_B200_DEBUG_SYNC");
+        c->debug_sync     = dbg && dbg[0] == '1';
         cudaError_t e     = cudaStreamCreateWithFlags(&c->compute, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_pose, cudaEventDisableTiming);
@@ -718,15 +747,15 @@ extern "C"
         ch.skel = skel;
         PCL_CK(c, cudaMalloc(&ch.d_blob, total));
         unsigned char* d = (unsigned char*)ch.d_blob;
-        PCL_CK(c, cudaMemcpy(d, keys.data(), kb, cudaMemcpyHostToDevice));
-        PCL_CK(c, cudaMemcpy(d + up16(kb), first.data(), fb, cudaMemcpyHostToDevice));
-        PCL_CK(c, cudaMemcpy(d + up16(kb) + up16(fb), next.data(), nb, cudaMemcpyHostToDevice));
-        PCL_CK(c, cudaMemcpy(d + up16(kb) + up16(fb) + up16(nb), hic.data(), hb, cudaMemcpyHostToDevice));
+        PCL_CK(c, copy_h2d(c, d, keys.data(), kb));
+        PCL_CK(c, copy_h2d(c, d + up16(kb), first.data(), fb));
+        PCL_CK(c, copy_h2d(c, d + up16(kb) + up16(fb), next.data(), nb));
+        PCL_CK(c, copy_h2d(c, d + up16(kb) + up16(fb) + up16(nb), hic.data(), hb));
         unsigned char* d2 = d + up16(kb) + up16(fb) + up16(nb) + up16(hb);
         if (simple)
         {
-            PCL_CK(c, cudaMemcpy(d2, skeys.data(), skb, cudaMemcpyHostToDevice));
-            PCL_CK(c, cudaMemcpy(d2 + up16(skb), shic.data(), shb, cudaMemcpyHostToDevice));
+            PCL_CK(c, copy_h2d(c, d2, skeys.data(), skb));
+            PCL_CK(c, copy_h2d(c, d2 + up16(skb), shic.data(), shb));
         }
         ch.rec.keys           = (const float4*)d;
         ch.rec.first_chan     = (const int32_t*)(d + up16(kb));
@@ -753,12 +782,12 @@ extern "C"
             std::vector<ClipRec> all;
             for (auto& x : c->clips)
                 all.push_back(x.rec);
-            PCL_CK(c, cudaMemcpy(nd, all.data(), all.size() * sizeof(ClipRec), cudaMemcpyHostToDevice));
+            PCL_CK(c, copy_h2d(c, nd, all.data(), all.size() * sizeof(ClipRec)));
             cudaFree(c->d_clips);
             c->d_clips = nd, c->cap_clips = ncap;
         }
         else
-            PCL_CK(c, cudaMemcpy(c->d_clips + id, &ch.rec, sizeof(ClipRec), cudaMemcpyHostToDevice));
+            PCL_CK(c, copy_h2d(c, c->d_clips + id, &ch.rec, sizeof(ClipRec)));
         *out = id;
         return PCL_OK;
     }
@@ -778,11 +807,12 @@ extern "C"
             PCL_CK(c, cudaStreamSynchronize(c->compute));
             PCL_CK(c, cudaMalloc((void**)&nd, (size_t)ncap * s.J * 4));
             if (s.n_masks)
-                PCL_CK(c, cudaMemcpy(nd, s.d_masks, (size_t)s.n_masks * s.J * 4, cudaMemcpyDeviceToDevice));
+                PCL_CK(c, cudaMemcpyAsync(nd, s.d_masks, (size_t)s.n_masks * s.J * 4, cudaMemcpyDeviceToDevice, c->compute));
+                PCL_CK(c, cudaStreamSynchronize(c->compute));
             cudaFree(s.d_masks);
             s.d_masks = nd, s.cap_masks = ncap;
         }
-        PCL_CK(c, cudaMemcpy(s.d_masks + (size_t)s.n_masks * s.J, enabled, (size_t)s.J * 4, cudaMemcpyHostToDevice));
+        PCL_CK(c, copy_h2d(c, s.d_masks + (size_t)s.n_masks * s.J, enabled, (size_t)s.J * 4));
         c->masks.push_back(MaskHost {skel, s.n_masks});
         s.n_masks++;
         *out = (pcl_mask)c->masks.size() - 1;
@@ -880,12 +910,12 @@ extern "C"
         step(cudaMalloc((void**)&b->d_palette, (size_t)N * s.pitch * 48));
         if (e == cudaSuccess)
         {
-            step(cudaMemset(b->d_clip_ids, 0, n * 4));
-            step(cudaMemset(b->d_mask_ids, 0xff, n * 4));
-            step(cudaMemset(b->d_phase, 0, n * 4));
-            step(cudaMemcpy(b->d_weight, ones.data(), n * 4, cudaMemcpyHostToDevice));
-            step(cudaMemcpy(b->d_len, ones.data(), n * 4, cudaMemcpyHostToDevice));
-            step(cudaMemset(b->d_palette, 0, (size_t)N * s.pitch * 48));
+            step(cudaMemsetAsync(b->d_clip_ids, 0, n * 4, c->compute));
+            step(cudaMemsetAsync(b->d_mask_ids, 0xff, n * 4, c->compute));
+            step(cudaMemsetAsync(b->d_phase, 0, n * 4, c->compute));
+            step(copy_h2d(c, b->d_weight, ones.data(), n * 4));
+            step(copy_h2d(c, b->d_len, ones.data(), n * 4));
+            step(cudaMemsetAsync(b->d_palette, 0, (size_t)N * s.pitch * 48, c->compute));
         }
         if (e != cudaSuccess) // a crowd too big for the GPU must leave nothing behind
         {
@@ -930,7 +960,9 @@ extern "C"
         const size_t bytes = (size_t)capacity * s.pitch * 48;
         cudaError_t  e     = cudaMalloc((void**)&p->base, bytes);
         if (e == cudaSuccess)
-            e = cudaMemset(p->base, 0, bytes);
+            e = cudaMemsetAsync(p->base, 0, bytes, c->compute);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(c->compute); // peers may write the pool as soon as they have its handle
         if (e != cudaSuccess)
         {
             cudaFree(p->base);
@@ -1142,7 +1174,7 @@ extern "C"
         const long long total = (mode == PCL_ADVANCE_ALL) ? b->N * b->K : b->N; // slot 0 is row 0 of the [K][N] arrays
         advance_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->compute>>>(b->d_phase, b->d_len, 0, total, dt);
         c->launches++;
-        PCL_CK(c, cudaGetLastError());
+        PCL_POST_LAUNCH(c, c->compute, "advance_kernel");
         return PCL_OK;
     }
 
@@ -1221,7 +1253,7 @@ extern "C"
             { int rc__ = ensure_smem(c, (const void*)order_scatter_kernel, (size_t)q.nbk * 8); if (rc__) return rc__; }
             order_scatter_kernel<<<ogrid, ORDER_THREADS, (size_t)q.nbk * 8, c->compute>>>(q);
             c->launches += 3;
-            PCL_CK(c, cudaGetLastError());
+            PCL_POST_LAUNCH(c, c->compute, "order_*_kernel");
             p.order = b->d_order;
         }
         // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM, except two-clip crowds beyond ~300 k instances
@@ -1262,7 +1294,7 @@ extern "C"
 #undef PCL_LAUNCH_POSE_MB
 #undef PCL_LAUNCH_POSE
         c->launches++;
-        PCL_CK(c, cudaGetLastError());
+        PCL_POST_LAUNCH(c, c->compute, "pose kernel");
         PCL_CK(c, cudaEventRecord(c->ev_pose, c->compute));
         b->posed = true;
         return PCL_OK;
@@ -1433,7 +1465,7 @@ extern "C"
 #undef PCL_LAUNCH_LBSC_T
 #undef PCL_LAUNCH_LBSC
                     c->launches++;
-                    PCL_CK(c, cudaGetLastError());
+                    PCL_POST_LAUNCH(c, c->compute, "lbs_cta_kernel");
                 }
                 if (count == full * cT)
                     return PCL_OK;
@@ -1479,7 +1511,7 @@ extern "C"
                 else PCL_LAUNCH_LBSI(false, 8, false)
 #undef PCL_LAUNCH_LBSI
                 c->launches++;
-                PCL_CK(c, cudaGetLastError());
+                PCL_POST_LAUNCH(c, c->compute, "lbs_inst_kernel");
                 return PCL_OK;
             }
         }
@@ -1516,7 +1548,7 @@ extern "C"
         else PCL_LAUNCH_LBS(false, true)
 #undef PCL_LAUNCH_LBS
         c->launches++;
-        PCL_CK(c, cudaGetLastError());
+        PCL_POST_LAUNCH(c, c->compute, "lbs_kernel");
         return PCL_OK;
     }
 
@@ -1544,7 +1576,7 @@ extern "C"
         const long long total = count * s.J * 4;
         export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, b->d_export, first, count, s.J, s.pitch);
         c->launches++;
-        PCL_CK(c, cudaGetLastError());
+        PCL_POST_LAUNCH(c, c->copy, "export_kernel");
         PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy));
         c->copy_pending = true;
         PCL_CK(c, cudaMemcpyAsync(host16, b->d_export, (size_t)count * s.J * 64, cudaMemcpyDeviceToHost, c->copy));
@@ -1669,7 +1701,7 @@ extern "C"
         const long long total = count * (s.J + 1) * 4;
         render_export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->compute>>>(b->d_palette, rb->d_mats, first, count, s.J + 1, s.pitch, draw_first);
         c->launches++;
-        PCL_CK(c, cudaGetLastError());
+        PCL_POST_LAUNCH(c, c->compute, "render_export_kernel");
         return PCL_OK;
     }
     int pcl_renderbuf_dev(pcl_renderbuf* r, const void** dptr)
@@ -1724,7 +1756,7 @@ extern "C"
         const long long total = count * s.J * 4; // every float4 of the range is overwritten: nothing to clear
         export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, staging, first, count, s.J, s.pitch);
         c->launches++;
-        PCL_CK(c, cudaGetLastError());
+        PCL_POST_LAUNCH(c, c->copy, "export_kernel (static staging)");
         PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy));
         c->copy_pending = true;
         PCL_CK(c, cudaMemcpyAsync(host16, staging, bytes, cudaMemcpyDeviceToHost, c->copy));

@@ -1067,8 +1067,8 @@ namespace pcl
     struct alignas(16) VRec // one vertex, warp-uniform
     {
         float px, py, pz, w0;
-        float nx, ny, nz, w1;
-        float tx, ty, tz, w2;
+        float nx, tx, ny, ty; // normal and tangent interleaved: (n.k, t.k) pairs feed the packed fp32 transforms of lbs_cta_kernel
+        float nz, tz, w1, w2;
         float    w3;
         uint32_t i01;  // 3 * palette slot of influence 0 | 3 * slot of influence 1 << 16 (16-byte units into a palette row)
         uint32_t i23;
@@ -1264,7 +1264,7 @@ namespace pcl
             const VRec* vr = vring + (st * LBS_I_SCH + sub) * LBS_I_CHUNK;
             // records are fetched one vertex ahead so that the broadcast loads overlap the previous vertex's math
             float4 na = *reinterpret_cast<const float4*>(&vr[0].px), nb = *reinterpret_cast<const float4*>(&vr[0].nx);
-            float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].tx);
+            float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].nz);
             uint4  nd = *reinterpret_cast<const uint4*>(&vr[0].w3);
 #pragma unroll
             for (int half = 0; half < 2; half++)
@@ -1275,13 +1275,14 @@ namespace pcl
 #pragma unroll
                 for (int j = 0; j < 4; j++)
                 {
-                    const float4 a = na, b = nb, t = nt_;
+                    const float4 a = na;
+                    const float4 b = make_float4(nb.x, nb.z, nt_.x, nt_.z), t = make_float4(nb.y, nb.w, nt_.y, nt_.w); // {n, w1}, {t, w2}
                     const uint4  d = nd;
                     if (half * 4 + j + 1 < LBS_I_CHUNK)
                     {
                         na  = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].px);
                         nb  = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].nx);
-                        nt_ = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].tx);
+                        nt_ = *reinterpret_cast<const float4*>(&vr[half * 4 + j + 1].nz);
                         nd  = *reinterpret_cast<const uint4*>(&vr[half * 4 + j + 1].w3);
                     }
                     if (d.w) // some slot changes bone at this vertex (warp-uniform, rare in a coherent mesh)
@@ -1573,18 +1574,18 @@ namespace pcl
             float* opf = reinterpret_cast<float*>(op);
             float* onf = reinterpret_cast<float*>(on);
             float4 na = *reinterpret_cast<const float4*>(&vr[0].px), nb = *reinterpret_cast<const float4*>(&vr[0].nx);
-            float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].tx);
+            float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].nz);
             uint4  nd = *reinterpret_cast<const uint4*>(&vr[0].w3);
 #pragma unroll
             for (int j = 0; j < LBS_C_VPW; j++)
             {
-                const float4 a = na, bb = nb, t = nt_;
+                const float4 a = na, q1 = nb, q2 = nt_; // q1 = {n.x, t.x, n.y, t.y}, q2 = {n.z, t.z, w1, w2}
                 const uint4  d = nd;
                 if (j + 1 < LBS_C_VPW)
                 {
                     na  = *reinterpret_cast<const float4*>(&vr[j + 1].px);
                     nb  = *reinterpret_cast<const float4*>(&vr[j + 1].nx);
-                    nt_ = *reinterpret_cast<const float4*>(&vr[j + 1].tx);
+                    nt_ = *reinterpret_cast<const float4*>(&vr[j + 1].nz);
                     nd  = *reinterpret_cast<const uint4*>(&vr[j + 1].w3);
                 }
                 if (d.w)
@@ -1594,7 +1595,7 @@ namespace pcl
                     if (d.w & 4) lbs_i_load(m[2], prow, d.z & 0xffffu);
                     if (d.w & 8) lbs_i_load(m[3], prow, d.z >> 16);
                 }
-                const float w0 = a.w, w1 = bb.w, w2 = t.w, w3 = __uint_as_float(d.x);
+                const float w0 = a.w, w1 = q2.z, w2 = q2.w, w3 = __uint_as_float(d.x);
                 float4 B[3];
                 {
                     const unsigned long long ww0 = pack2(w0, w0), ww1 = pack2(w1, w1), ww2 = pack2(w2, w2), ww3 = pack2(w3, w3);
@@ -1608,19 +1609,37 @@ namespace pcl
                         unpack2(lo, B[r].x, B[r].y), unpack2(hi, B[r].z, B[r].w);
                     }
                 }
-                opf[j * 3 + 0] = B[0].x * a.x + B[0].y * a.y + B[0].z * a.z + B[0].w; // mesh.vert:104
-                opf[j * 3 + 1] = B[1].x * a.x + B[1].y * a.y + B[1].z * a.z + B[1].w;
-                opf[j * 3 + 2] = B[2].x * a.x + B[2].y * a.y + B[2].z * a.z + B[2].w;
+                // mesh.vert:104-110.  Position: one FMA chain per row.  Normal and tangent go through the same 3x3 block, so
+                // row r of both is ONE packed chain on the (n.k, t.k) pairs the record delivers: 9 FFMA2 instead of 18 FFMA, and
+                // both squared lengths are one more packed chain (fewer instructions = less energy: the kernel runs at the
+                // board's power cap, where time follows joules rather than latencies).
+                opf[j * 3 + 0] = fmaf(B[0].x, a.x, fmaf(B[0].y, a.y, fmaf(B[0].z, a.z, B[0].w)));
+                opf[j * 3 + 1] = fmaf(B[1].x, a.x, fmaf(B[1].y, a.y, fmaf(B[1].z, a.z, B[1].w)));
+                opf[j * 3 + 2] = fmaf(B[2].x, a.x, fmaf(B[2].y, a.y, fmaf(B[2].z, a.z, B[2].w)));
                 if (NT)
                 {
-                    const float nx = B[0].x * bb.x + B[0].y * bb.y + B[0].z * bb.z, ny = B[1].x * bb.x + B[1].y * bb.y + B[1].z * bb.z,
-                                nz = B[2].x * bb.x + B[2].y * bb.y + B[2].z * bb.z;
-                    const float tx = B[0].x * t.x + B[0].y * t.y + B[0].z * t.z, ty = B[1].x * t.x + B[1].y * t.y + B[1].z * t.z,
-                                tz = B[2].x * t.x + B[2].y * t.y + B[2].z * t.z;
-                    const float rn = rsqrt_ftz(nx * nx + ny * ny + nz * nz);
-                    const float rt = rsqrt_ftz(tx * tx + ty * ty + tz * tz);
-                    onf[j * 6 + 0] = nx * rn, onf[j * 6 + 1] = ny * rn, onf[j * 6 + 2] = nz * rn;
-                    onf[j * 6 + 3] = tx * rt, onf[j * 6 + 4] = ty * rt, onf[j * 6 + 5] = tz * rt;
+                    const unsigned long long vx = pack2(q1.x, q1.y), vy = pack2(q1.z, q1.w), vz = pack2(q2.x, q2.y);
+                    unsigned long long       o[3];
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+                    {
+                        o[r] = mul2(vx, pack2(B[r].x, B[r].x));
+                        o[r] = fma2(vy, pack2(B[r].y, B[r].y), o[r]);
+                        o[r] = fma2(vz, pack2(B[r].z, B[r].z), o[r]);
+                    }
+                    unsigned long long l2 = mul2(o[0], o[0]);
+                    l2                    = fma2(o[1], o[1], l2);
+                    l2                    = fma2(o[2], o[2], l2);
+                    float ln, lt;
+                    unpack2(l2, ln, lt);
+                    const float rn = rsqrt_ftz(ln), rt = rsqrt_ftz(lt);
+#pragma unroll
+                    for (int r = 0; r < 3; r++)
+                    {
+                        float nr, tr;
+                        unpack2(o[r], nr, tr);
+                        onf[j * 6 + r] = nr * rn, onf[j * 6 + 3 + r] = tr * rt;
+                    }
                 }
             }
             if (s >= LBS_C_TILES)
