@@ -1422,14 +1422,24 @@ extern "C"
                 const int    ctiles = lbs_c_smem_bytes(prow, nt, 3, cT) <= (size_t)c->max_smem_optin ? 3 : 2;
                 const size_t smem_c = lbs_c_smem_bytes(prow, nt, ctiles, cT);
                 const int    ti     = cT == 32 ? 0 : (cT == 16 ? 1 : 2);
-                const long long full = count / cT; // whole tiles; a ragged remainder goes to lbs_inst_kernel / lbs_kernel below
-                if (full > 0)
+                const long long full = (count + cT - 1) / cT; // tiles; the last one may be ragged
+                // rows the stores may touch: the ring's capacity for whole tiles; for a ragged last tile, maps of this launch's
+                // own height, so that the TMA drops the rows of the instances that do not exist
+                CUtensorMap tmp_pos = out->tm_pos[ti], tmp_nt = out->tm_nt[ti];
+                if (count % cT != 0)
+                {
+                    if (!make_stream_tmap(&tmp_pos, out->d_pos, slot_first + count, (long long)out->Vp * 3, (unsigned)cT) ||
+                        (nt && !make_stream_tmap(&tmp_nt, out->d_nt, slot_first + count, (long long)out->Vp * 6, (unsigned)cT)))
+                        return fail(c, PCL_ERR_CUDA, "pcl_batch_skin: cuTensorMapEncodeTiled failed");
+                    if (!nt)
+                        tmp_nt = tmp_pos;
+                }
                 {
                     MeshRec& mm = c->meshes[mesh];
                     { int rc__ = ensure_vrec_cta(c, mm, cT); if (rc__) return rc__; }
                     LbsCParams q {};
                     q.vrec = mm.d_vrec_cta[ti], q.palette = b->d_palette;
-                    q.first = first, q.slot_first = slot_first, q.n_tiles = (int32_t)full;
+                    q.first = first, q.slot_first = slot_first, q.count = count, q.n_tiles = (int32_t)full;
                     q.Vp = m.Vp, q.n_sc = (m.Vp + lbs_c_scv(cT) - 1) / lbs_c_scv(cT), q.pitch = s.pitch, q.prow = prow;
                     int vs = c->opt_lbs_vsplit;
                     if (vs == 0)
@@ -1450,7 +1460,7 @@ extern "C"
 #define PCL_LAUNCH_LBSC(NT_, TL_, T_)                                                                                        \
     {                                                                                                                       \
         { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<NT_, TL_, T_>, smem_c); if (rc__) return rc__; }             \
-        lbs_cta_kernel<NT_, TL_, T_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, out->tm_pos[ti], out->tm_nt[ti]);       \
+        lbs_cta_kernel<NT_, TL_, T_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, tmp_pos, tmp_nt);                         \
     }
 #define PCL_LAUNCH_LBSC_T(T_)                                                                                               \
     {                                                                                                                       \
@@ -1467,10 +1477,7 @@ extern "C"
                     c->launches++;
                     PCL_POST_LAUNCH(c, c->compute, "lbs_cta_kernel");
                 }
-                if (count == full * cT)
-                    return PCL_OK;
-                first += full * cT, slot_first += full * cT, count -= full * cT;
-                var = fits ? 2 : 0;
+                return PCL_OK;
             }
             if (var == 2)
             {

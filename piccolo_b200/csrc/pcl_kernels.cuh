@@ -1399,8 +1399,8 @@ namespace pcl
     // the store warp also refills the CTA-wide vertex-record ring (TMA bulk loads, complete_tx on mbarriers).
     // Bone matrices stay in registers exactly as in lbs_inst_kernel; because a warp now visits vertices
     // 4w..4w+3 of every superchunk, the upload packs the influence slots along that visiting order (`vrec_cta`).
-    // Whole 32-instance tiles only (the boxes are not clipped in the instance dimension by `count`): the
-    // launcher hands a ragged remainder to lbs_inst_kernel.
+    // A ragged last tile is clipped by the TMA itself: for such launches the launcher encodes tensor maps whose row count
+    // is slot_first + count, and the store boxes' rows beyond it are dropped.
     // -------------------------------------------------------------------------------------------
     constexpr int LBS_C_WARPS   = 8;                       // compute warps
     constexpr int LBS_C_THREADS = (LBS_C_WARPS + 1) * 32;  // + 1 store / load warp
@@ -1440,7 +1440,7 @@ namespace pcl
     {
         const VRec*   vrec;    // packed along the (warp, stream) visiting order for this T, padded to whole record stages
         const float4* palette; // [N][pitch][3]
-        long long     first, slot_first;
+        long long     first, slot_first, count; // count need not be a multiple of T: see the last tile below
         int32_t       n_tiles, Vp, n_sc, pitch, prow, vsplit;
     };
 
@@ -1491,8 +1491,11 @@ namespace pcl
             {
                 const uint32_t row_bytes = (uint32_t)par.pitch * 48;
                 mbar_expect_tx(&bars[0], row_bytes * T);
+                // a ragged last tile: the missing instances shadow the last real one; their rows lie beyond the row count of
+                // the tensor maps the launcher built for this launch, so the stores drop them
                 for (int i = 0; i < T; i++)
-                    tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + i0 + i) * par.pitch * 3, row_bytes, &bars[0]);
+                    tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + min(i0 + i, par.count - 1)) * par.pitch * 3, row_bytes,
+                             &bars[0]);
                 for (int st = 0; st < LBS_C_RSTAGES && st * RSC < n_steps; st++)
                 {
                     mbar_expect_tx(&rbar[st], LBS_C_RSTAGE_BYTES);

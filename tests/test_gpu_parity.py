@@ -443,7 +443,7 @@ def test_lbs_vs_oracle_player(ctx, player_dev, oracle, player, variant, V, N):
 @pytest.mark.parametrize("variant", [0, 1, -1, 2, 3])
 def test_lbs_config5_synthetic(ctx, oracle, variant):
     """257 palette slots: 32 palettes do not fit in shared memory.  The TMA-store crowd kernel (3) drops to 8 instances per
-    CTA (4 vertex streams per warp) and handles the ragged 3-instance remainder with the lane-per-vertex kernel; forcing the
+    CTA (4 vertex streams per warp; the ragged last tile of 3 instances is clipped by the launch's tensor maps); forcing the
     LSU crowd kernel (2), which only exists for 32 palettes, must be refused, not silently mis-skinned."""
     from piccolo_b200 import capi
     sk = A.make_synthetic_skeleton(256)
@@ -509,6 +509,46 @@ def test_lbs_tma_store_kernel_smaller_instance_tiles_on_player(ctx, player_dev, 
     if flags_nt:
         ok = np.isfinite(nt32)
         assert np.array_equal(ok, np.isfinite(nt[:N - 16])) and np.abs(nt[:N - 16][ok] - nt32[ok]).max() <= 4e-6
+
+
+@pytest.mark.parametrize("cta_tile", [32, 16, 8])
+def test_lbs_ragged_last_tile_is_clipped_by_the_tensor_maps(ctx, player_dev, player, cta_tile):
+    """An instance count that is not a multiple of the tile: the last tile's missing instances are dropped by tensor maps encoded
+    for this launch (rows = slot_first + count).  The ring rows behind the launch must keep what was there, bit for bit, and the
+    rows of the launch must equal the lane-per-vertex kernel's."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    mesh = A.make_player_mesh(player[0], V=3000, seed=11)
+    mh = ctx.upload_mesh(mesh, 58)
+    cap, N, slot0 = 260, 197, 7  # 197 = 6 x 32 + 5 = 12 x 16 + 5 = 24 x 8 + 5
+    rng = np.random.default_rng(cta_tile)
+    sb = ctx.skinbuf(mh, mesh.V, cap, capi.PCL_SKIN_POS_NRM_TAN)
+    old = ctx.batch(skel, cap, 1)
+    old.set(clip_ids=np.full((cap, 1), clip, np.int32), phase=rng.uniform(0, 1, cap).astype(np.float32))
+    old.pose()
+    old.skin(mh, sb)
+    before_pos, before_nt = sb.download()
+    new = ctx.batch(skel, N, 1)
+    new.set(clip_ids=np.full((N, 1), clip, np.int32), phase=rng.uniform(0, 1, N).astype(np.float32))
+    new.pose()
+    try:
+        ctx.set_option("lbs_variant", 3), ctx.set_option("lbs_cta_tile", cta_tile)
+        new.skin(mh, sb, 0, N, slot0)
+        pos, nt = sb.download()
+        ctx.set_option("lbs_variant", 0)
+        new.skin(mh, sb, 0, N, slot0)
+        ref_pos, ref_nt = sb.download()
+    finally:
+        ctx.set_option("lbs_variant", -1), ctx.set_option("lbs_cta_tile", 0)
+    keep = np.ones(cap, bool)
+    keep[slot0:slot0 + N] = False
+    assert np.array_equal(pos[keep], before_pos[keep]) and np.array_equal(nt[keep], before_nt[keep], equal_nan=True)
+    assert np.abs(pos[~keep] - ref_pos[~keep]).max() <= 4e-6 * max(1.0, float(np.abs(ref_pos).max()))
+    ok = np.isfinite(ref_nt[~keep])
+    assert np.abs(nt[~keep][ok] - ref_nt[~keep][ok]).max() <= 4e-6
+    for x in (old, new):
+        x.close()
+    sb.close()
 
 
 @pytest.mark.parametrize("variant", [0, 2, 3])
