@@ -1579,6 +1579,16 @@ namespace pcl
             float4 na = *reinterpret_cast<const float4*>(&vr[0].px), nb = *reinterpret_cast<const float4*>(&vr[0].nx);
             float4 nt_ = *reinterpret_cast<const float4*>(&vr[0].nz);
             uint4  nd = *reinterpret_cast<const uint4*>(&vr[0].w3);
+            // The previous superchunk's tile is handed to the store warp HERE, not right behind its column stores: the proxy
+            // fence (MEMBAR + FENCE.VIEW.ASYNC) and bar.arrive wait for those stores to drain - 11 % of a compute warp's time
+            // when issued at once (profiles/r1_lbs_v6_*).  Behind the record loads of the next superchunk the drain has had a few
+            // dozen cycles: +1 %.  Any later (behind the first vertex's matrix reloads -1.3 %, behind its blend -1 %, behind the whole
+            // vertex -3 %) the tensor stores start too late.
+            if (s > 0)
+            {
+                fence_async_smem();
+                named_arrive(1 + (s - 1) % LBS_C_TILES, LBS_C_THREADS);
+            }
 #pragma unroll
             for (int j = 0; j < LBS_C_VPW; j++)
             {
@@ -1657,11 +1667,8 @@ namespace pcl
                 for (int q = 0; q < 6; q++)
                     *reinterpret_cast<float4*>(tb + off_n[q]) = on[q];
             }
-            // (handing the tile over one vertex later, so that the proxy fence finds the column stores already drained, was
-            // measured 3 % slower: the tensor stores start later and the compute warps wait longer for a free tile)
-            // (one proxy fence in the store warp after the barrier instead of one per compute warp: +0.8 %, not adopted)
-            fence_async_smem();
-            named_arrive(1 + b, LBS_C_THREADS);
         }
+        fence_async_smem();
+        named_arrive(1 + (n_steps - 1) % LBS_C_TILES, LBS_C_THREADS);
     }
 } // namespace pcl
