@@ -1584,7 +1584,9 @@ namespace pcl
             // when issued at once (profiles/r1_lbs_v6_*).  Behind the record loads of the next superchunk the drain has had a few
             // dozen cycles: +1 %.  Any later (behind the first vertex's matrix reloads -1.3 %, behind its blend -1 %, behind the whole
             // vertex -3 %) the tensor stores start too late.
-            if (s > 0)
+            // (Only with whole-warp tiles: with 2 or 4 vertex streams per warp the late hand-over costs 3 % / 20 %.)
+            constexpr bool LATE_HANDOVER = T == 32;
+            if (LATE_HANDOVER && s > 0)
             {
                 fence_async_smem();
                 named_arrive(1 + (s - 1) % LBS_C_TILES, LBS_C_THREADS);
@@ -1667,8 +1669,16 @@ namespace pcl
                 for (int q = 0; q < 6; q++)
                     *reinterpret_cast<float4*>(tb + off_n[q]) = on[q];
             }
+            if (!LATE_HANDOVER)
+            {
+                fence_async_smem();
+                named_arrive(1 + b, LBS_C_THREADS);
+            }
         }
-        fence_async_smem();
-        named_arrive(1 + (n_steps - 1) % LBS_C_TILES, LBS_C_THREADS);
+        if (T == 32)
+        {
+            fence_async_smem();
+            named_arrive(1 + (n_steps - 1) % LBS_C_TILES, LBS_C_THREADS);
+        }
     }
 } // namespace pcl
