@@ -131,6 +131,12 @@ int pcl_batch_destroy(pcl_batch* b);
  * clip 0, phase 0, weight 1, length 1, mask -1 (= every bone enabled).  Synchronous. */
 int pcl_batch_set(pcl_batch* b, int64_t first, int64_t count, const int32_t* clip_ids, const float* phase,
                   const float* weight, const float* clip_len, const int32_t* mask_ids);
+/* The per-frame part of pcl_batch_set - the fields gameplay code rewrites every frame, BlendState::blend_ratio and
+ * blend_weight (resource/res_type/data/blend_state.h:32-45) - without stalling the caller: phase / weight ([count][K], either may
+ * be NULL) are copied into a pinned staging buffer owned by the batch and enqueued on the compute stream, ordered before the
+ * next pose; the call returns without waiting for the GPU (it waits only for the previous staging copy to have left the
+ * buffer), and the caller's arrays may be reused as soon as it returns. */
+int pcl_batch_set_frame_async(pcl_batch* b, int64_t first, int64_t count, const float* phase, const float* weight);
 int pcl_batch_get_phases(pcl_batch* b, int64_t first, int64_t count, float* phase /*[count][K]*/);
 /* ratio += dt / length; ratio -= floor(ratio)   (animation_component.cpp:19-21), on the device */
 int pcl_batch_advance(pcl_batch* b, float dt, int32_t mode);

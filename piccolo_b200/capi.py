@@ -47,6 +47,7 @@ SIGNATURES = {
     "pcl_batch_create": (C.c_int, [_vp, C.c_int32, _i64, C.c_int32, C.POINTER(_vp)]),
     "pcl_batch_destroy": (C.c_int, [_vp]),
     "pcl_batch_set": (C.c_int, [_vp, _i64, _i64, _ip, _fp, _fp, _fp, _ip]),
+    "pcl_batch_set_frame_async": (C.c_int, [_vp, _i64, _i64, _fp, _fp]),
     "pcl_batch_get_phases": (C.c_int, [_vp, _i64, _i64, _fp]),
     "pcl_batch_advance": (C.c_int, [_vp, C.c_float, C.c_int32]),
     "pcl_batch_pose": (C.c_int, [_vp]),
@@ -238,6 +239,12 @@ class Batch:
         for a in arrs:
             assert a is None or a.size == count * self.K, "arrays must be [count][K]"
         self.ctx._ck(self.ctx.L.pcl_batch_set(self.h, first, count, _i(arrs[0]), _f(arrs[1]), _f(arrs[2]), _f(arrs[3]), _i(arrs[4])))
+
+    def set_frame_async(self, phase=None, weight=None, first=0):
+        """Per-frame inputs without a host stall (pcl_batch_set_frame_async)."""
+        arrs = [_c32(phase, np.float32), _c32(weight, np.float32)]
+        count = next(a.size // self.K for a in arrs if a is not None)
+        self.ctx._ck(self.ctx.L.pcl_batch_set_frame_async(self.h, first, count, _f(arrs[0]), _f(arrs[1])))
 
     def phases(self, first=0, count=None) -> np.ndarray:
         count = self.N - first if count is None else count

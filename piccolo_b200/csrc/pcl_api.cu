@@ -106,6 +106,8 @@ struct pcl_batch
     float*    d_derived = nullptr;
     float4*   d_export  = nullptr;
     long long export_cap = 0; // instances
+    float*      h_stage = nullptr;  // pinned [2][N*K] staging of pcl_batch_set_frame_async
+    cudaEvent_t ev_stage = nullptr; // the last staging copy has left h_stage
     pcl_pool* pool = nullptr;     // d_palette points into this pool (not owned) when attached
     int32_t*  d_order = nullptr;  // [N] frame-coherent visiting order of the pose kernel (allocated on first use)
     int32_t*  d_ohist = nullptr;  // [2][ORDER_MAX_BUCKETS] histogram (kept zero between launches) and scatter cursors
@@ -940,6 +942,10 @@ extern "C"
         else
             cudaFree(b->d_palette);
         cudaFree(b->d_derived), cudaFree(b->d_export), cudaFree(b->d_order), cudaFree(b->d_ohist);
+        if (b->h_stage)
+            cudaFreeHost(b->h_stage);
+        if (b->ev_stage)
+            cudaEventDestroy(b->ev_stage);
         delete b;
         return PCL_OK;
     }
@@ -1146,6 +1152,42 @@ extern "C"
             return rc;
         if (clip_len && (rc = put_f(b->d_len, clip_len)))
             return rc;
+        return PCL_OK;
+    }
+
+    int pcl_batch_set_frame_async(pcl_batch* b, int64_t first, int64_t count, const float* phase, const float* weight)
+    {
+        if (!b || first < 0 || count < 0 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_set_frame_async: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        PCL_CK(c, cudaSetDevice(c->device));
+        const int    K = b->K;
+        const size_t n = (size_t)b->N * K;
+        if (!b->h_stage)
+        {
+            PCL_CK(c, cudaHostAlloc((void**)&b->h_stage, 2 * n * sizeof(float), cudaHostAllocDefault));
+            PCL_CK(c, cudaEventCreateWithFlags(&b->ev_stage, cudaEventDisableTiming));
+        }
+        else
+            PCL_CK(c, cudaEventSynchronize(b->ev_stage)); // the previous frame's inputs have been read out of the staging buffer
+        const float* src[2] = {phase, weight};
+        float*       dst[2] = {b->d_phase, b->d_weight};
+        for (int a = 0; a < 2; a++)
+        {
+            if (!src[a])
+                continue;
+            float* st = b->h_stage + a * n;
+            if (K == 1)
+                std::memcpy(st, src[a], (size_t)count * sizeof(float));
+            else
+                for (int64_t i = 0; i < count; i++)
+                    for (int k = 0; k < K; k++)
+                        st[(size_t)k * count + i] = src[a][i * K + k]; // [count][K] -> [K][count], the device layout
+            for (int k = 0; k < K; k++)
+                PCL_CK(c, cudaMemcpyAsync(dst[a] + (size_t)k * b->N + first, st + (size_t)k * count, (size_t)count * sizeof(float),
+                                          cudaMemcpyHostToDevice, c->compute));
+        }
+        PCL_CK(c, cudaEventRecord(b->ev_stage, c->compute));
         return PCL_OK;
     }
 

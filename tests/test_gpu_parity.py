@@ -325,6 +325,35 @@ def test_pose_register_allocation_variants_agree(ctx, player_dev, oracle, player
     assert_mats_close(got[2], ref, tol=MAT_TOL if K == 1 else 2e-5)
 
 
+@pytest.mark.parametrize("K", [1, 2])
+def test_set_frame_async_equals_set(ctx, player_dev, K):
+    """pcl_batch_set_frame_async: the per-frame inputs through the batch's pinned staging buffer, enqueued without a host
+    stall; same device state as pcl_batch_set, for whole batches and sub-ranges, frame after frame."""
+    skel, clip = player_dev
+    N = 1000
+    rng = np.random.default_rng(K)
+    a, b = ctx.batch(skel, N, K), ctx.batch(skel, N, K)
+    ids = np.full((N, K), clip, np.int32)
+    a.set(clip_ids=ids), b.set(clip_ids=ids)
+    for frame in range(4):
+        ph = rng.uniform(0, 1, (N, K)).astype(np.float32)
+        w = rng.uniform(0.1, 1, (N, K)).astype(np.float32)
+        a.set(phase=ph, weight=w)
+        if frame % 2 == 0:
+            b.set_frame_async(phase=ph, weight=w)
+        else:  # two sub-ranges, the caller's arrays scribbled over right after the call
+            p0, w0 = ph[:333].copy(), w[:333].copy()
+            b.set_frame_async(phase=p0, weight=w0, first=0)
+            p0[:] = -1.0
+            w0[:] = -1.0
+            b.set_frame_async(phase=ph[333:], weight=None, first=333)
+            b.set_frame_async(phase=None, weight=w[333:], first=333)
+        a.pose(), b.pose()
+        assert np.array_equal(a.phases(), b.phases())
+        assert np.array_equal(a.download_palette(), b.download_palette())
+    a.close(), b.close()
+
+
 def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, player):
     """The opt-in shared-memory size is a property of (device, kernel), not of a context: a second context that needs less
     must not shrink what the first one launches with (regression: 'invalid argument' on the first context's next pose)."""
