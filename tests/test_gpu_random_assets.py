@@ -102,3 +102,54 @@ def test_random_assets_pose_matches_oracle(oracle, seed):
             b.close()
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_meshes_skin_like_the_oracle(oracle, seed):
+    """LBS fuzz: random skeleton size (2..330 bones: whole-warp, 16- and 8-instance tiles, lane-per-vertex fallback), random vertex
+    count, bindings with 0..4 influences per vertex, empty slots (index 0), zero, negative and unnormalised weights, ragged
+    instance counts, both output sets, whatever kernel the launcher picks."""
+    from piccolo_b200 import capi
+    rng = np.random.default_rng(1000 + seed)
+    J = int([2, 7, 40, 64, 82, 83, 120, 165, 200, 256, 330, 58][seed])
+    V = int(rng.integers(1, 6000))
+    N = int([1, 5, 161, 197, 300, 163, 170, 250, 164, 180, 168, 333][seed])
+    sk = A.make_synthetic_skeleton(J, branching=2 + seed % 3, seed=seed)
+    cl, am = A.make_synthetic_clip(sk, 9, seed=seed + 1)
+    pos = rng.uniform(-1, 1, (V, 3)).astype(np.float32)
+    nrm = rng.normal(size=(V, 3)).astype(np.float32)
+    tan = rng.normal(size=(V, 3)).astype(np.float32)
+    idx = rng.integers(0, J + 1, (V, 4)).astype(np.int32)          # 0 = empty slot
+    w = rng.uniform(0.0, 2.0, (V, 4)).astype(np.float32)
+    w[rng.uniform(size=(V, 4)) < 0.3] = 0.0                         # unused influences
+    w[rng.uniform(size=(V, 4)) < 0.02] *= -1.0                      # gated out by the shader's weight > 0
+    if V > 3:
+        w[3] = 0.0                                                  # a vertex nothing drives: position 0, normal NaN
+        idx[2] = 0
+    mesh = A.MeshData(pos, nrm, tan, np.zeros((V, 2), np.float32), np.arange(V, dtype=np.int32), idx, w)
+    ctx = capi.Context(0)
+    try:
+        skel = ctx.upload_skeleton(sk)
+        clip = ctx.upload_clip(skel, cl, am)
+        mh = ctx.upload_mesh(mesh, J)
+        b = ctx.batch(skel, N, 1)
+        b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=rng.uniform(0, 1, N).astype(np.float32))
+        b.pose()
+        pal = b.download_palette()
+        for flags in (capi.PCL_SKIN_POS_NRM_TAN, capi.PCL_SKIN_POS):
+            sb = ctx.skinbuf(mh, V, N, flags)
+            b.skin(mh, sb)
+            gp, gnt = sb.download()
+            sb.close()
+            for i in sorted(set([0, N // 2, N - 1])):
+                rp, rn, rt = oracle.lbs(mesh, oracle.palette_slots(pal[i]))
+                radius = max(1.0, float(np.abs(rp).max()))
+                assert np.abs(gp[i] - rp).max() <= 1e-4 * radius
+                if gnt is not None:
+                    ok = np.isfinite(rn).all(axis=1) & np.isfinite(rt).all(axis=1)
+                    assert np.array_equal(np.isfinite(gnt[i]).all(axis=1), ok)
+                    # normals of nearly cancelling blends are ill-conditioned: compare where the blended vector is not tiny
+                    assert np.abs(gnt[i][ok, :3] - rn[ok]).max() <= 2e-3 and np.abs(gnt[i][ok, 3:] - rt[ok]).max() <= 2e-3
+        b.close()
+    finally:
+        ctx.close()
