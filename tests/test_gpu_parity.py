@@ -841,3 +841,51 @@ def test_palette_pool_across_two_gpus_under_torchrun(tmp_path):
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
     assert line["identical"] is True and line["world"] == 2
+
+
+def test_two_contexts_driven_from_two_threads(player):
+    """Two contexts on one GPU, each driven by its own host thread at the same time (ctypes releases the GIL in every call):
+    different skeletons, so the shared constant bank of the step-ordered pose kernel changes hands on every launch; the results
+    must be those of the sequential runs."""
+    import threading
+    from piccolo_b200 import capi
+    sk, cl, am, mk = player
+    sk2 = A.make_synthetic_skeleton(40, branching=3, seed=4)
+    cl2, am2 = A.make_synthetic_clip(sk2, 11, seed=5)
+    jobs = [(sk, cl, am, 3001), (sk2, cl2, am2, 2500)]
+
+    def run(job, rounds, out):
+        s, c, m, n = job
+        ctx = capi.Context(0)
+        try:
+            skel = ctx.upload_skeleton(s)
+            clip = ctx.upload_clip(skel, c, m)
+            mesh = A.make_player_mesh(s, V=1500, seed=n)
+            mh = ctx.upload_mesh(mesh, s.J)
+            b = ctx.batch(skel, n, 1)
+            sb = ctx.skinbuf(mh, mesh.V, n, capi.PCL_SKIN_POS_NRM_TAN)
+            b.set(clip_ids=np.full((n, 1), clip, np.int32), phase=np.linspace(0, 0.95, n, dtype=np.float32))
+            for _ in range(rounds):
+                b.tick(1.0 / 60.0, capi.PCL_ADVANCE_ALL)
+                b.skin(mh, sb)
+            out.append((b.download_palette(), sb.download()[0]))
+            sb.close(), b.close()
+        except Exception as e:  # surfaced by the assertion below
+            out.append(e)
+        finally:
+            ctx.close()
+
+    want = []
+    for j in jobs:
+        o = []
+        run(j, 25, o)
+        want.append(o[0])
+    got = [[], []]
+    th = [threading.Thread(target=run, args=(jobs[i], 25, got[i])) for i in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for i in range(2):
+        assert not isinstance(got[i][0], Exception), got[i][0]
+        assert np.array_equal(got[i][0][0], want[i][0]) and np.array_equal(got[i][0][1], want[i][1])
