@@ -377,6 +377,9 @@ namespace pcl
     // normalise (pcl_math.cuh) ptxas schedules across whole bones and the registers are worth more than the warps:
     // 1.36 / 1.40 / 1.44 ms, and 33 us instead of 50 us for 10 k instances.  Two clips per instance still prefer 12 warps for the
     // largest crowds (2.04 vs 2.23 ms at 1 M) and 8 below (0.236 vs 0.254 ms at 100 k); the launcher picks.
+#ifndef PCL_POSE_PREFETCH2
+#define PCL_POSE_PREFETCH2 1
+#endif
     constexpr int POSE_S_THREADS = 128;
     // SORTED: lane l of warp w works on instance order[32 w + l] instead of 32 w + l.  The order groups instances by the
     // (clip, frame) their phase falls in, so the 32 key gathers of a warp collapse onto one or two addresses (broadcast)
@@ -440,15 +443,22 @@ namespace pcl
 
         // software pipeline: clamp values one group ahead, keys one bone ahead (register budget allows it for K <= 2)
         constexpr bool PREFETCH = K <= 2;
+        // One clip per instance and the 255-register form: keys TWO bones ahead (two rotating buffers; POSE_G is even, so a
+        // bone's buffer is its position in the group modulo 2) - one bone's worth of work did not cover a miss to L2
+        constexpr int  PD = (PCL_POSE_PREFETCH2 && K == 1 && MB == 2) ? 2 : 1;
         int4    hic_cur[K], hic_nxt[K];
-        KeyPair nk[PREFETCH ? K : 1];
+        KeyPair nk[PREFETCH ? K * PD : 1];
 #pragma unroll
         for (int k = 0; k < K; k++)
         {
             hic_cur[k] = __ldg(reinterpret_cast<const int4*>(st[k].hic));
             hic_nxt[k] = hic_cur[k];
             if (PREFETCH)
+            {
                 nk[k] = fetch_keys(st[k], 0, hic_decode(hic_cur[k].x));
+                if (PD == 2)
+                    nk[K + k] = fetch_keys(st[k], 1, hic_decode(hic_cur[k].y));
+            }
         }
 
         for (int s0 = 0; s0 < par.n_steps_padded; s0 += POSE_G)
@@ -475,7 +485,7 @@ namespace pcl
                 for (int k = 0; k < K; k++)
                 {
                     hcur[k] = pick4(hic_cur[k], g);
-                    ck[k]   = PREFETCH ? nk[k] : fetch_keys(st[k], s, hic_decode(hcur[k]));
+                    ck[k]   = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s, hic_decode(hcur[k]));
                 }
                 // this bone's samples first (they consume the keys requested one bone ago) ...
                 float3 P[K], S[K];
@@ -484,11 +494,13 @@ namespace pcl
                 for (int k = 0; k < K; k++)
                     sample_keys(ck[k], st[k].r, P[k], S[k], Q[k]);
                 // ... then the next bone's keys are requested; they land while the rest of this bone is computed
-                if (PREFETCH && s + 1 < par.J)
+                if (PREFETCH && s + PD < par.J)
                 {
 #pragma unroll
                     for (int k = 0; k < K; k++)
-                        nk[k] = fetch_keys(st[k], s + 1, hic_decode(g + 1 < POSE_G ? pick4(hic_cur[k], g + 1) : hic_nxt[k].x), opaque_zero(Q[k].w));
+                        nk[(PD == 2 ? (g & 1) * K : 0) + k] =
+                            fetch_keys(st[k], s + PD, hic_decode(g + PD < POSE_G ? pick4(hic_cur[k], g + PD) : pick4(hic_nxt[k], g + PD - POSE_G)),
+                                       opaque_zero(Q[k].w));
                 }
                 TRS loc; // resetSkeleton -> Node::resetToInitialPose, skeleton.cpp:45, node.cpp:197-206
                 loc.p = make_float3(rec.bpos.x, rec.bpos.y, rec.bpos.z), loc.q = Quat {rec.brot.x, rec.brot.y, rec.brot.z, rec.brot.w};
