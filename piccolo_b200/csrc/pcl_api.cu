@@ -1453,9 +1453,10 @@ extern "C"
             const bool fits3 = cT && m.max_slot * 3 <= 0xffff && out->has_tmaps;
             if (var < 0)
             {
-                // measured on the player mesh (tools/lbs_sweep.py): below ~200 instances the long per-CTA vertex walk of the
-                // crowd kernels (a ~35 us floor) loses to the lane-per-vertex kernel, which spreads over many more CTAs
-                var = (fits3 && count >= 160) ? 3 : ((fits && !fits3 && count >= 160) ? 2 : 0);
+                // measured (tools/lbs_sweep.py; player, 120- and 256-bone skeletons): with the finer vertex splits small launches
+                // get, the TMA-store kernel is level with the lane-per-vertex kernel at 16 instances and ahead from 32 (128
+                // player instances: 19 us against 30 us); lbs_inst_kernel (no tensor maps available) keeps its ~35 us floor
+                var = (fits3 && count >= 32) ? 3 : ((fits && !fits3 && count >= 160) ? 2 : 0);
             }
             if (var == 3)
             {
@@ -1486,8 +1487,12 @@ extern "C"
                     int vs = c->opt_lbs_vsplit;
                     if (vs == 0)
                     {
-                        // at least 32 superchunks per CTA: finer splits measured slower (palette reloads, pipeline fills)
-                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(16, q.n_sc / 32));
+                        // at least 32 superchunks per CTA: finer splits measured slower (palette reloads, pipeline fills) - unless the
+                        // launch is so small that it would leave SMs idle; then down to 8 superchunks per CTA
+                        int min_sc = 32;
+                        while (min_sc > 8 && full * std::min<long long>(64, q.n_sc / min_sc) < 2LL * c->sm_count)
+                            min_sc >>= 1;
+                        const int max_vs = (int)std::max<long long>(1, std::min<long long>(min_sc == 32 ? 16 : 64, q.n_sc / min_sc));
                         double    best   = -1.0;
                         for (int cand = 1; cand <= max_vs; cand++)
                         {

@@ -588,7 +588,7 @@ def test_lbs_ring_slots_and_linearity(ctx, player_dev, player, variant):
     mesh = A.make_player_mesh(player[0], V=16380, seed=1)
     m2 = A.MeshData(mesh.pos * np.float32(2.0), mesh.nrm, mesh.tan, mesh.uv, mesh.index_buffer, mesh.bind_idx, mesh.bind_w)
     h1, h2 = ctx.upload_mesh(mesh, 58), ctx.upload_mesh(m2, 58)
-    N, C = 160, 32  # variant 3 works on whole 32-instance tiles (a ragged remainder is handed to the variant-2 kernel)
+    N, C = 160, 32
     b = ctx.batch(skel, N, 1)
     b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=np.linspace(0, 1, N, dtype=np.float32))
     b.pose()
