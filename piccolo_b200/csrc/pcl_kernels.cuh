@@ -23,7 +23,7 @@ namespace pcl
         int32_t joint; // bone position in bones_map; palette slot = joint + 1
         int32_t psrc;  // parent's derived TRS: -1 root, -2 result of the previous step (still in registers), >= 0 smem slot
         int32_t store; // smem slot to keep this bone's derived TRS in for later children, or -1
-        int32_t pad;
+        int32_t pstep; // processing step of the parent (-1 root): pose_level_kernel's parent lookup
         float4  bpos, brot, bscl;  // bind TRS (brot = normalised (w,x,y,z)), Node::m_initial_*
         float4  ib0, ib1, ib2;     // inverse bind rows 0..2 (Node::m_inverse_Tpose)
     };
@@ -61,9 +61,10 @@ namespace pcl
         const int32_t* mask_ids; // [K][N]  (-1 = all enabled)
         float4*        palette;  // [N][pitch][3]
         float*         derived;  // [N][J][10] or nullptr
+        const int32_t* sched;    // [n_rounds][POSE_L_WARPS] step index or -1 (pose_level_kernel)
         const int32_t* order;    // [N] visiting order (frame-coherent, see order_* kernels) or nullptr = 0, 1, 2, ...
         long long      N;
-        int32_t        J, pitch, nslot, n_steps_padded;
+        int32_t        J, pitch, nslot, n_steps_padded, n_rounds;
         float          dt;
         int32_t        advance; // 0, PCL_ADVANCE_FIRST_ONLY, PCL_ADVANCE_ALL
     };
@@ -639,6 +640,112 @@ namespace pcl
                 }
             }
             __syncwarp();
+        }
+    }
+
+    // -------------------------------------------------------------------------------------------
+    // pose kernel for SMALL crowds (one clip per instance): bones of one hierarchy level in parallel.
+    //
+    // pose_simple_kernel gives every instance one lane, which walks all J bones: 58 x ~1000 cycles = 30 us however few
+    // instances there are - the time of ONE AnimationComponent::tick on the host.  Bones of the same depth do not depend on each
+    // other, so here a CTA of POSE_L_WARPS warps shares 32 instances: in every round each warp takes one bone of the current
+    // level (the schedule is built at upload: level by level, ceil(width / warps) rounds per level), derived transforms are
+    // exchanged through shared memory ([step][component][lane]) and a __syncthreads() closes the round.  The player's 58 bones
+    // in 13 levels (widths 1,1,1,3,3,3,5,5,4,2,10,10,10) take 16 rounds instead of 58 steps.  Same device functions, same
+    // operation order per bone as the other pose kernels - the results are bit-identical; only worth it while the crowd leaves
+    // SMs idle (the launcher uses it up to ~3 CTAs per SM), because at narrow levels most warps wait.
+    // -------------------------------------------------------------------------------------------
+    constexpr int POSE_L_WARPS = 8;
+    __host__ __device__ inline size_t pose_l_smem_bytes(int J) { return (size_t)J * 10 * 32 * sizeof(float); }
+
+    __global__ void __launch_bounds__(POSE_L_WARPS * 32) pose_level_kernel(const PoseParams par)
+    {
+        extern __shared__ __align__(16) float smem[];
+        const int       lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const long long inst0 = (long long)blockIdx.x * 32;
+        const bool      active = (inst0 + lane) < par.N;
+        const long long inst   = min(inst0 + lane, par.N - 1); // idle lanes shadow the last instance, never store
+
+        const ClipRec cr = par.clips[__ldg(par.clip_ids + inst)];
+        float         ph = par.phase[inst];
+        if (par.advance != 0)
+        {
+            ph += par.dt / __ldg(par.clip_len + inst); // animation_component.cpp:19-21
+            ph -= floorf(ph);
+        }
+        const float exact = ph * (float)cr.total_frame_m1; // skeleton.cpp:52-55
+        SimpleSlot  st;
+        st.lo = (int)floorf(exact), st.hi = (int)ceilf(exact), st.r = exact - (float)st.lo;
+        st.keys = cr.keys_step, st.hic = cr.hic_step, st.F = cr.F, st.w = 1.0f, st.mask_off = -1;
+        float4* pal = par.palette + (size_t)inst * par.pitch * 3;
+        if (warp == 0 && active)
+        {
+            pal[0] = make_float4(1, 0, 0, 0), pal[1] = make_float4(0, 1, 0, 0), pal[2] = make_float4(0, 0, 1, 0); // slot 0 = identity
+        }
+        __syncthreads(); // every warp has read the old phase before warp 0 replaces it
+        if (warp == 0 && active && par.advance != 0)
+            par.phase[inst] = ph;
+
+        // software pipeline over the warp's own rounds: keys one round ahead, clamp values two rounds ahead (each is a dependent
+        // global load; a round of arithmetic covers one of them)
+        const int32_t* my = par.sched + warp;
+        int            s_cur = __ldg(my), s_nxt = par.n_rounds > 1 ? __ldg(my + POSE_L_WARPS) : -1;
+        int            h_nxt = s_nxt >= 0 ? __ldg(st.hic + s_nxt) : 0;
+        KeyPair        k_cur = fetch_keys(st, max(s_cur, 0), hic_decode(__ldg(st.hic + max(s_cur, 0))));
+        for (int r = 0; r < par.n_rounds; r++)
+        {
+            const int     s = s_cur;
+            const KeyPair k = k_cur;
+            // next round's keys, the round after's clamp value
+            const int s_nn = r + 2 < par.n_rounds ? __ldg(my + (r + 2) * POSE_L_WARPS) : -1;
+            if (s_nxt >= 0)
+                k_cur = fetch_keys(st, s_nxt, hic_decode(h_nxt));
+            h_nxt = s_nn >= 0 ? __ldg(st.hic + s_nn) : 0;
+            s_cur = s_nxt, s_nxt = s_nn;
+            if (s >= 0)
+            {
+                const StepRec& rec = c_steps[s];
+                float3         P, S;
+                Quat           Q;
+                sample_keys(k, st.r, P, S, Q);
+                TRS loc; // Node::resetToInitialPose + rotate(LOCAL) / scale / translate(AREN), as in pose_simple_kernel
+                loc.p = make_float3(rec.bpos.x, rec.bpos.y, rec.bpos.z), loc.q = Quat {rec.brot.x, rec.brot.y, rec.brot.z, rec.brot.w};
+                loc.s = make_float3(rec.bscl.x, rec.bscl.y, rec.bscl.z);
+                loc.q = qmul(loc.q, qnormalise(Q));
+                loc.s = loc.s * S;
+                loc.p = loc.p + P;
+                TRS der;
+                if (rec.pstep < 0)
+                    der = loc;
+                else
+                {
+                    const float* sp = smem + (size_t)rec.pstep * 320 + lane;
+                    TRS          pt;
+                    pt.p = make_float3(sp[0], sp[32], sp[64]);
+                    pt.q = Quat {sp[96], sp[128], sp[160], sp[192]};
+                    pt.s = make_float3(sp[224], sp[256], sp[288]);
+                    der  = compose(pt, loc);
+                }
+                float* dp = smem + (size_t)s * 320 + lane;
+                dp[0] = der.p.x, dp[32] = der.p.y, dp[64] = der.p.z;
+                dp[96] = der.q.w, dp[128] = der.q.x, dp[160] = der.q.y, dp[192] = der.q.z;
+                dp[224] = der.s.x, dp[256] = der.s.y, dp[288] = der.s.z;
+                if (active)
+                {
+                    const int bone = rec.joint;
+                    if (par.derived)
+                    {
+                        float* o = par.derived + ((size_t)inst * par.J + bone) * 10;
+                        o[0] = der.p.x, o[1] = der.p.y, o[2] = der.p.z, o[3] = der.q.w, o[4] = der.q.x;
+                        o[5] = der.q.y, o[6] = der.q.z, o[7] = der.s.x, o[8] = der.s.y, o[9] = der.s.z;
+                    }
+                    float4 r0, r1, r2;
+                    palette_rows(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                    float4* row = pal + (size_t)(bone + 1) * 3;
+                    row[0] = r0, row[1] = r1, row[2] = r2;
+                }
+            }
+            __syncthreads();
         }
     }
 

@@ -272,6 +272,7 @@ def test_pose_frame_coherent_order_changes_nothing(ctx, player, K, N):
         w = rng.uniform(0.1, 1, (N, K)).astype(np.float32)
         ln = rng.uniform(0.5, 2.0, (N, K)).astype(np.float32)
         out = {}
+        c2.set_option("pose_level", 0)  # the property is about the lane-per-instance kernel: same kernel, another visiting order
         for mode in (0, 1):
             c2.set_option("pose_sort", mode)
             b = c2.batch(skel, N, K)
@@ -354,6 +355,50 @@ def test_set_frame_async_equals_set(ctx, player_dev, K):
     a.close(), b.close()
 
 
+@pytest.mark.parametrize("shape", ["player", "chain", "star", "bushy200"])
+def test_level_parallel_pose_kernel_matches_the_lane_kernels(ctx, player, oracle, shape):
+    """pose_level: small one-clip crowds are posed level by level, 8 warps sharing 32 instances.  Same device functions per bone as
+    the lane-per-instance kernels, but compiled in another context, so nvcc contracts a few other multiply-adds: palettes and
+    derived transforms agree to a few ulp (2e-6 scaled, five times tighter than the gate against the reference), the advanced
+    phases to the bit - for pose and tick, whole and ragged tiles, on a chain (one bone per level), a star (one huge level)
+    and a bushy 200-bone tree."""
+    from piccolo_b200 import capi
+    if shape == "player":
+        sk, cl, am, _ = player
+    else:
+        J, br = {"chain": (40, 1), "star": (90, 89), "bushy200": (200, 3)}[shape]
+        sk = A.make_synthetic_skeleton(J, branching=br, seed=11)
+        cl, am = A.make_synthetic_clip(sk, 13, seed=12)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    for N in (1, 33, 500):
+        ph = np.random.default_rng(N).uniform(0, 1, N).astype(np.float32)
+        ln = np.random.default_rng(N + 1).uniform(0.5, 2.0, N).astype(np.float32)
+        out = {}
+        for mode in (0, 1):
+            ctx.set_option("pose_level", mode)
+            try:
+                b = ctx.batch(skel, N, 1)
+                b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph, clip_len=ln)
+                b.keep_derived(True)
+                b.pose()
+                r = [b.download_palette(), b.download_derived()]
+                b.tick(1.0 / 30.0, capi.PCL_ADVANCE_FIRST_ONLY)
+                b.tick(0.0421, capi.PCL_ADVANCE_ALL)
+                r += [b.download_palette(), b.phases()]
+                out[mode] = r
+                b.close()
+            finally:
+                ctx.set_option("pose_level", -1)
+        assert np.array_equal(out[0][3], out[1][3])  # phases
+        assert_mats_close(out[1][0], out[0][0], tol=2e-6)
+        assert_mats_close(out[1][2], out[0][2], tol=2e-6)
+        d0, d1 = out[0][1], out[1][1]
+        assert np.abs(d0 - d1).max() <= 2e-6 * max(1.0, float(np.abs(d0).max()))
+        ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((N, 1), np.int32), ph)
+        assert_mats_close(out[1][0], ref)
+
+
 def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, player):
     """The opt-in shared-memory size is a property of (device, kernel), not of a context: a second context that needs less
     must not shrink what the first one launches with (regression: 'invalid argument' on the first context's next pose)."""
@@ -370,7 +415,8 @@ def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, pla
     finally:
         c2.close()
     b = gpu_pose(ctx, skel, np.full((N, 1), clip), ph)
-    assert np.array_equal(a, b) and np.array_equal(a[:40], small)
+    assert np.array_equal(a, b)
+    assert_mats_close(small, a[:40], tol=2e-6)  # 40 instances take the level-parallel kernel: same values to a few ulp
 
 
 def test_pose_is_independent_of_batch_composition(ctx, player_dev):
@@ -382,7 +428,13 @@ def test_pose_is_independent_of_batch_composition(ctx, player_dev):
     big.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph)
     big.pose()
     sel = np.random.default_rng(0).choice(N, 2000, replace=False)
-    small = gpu_pose(ctx, skel, np.full((2000, 1), clip), ph[sel])
+    ctx.set_option("pose_level", 0)  # same kernel for both crowd sizes: bit-identical; the small-crowd kernel: a few ulp (below)
+    try:
+        small = gpu_pose(ctx, skel, np.full((2000, 1), clip), ph[sel])
+    finally:
+        ctx.set_option("pose_level", -1)
+    small_level = gpu_pose(ctx, skel, np.full((2000, 1), clip), ph[sel])
+    assert_mats_close(small_level, small, tol=2e-6)
     for chunk in range(0, 2000, 500):
         idx = sel[chunk:chunk + 500]
         lo, hi = idx.min(), idx.max() + 1
