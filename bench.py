@@ -16,9 +16,12 @@ that skin all instances (4 ring chunks).  Instances shard across GPUs with no co
 `value`  : device-resident steps, timed with CUDA events on the library's compute stream, max over ranks.
 `e2e`    : same step through the C ABI with HOST buffers: per-step host->device upload of every
            instance's phases and weights, and device->host download of every instance's AnimationResult
-           (58 4x4 matrices) into pinned memory, double-buffered (frame i's result lands while frame
-           i + 1 is computed; one sync at the end of the timed region); skinned streams stay on the
-           device like the reference's vertex-shader output does.
+           (58 joint matrices, rows 0..2 = 48 B each: row 3 is the constant 0 0 0 1 and is filled in by the
+           host mirror) into pinned memory, double-buffered (frame i's result lands while frame i + 1 is
+           computed; one sync at the end of the timed region); skinned streams stay on the device like the
+           reference's vertex-shader output does.  `e2e.host_link_GBps` is the D2H rate this needs from the
+           host link over all ranks, `e2e.host_link_ceiling_GBps` the rate of bare pinned copies of the same
+           size issued by all ranks at once, measured in the same run.
 `roofline`: the LBS kernel (dominant), algorithmic bytes / measured launch time vs the measured HBM peak.
 `cpu_baseline` / --impl reference: the reference's own Skeleton code (oracle/_ref) + the mesh.vert
            restatement on the host cores.
@@ -101,15 +104,13 @@ class ClockSampler:
 
 def build_workload(first, n_inst):
     """Instances [first, first + n_inst) of the global crowd (per-instance inputs depend only on the global id,
-    so a rank's shard is identical to the same range of an unsharded run)."""
-    from piccolo_b200 import assets as A
+    so a rank's shard is identical to the same range of an unsharded run).  piccolo_b200/workloads.py holds the
+    definitions; tests/test_gpu_full_size.py checks the same arrays against the oracle."""
+    from piccolo_b200 import assets as A, workloads as W
     sk, cl, am, mk = A.load_player()
-    run = A.make_variant_clip(cl, 17, seed=1234)
+    run = W.config3_clips(cl)[1]
     mesh = A.make_player_mesh(sk, V=V_PLAYER, seed=42)
-    i = np.arange(first, first + n_inst, dtype=np.float64)
-    w = np.modf(i * 0.7548776662)[0].astype(np.float32)
-    weight = np.stack([w, np.float32(1) - w], 1)
-    phase = np.stack([np.modf(i * 0.6180339887)[0], np.modf(i * 0.6180339887 + 0.5)[0]], 1).astype(np.float32)
+    phase, weight = W.config3_inputs(first, n_inst)
     return sk, cl, run, am, mk, mesh, phase, weight
 
 
@@ -127,14 +128,21 @@ def lbs_algorithmic_bytes(count, V, J, out_bytes):
     return count * (V * out_bytes + (J + 1) * 48) + V * 68
 
 
-def other_configs(ctx, capi, sk, cl, am, skel, clip0, peak):
-    """configs[1] (10 k instances, single clip, pose only), configs[3] (1 M-instance crowd, 8 mixed clips, random phases,
-    pose only; this GPU's shard when sharded) and configs[4] (256 joints x 49 998 vertices LBS stress, N = 512)."""
-    from piccolo_b200 import assets as A
+def other_configs(ctx, capi, grp, sk, cl, am, mk, skel, clip0, peak, with_cpu):
+    """The other BASELINE.json configs, each beside the reference's CPU figure for the same work when `with_cpu`:
+      configs[1]  10 000 instances, single clip, pose only                                  (rank 0)
+      configs[3]  1 M-instance crowd, 8 mixed clips, random phases, pose only, SHARDED over all ranks (strong scaling:
+                  every rank poses shard_range(1 000 000, world, rank); time = max over ranks, barrier-bracketed)
+      configs[4]  256 joints x 49 998 vertices LBS stress: the sweep N in {1, 8, 64, 512, 4096} x {POS, POS+NRM+TAN}
+                  on the random-binding mesh (worst case) and on a coherent mesh                 (rank 0)
+    Parity for the same arrays at the same sizes: tests/test_gpu_full_size.py."""
+    from piccolo_b200 import workloads as W
+    from piccolo_b200.sharding import shard_range
     out = {}
+    rank, world = grp.rank, grp.world
 
-    def time_it(fn, reps):
-        for _ in range(3):
+    def time_it(fn, reps, warm=3):
+        for _ in range(warm):
             fn()
         ctx.sync()
         ctx.timer_begin()
@@ -142,43 +150,105 @@ def other_configs(ctx, capi, sk, cl, am, skel, clip0, peak):
             fn()
         return ctx.timer_end() / reps
 
+    cpu_tick = None
+    if with_cpu and rank == 0:
+        cpu_tick = cpu_tick_rate(sk, cl, am, mk, budget_s=3.0)
+
     # config 2
-    n = 10000
-    b = ctx.batch(skel, n, 1)
-    b.set(clip_ids=np.full((n, 1), clip0, np.int32), phase=np.modf(np.arange(n) * 0.6180339887)[0].astype(np.float32))
-    ms = time_it(b.pose, 50)
-    out["config2_10k_pose"] = {"ms": round(ms, 4), "instances_per_s": round(n / ms * 1e3), "joints_per_s": round(n * sk.J / ms * 1e3),
-                               "GBps": round(n * (12 + 60 * 48) / ms / 1e6, 1)}
+    if rank == 0:
+        n = 10000
+        b = ctx.batch(skel, n, 1)
+        b.set(clip_ids=np.full((n, 1), clip0, np.int32), phase=W.config2_inputs(0, n))
+        ms = time_it(b.pose, 50)
+        gb = n * (12 + 60 * 48) / ms / 1e6
+        out["config2_10k_pose"] = {"ms": round(ms, 4), "instances_per_s": round(n / ms * 1e3), "joints_per_s": round(n * sk.J / ms * 1e3),
+                                   "GBps": round(gb, 1), "frac": round(gb / peak, 4)}
+        if cpu_tick:
+            out["config2_10k_pose"]["cpu_baseline"] = cpu_tick
+        b.close()
+    # config 4, sharded
+    total = 1000000
+    first, count = shard_range(total, world, rank)
+    clips = [clip0] + [ctx.upload_clip(skel, c, am) for c in W.config4_clips(cl)[1:]]
+    pick, phase = W.config4_inputs(first, count, total)
+    b = ctx.batch(skel, count, 1)
+    b.set(clip_ids=np.int32(clips)[pick], phase=phase)
+    for _ in range(3):
+        b.pose()
+    ctx.sync()
+    grp.barrier()
+    reps = 10
+    ctx.timer_begin()
+    for _ in range(reps):
+        b.pose()
+    my_ms = ctx.timer_end() / reps
+    grp.barrier()
+    ms = grp.max(my_ms)
     b.close()
-    # config 4
-    n = 1000000
-    clips = [clip0] + [ctx.upload_clip(skel, A.make_variant_clip(cl, f, seed=100 + i), am) for i, f in enumerate((17, 23, 29, 31, 37, 41, 47))]
-    rng = np.random.default_rng(7)
-    b = ctx.batch(skel, n, 1)
-    b.set(clip_ids=np.int32(clips)[rng.integers(0, 8, (n, 1))], phase=rng.uniform(0, 1, (n, 1)).astype(np.float32))
-    ms = time_it(b.pose, 10)
-    gb = n * (12 + 60 * 48) / ms / 1e6
-    out["config4_1M_mixed_clips_pose"] = {"ms": round(ms, 4), "instances_per_s": round(n / ms * 1e3), "joints_per_s": round(n * sk.J / ms * 1e3),
-                                          "GBps": round(gb, 1), "frac": round(gb / peak, 4)}
-    b.close()
-    # config 5
-    sk5 = A.make_synthetic_skeleton(256)
-    cl5, am5 = A.make_synthetic_clip(sk5, 32)
-    mesh5 = A.make_synthetic_mesh(sk5, V=49998)
-    s5 = ctx.upload_skeleton(sk5)
-    c5 = ctx.upload_clip(s5, cl5, am5)
-    m5 = ctx.upload_mesh(mesh5, 256)
-    n = 512
-    b = ctx.batch(s5, n, 1)
-    b.set(clip_ids=np.full((n, 1), c5, np.int32), phase=np.linspace(0, 1, n, endpoint=False, dtype=np.float32))
-    b.pose()
-    sb5 = ctx.skinbuf(m5, mesh5.V, n, capi.PCL_SKIN_POS_NRM_TAN)
-    ms = time_it(lambda: b.skin(m5, sb5), 10)
-    gb = (n * (mesh5.V * 36 + 257 * 48) + mesh5.V * 68) / ms / 1e6
-    out["config5_256j_50kv_lbs_N512"] = {"ms": round(ms, 4), "vertices_per_s": round(n * mesh5.V / ms * 1e3), "GBps": round(gb, 1), "frac": round(gb / peak, 4),
-                                         "note": "random 4-bone bindings (worst case for bone reuse); lbs_cta_kernel with 8-instance tiles (257 palette slots)"}
-    sb5.close(), b.close()
+    if rank == 0:
+        gb = total * (12 + 60 * 48) / ms / 1e6
+        out["config4_1M_mixed_clips_pose_sharded"] = {
+            "ms": round(ms, 4), "rank0_ms": round(my_ms, 4), "n_gpus": world, "instances_per_gpu": count, "scaling": "strong",
+            "instances_per_s": round(total / ms * 1e3), "joints_per_s": round(total * sk.J / ms * 1e3),
+            "GBps_aggregate": round(gb, 1), "frac_per_gpu": round(gb / world / peak, 4)}
+        if cpu_tick:
+            out["config4_1M_mixed_clips_pose_sharded"]["cpu_baseline"] = cpu_tick
+    # config 5 sweep
+    if rank == 0:
+        sweep = {}
+        for label, coherent in (("random_bindings", False), ("coherent_mesh", True)):
+            sk5, cl5, am5, mesh5 = W.config5_assets(coherent)
+            s5 = ctx.upload_skeleton(sk5)
+            c5 = ctx.upload_clip(s5, cl5, am5)
+            m5 = ctx.upload_mesh(mesh5, sk5.J)
+            rows = []
+            pal_for_cpu = None
+            for n in W.CONFIG5_SWEEP_N:
+                b = ctx.batch(s5, n, 1)
+                b.set(clip_ids=np.full((n, 1), c5, np.int32), phase=W.config5_phases(n))
+                ms_pose = time_it(b.pose, 10)
+                if pal_for_cpu is None or len(pal_for_cpu) < 64:
+                    m = capi.expand_3x4(b.download_palette3x4(count=min(n, 64)))
+                    pal_for_cpu = np.concatenate([np.tile(np.eye(4, dtype=np.float32).reshape(1, 1, 16), (len(m), 1, 1)), m], 1)
+                for fl, name, ob in ((capi.PCL_SKIN_POS, "POS", 12), (capi.PCL_SKIN_POS_NRM_TAN, "POS+NRM+TAN", 36)):
+                    sb5 = ctx.skinbuf(m5, mesh5.V, n, fl)
+                    ms = time_it(lambda: b.skin(m5, sb5), 20 if n <= 512 else 10)
+                    gb = (n * (mesh5.V * ob + (sk5.J + 1) * 48) + mesh5.V * 68) / ms / 1e6
+                    rows.append({"N": n, "out": name, "ms": round(ms, 4), "pose_ms": round(ms_pose, 4), "vertices_per_s": round(n * mesh5.V / ms * 1e3),
+                                 "GBps": round(gb, 1), "frac": round(gb / peak, 4)})
+                    sb5.close()
+                b.close()
+            sweep[label] = rows
+            if with_cpu:
+                sweep[label + "_cpu_baseline"] = cpu_lbs_rate(mesh5, pal_for_cpu, budget_s=3.0)
+        out["config5_256j_50kv_lbs_sweep"] = sweep
     return out
+
+
+def host_link_ceiling(torch, local, nbytes, barrier, max_over_ranks, reps=6):
+    """Aggregate GB/s of bare cudaMemcpyAsync device -> pinned host copies of `nbytes`, every rank copying at once
+    (barrier on both sides, CUDA events, max over ranks): the ceiling the end-to-end result download is held against."""
+    try:
+        dev = torch.empty(nbytes, dtype=torch.uint8, device="cuda:%d" % local)
+        host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        st = torch.cuda.Stream(device=local)
+        with torch.cuda.stream(st):
+            host.copy_(dev, non_blocking=True)
+            st.synchronize()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for _ in range(reps):
+                host.copy_(dev, non_blocking=True)
+            e1.record(st)
+            e1.synchronize()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        barrier()
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        del dev, host
+        return round(world * nbytes * reps / (ms * 1e-3) / 1e9, 2)
+    except Exception:
+        return None
 
 
 def bind_to_gpu_numa_node(local):
@@ -239,14 +309,16 @@ def run_ours(args):
     # Double-buffered frame loop, the way a host engine would drive it: frame i's AnimationResult lands in pinned buffer i % 2
     # while frame i + 1 is computed; the per-frame inputs go through the batch's pinned staging buffer without a host stall.
     # Every step still uploads all of its inputs and downloads every instance's result; the timed region ends with a sync.
-    host_pal = [ctx.pinned((N, sk.J, 16), np.float32) for _ in range(2)]
+    host_pal = [ctx.pinned((N, sk.J, 12), np.float32) for _ in range(2)]
+    if args.export_mode:
+        ctx.set_option("export_mode", args.export_mode)
     h_phase, h_weight = phase.copy(), weight.copy()
     frame = [0]
 
     def step_e2e():
         b.set_frame_async(phase=h_phase, weight=h_weight)  # H2D of this step's inputs
         b.pose()
-        b.download_palette(out=host_pal[frame[0] & 1], asynchronous=True)  # D2H of AnimationResult, overlaps the skinning
+        b.download_palette3x4(out=host_pal[frame[0] & 1], asynchronous=True)  # D2H of AnimationResult (rows 0..2), overlaps the skinning
         skin_all()
         frame[0] += 1
 
@@ -311,12 +383,15 @@ def run_ours(args):
     e2e_ms = max_over_ranks(max(e2e_ms, e2e_wall))  # host-side work counts too
     barrier()
 
-    # ---- the other BASELINE.json configs, measured briefly on rank 0's GPU (informational; parity for them is in tests/) ----
+    # ---- what the host link can carry: bare pinned D2H copies of the same size, all ranks at once ---------------------
+    link = host_link_ceiling(torch, local, int(host_pal[0].nbytes), barrier, max_over_ranks)
+
+    # ---- the other BASELINE.json configs (parity for them at these sizes: tests/test_gpu_full_size.py) ----
     others = None
-    if rank == 0 and not args.no_other_configs:
+    if not args.no_other_configs:
         sb.close()  # give the 14.7 GB ring back first
         sb = None
-        others = other_configs(ctx, capi, sk, cl, am, skel, c0, peak)
+        others = other_configs(ctx, capi, grp, sk, cl, am, mk, skel, c0, peak, with_cpu=(world == 1 and not args.no_cpu_baseline))
 
     total = N * world
     out = {
@@ -332,12 +407,15 @@ def run_ours(args):
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": round(total * args.steps / (e2e_ms * 1e-3), 1), "unit": "instances/s",
                 "h2d_bytes_per_step": int(h_phase.nbytes + h_weight.nbytes), "d2h_bytes_per_step": int(host_pal[0].nbytes),
-                "ms_per_step": round(e2e_ms / args.steps, 4)},
+                "ms_per_step": round(e2e_ms / args.steps, 4), "result_layout": "rows 0..2 of each joint matrix (48 B/bone); row 3 = 0 0 0 1 is constant",
+                "export_mode": args.export_mode,
+                "host_link_GBps": round(world * host_pal[0].nbytes * args.steps / (e2e_ms * 1e-3) / 1e9, 2),
+                "host_link_ceiling_GBps": link, "frac_of_ceiling": round(world * host_pal[0].nbytes * args.steps / (e2e_ms * 1e-3) / 1e9 / link, 4) if link else None},
         "roofline": roofline,
         "joints_per_s": round(total * sk.J * args.steps / (ms * 1e-3), 0),
         "skinned_vertices_per_s": round(total * mesh.V * args.steps / (ms * 1e-3), 0),
     }
-    if others:
+    if others and rank == 0:
         out["other_configs"] = others
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(sk, cl, am, mk, mesh, budget_s=args.cpu_budget)
@@ -394,6 +472,43 @@ def cpu_reference_rate(sk, cl, am, mk, mesh, budget_s, threads):
     r_lbs = k / (time.perf_counter() - t0)
     rate = 1.0 / (1.0 / r_pose + 1.0 / r_lbs)
     return rate, "port", "oracle/oracle.c: %d poses on %d threads + %d single-thread LBS passes" % (n, threads, k)
+
+
+def cpu_tick_rate(sk, cl, am, mk, budget_s=3.0):
+    """The reference's full AnimationComponent::tick of the player skeleton (what configs[1] and configs[3] compute per
+    instance; the reference samples one clip whatever the crowd mixes), all host threads, a bounded sample."""
+    from oracle import pyoracle as O
+    threads = os.cpu_count() or 1
+    try:
+        if not O.RefLib.available():
+            return None
+        with tempfile.TemporaryDirectory() as td:
+            ref, h = _ref_session(sk, cl, am, mk, td)
+            r = ref.bench_pose(h, threads, 200, True)
+            per_thread = max(200, int(r * budget_s / threads))
+            r = ref.bench_pose(h, threads, per_thread, True)
+        return {"value": round(r, 1), "unit": "instances/s", "cores": threads, "kind": "reference",
+                "sample": "oracle/_ref: %d full ticks of the 58-bone player skeleton" % (per_thread * threads)}
+    except Exception as e:  # a baseline that cannot run must not take the bench line down
+        return {"error": str(e)[:200]}
+
+
+def cpu_lbs_rate(mesh, palettes, budget_s=3.0):
+    """mesh.vert restatement (reference matrix operators) of `mesh` on all host threads, POS+NRM+TAN, bounded sample."""
+    from oracle import pyoracle as O
+    threads = os.cpu_count() or 1
+    try:
+        if not O.RefLib.available():
+            return None
+        with tempfile.TemporaryDirectory() as td:
+            ref = O.RefLib(td)
+            r = ref.bench_lbs(mesh, palettes[np.arange(threads) % len(palettes)], threads)
+            n = max(threads, int(r * budget_s))
+            r = ref.bench_lbs(mesh, palettes[np.arange(n) % len(palettes)], threads)
+        return {"value": round(r, 2), "unit": "instances/s", "vertices_per_s": round(r * mesh.V), "cores": threads, "kind": "reference",
+                "sample": "oracle/_ref mesh.vert restatement: %d instances x %d vertices" % (n, mesh.V)}
+    except Exception as e:
+        return {"error": str(e)[:200]}
 
 
 def cpu_baseline(sk, cl, am, mk, mesh, budget_s=16.0):
@@ -453,6 +568,7 @@ def main():
     ap.add_argument("--lbs-variant", type=int, default=None)
     ap.add_argument("--lbs-warps", type=int, default=0)
     ap.add_argument("--lbs-vsplit", type=int, default=0)
+    ap.add_argument("--export-mode", type=int, default=0, help="pcl_set_option export_mode for the e2e result download")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-configs", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=16.0)

@@ -172,6 +172,18 @@ int pcl_batch_download_palette(pcl_batch* b, int64_t first, int64_t count, float
 /* Same, enqueued on the context's copy stream after the last pose; returns at once.  host16 must stay
  * valid until pcl_sync().  Overlaps with a following pcl_batch_skin. */
 int pcl_batch_download_palette_async(pcl_batch* b, int64_t first, int64_t count, float* host16);
+/* Compact read-back: rows 0..2 of every joint matrix, [count][J][12] floats (48 B per bone instead of 64), bones_map order,
+ * no identity slot.  Row 3 of every AnimationResult matrix is the constant 0 0 0 1 (Matrix4x4::toMatrix4x4_ of an affine
+ * product, core/math/matrix4.h:98-119; the inverse binds are checked to be affine at upload), so the caller fills it in
+ * on the host - the host mirror's AnimationBatch does - and a quarter of the bytes never crosses the host link.
+ * Asynchronous like pcl_batch_download_palette_async: enqueued on the copy stream behind the last pose, host12 must
+ * stay valid until pcl_sync(); the next pose waits until the palette has been read.  How the bytes travel is the
+ * "export_mode" option (pcl_set_option): 1 = one strided DMA straight out of the device palette (no kernel, no staging
+ * buffer), 2 = a kernel writes into host12 itself, which must then be pinned (pcl_host_alloc / cudaHostAlloc /
+ * cudaHostRegister; pageable memory falls back to 3), 3 = kernel -> device staging buffer -> linear DMA; 0 = auto. */
+int pcl_batch_download_palette3x4_async(pcl_batch* b, int64_t first, int64_t count, float* host12);
+/* the same, synchronous */
+int pcl_batch_download_palette3x4(pcl_batch* b, int64_t first, int64_t count, float* host12);
 /* derived TRS [count][J][10] = P.xyz, Q.wxyz, S.xyz (needs pcl_batch_keep_derived) */
 int pcl_batch_download_derived(pcl_batch* b, int64_t first, int64_t count, float* host10);
 /* device pointer + geometry of the compact palette, for consumers living on the GPU */
@@ -255,7 +267,8 @@ int pcl_batch_push_to_pool(pcl_batch* b, pcl_pool* pool, int64_t first);
  * warp-specialised TMA store pipeline);
  * "lbs_warps" (0 = auto, 8, 12: resident warps per SM of the crowd kernel); "lbs_vsplit" (0 = auto);
  * "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only); "lbs_cta_tile" (0 = auto, 32, 16, 8: instances per
- * CTA of variant 3 - auto takes the largest whose palettes fit in shared memory: 32 up to 82 bones, 16 up to ~165, 8 up to ~340).
+ * CTA of variant 3 - auto takes the largest whose palettes fit in shared memory: 32 up to 82 bones, 16 up to ~165, 8 up to ~340);
+ * "export_mode" (0 = auto, 1, 2, 3: see pcl_batch_download_palette3x4_async).
  * PCL_ERR_INVALID for unknown keys. */
 int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
 

@@ -375,7 +375,7 @@ def make_variant_clip(base: AnimationClip, frames: int, seed: int, max_deg: floa
     return AnimationClip(frames, base.node_count, list(base.names), pk, rk, sk, list(base.node_map), base.skeleton_file_path)
 
 
-def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42) -> MeshData:
+def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42, full4: bool = False) -> MeshData:
     """Synthetic stand-in for the missing robot.mesh_bind.json: a tessellated tube
     (capsule side) around every bone, emitted as FULLY EXPANDED triangles in strip order - three vertices per
     triangle, index_buffer[i] == i, which is the only case in which the reference's per-index binding upload is
@@ -428,14 +428,22 @@ def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42) -> Mesh
         k = V - pos.shape[0]
         pos, nrm, tan = (np.concatenate([a, np.repeat(a[-1:], k, 0)], 0) for a in (pos, nrm, tan))
     pos, nrm, tan = pos[:V], nrm[:V], tan[:V]
-    d = np.linalg.norm(pos[:, None, :] - P[None, :, :], axis=2)  # [V,J]
-    nearest = np.argsort(d, axis=1, kind="stable")[:, :4]
-    dn = np.take_along_axis(d, nearest, 1)
-    on = dn <= 1.6 * dn[:, :1] + 1e-9
+    nearest, dn = np.zeros((V, 4), np.int64), np.zeros((V, 4))
+    for v0 in range(0, V, 8192):  # [V,J] distances in slabs (a 50 k x 256 mesh would need 300 MB at once)
+        d = np.linalg.norm(pos[v0:v0 + 8192, None, :] - P[None, :, :], axis=2)
+        nearest[v0:v0 + 8192] = np.argsort(d, axis=1, kind="stable")[:, :4]
+        dn[v0:v0 + 8192] = np.take_along_axis(d, nearest[v0:v0 + 8192], 1)
+    on = (dn <= 1.6 * dn[:, :1] + 1e-9) | full4
     idx = np.where(on, nearest + 1, 0).astype(np.int32)
     w = np.where(on, 1.0 / (dn + 1e-3), 0.0).astype(F32)
     uv = rng.uniform(0, 1, size=(V, 2))
     return MeshData(pos.astype(F32), nrm.astype(F32), tan.astype(F32), uv.astype(F32), np.arange(V, dtype=np.int32), idx, w)
+
+
+def make_coherent_mesh(skel: SkeletonData, V: int = 49998, seed: int = 11) -> MeshData:
+    """A character-like mesh for any skeleton: make_player_mesh's tubes around the bones, every vertex bound to its FOUR
+    nearest bones with non-zero inverse-distance weights (config 5 asks for 4 non-zero weights per vertex)."""
+    return make_player_mesh(skel, V=V, seed=seed, full4=True)
 
 
 def make_synthetic_skeleton(J: int = 256, branching: int = 3, seed: int = 5) -> SkeletonData:

@@ -58,6 +58,8 @@ SIGNATURES = {
     "pcl_batch_skin": (C.c_int, [_vp, C.c_int32, _vp, _i64, _i64, _i64]),
     "pcl_batch_download_palette": (C.c_int, [_vp, _i64, _i64, _fp]),
     "pcl_batch_download_palette_async": (C.c_int, [_vp, _i64, _i64, _fp]),
+    "pcl_batch_download_palette3x4_async": (C.c_int, [_vp, _i64, _i64, _fp]),
+    "pcl_batch_download_palette3x4": (C.c_int, [_vp, _i64, _i64, _fp]),
     "pcl_batch_download_derived": (C.c_int, [_vp, _i64, _i64, _fp]),
     "pcl_batch_palette_dev": (C.c_int, [_vp, C.POINTER(_vp), _ip, _ip]),
     "pcl_skinbuf_dev": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), _ip]),
@@ -285,6 +287,15 @@ class Batch:
         self.ctx._ck(fn(self.h, first, count, _f(out)))
         return out
 
+    def download_palette3x4(self, first=0, count=None, out=None, asynchronous=False) -> np.ndarray:
+        """Rows 0..2 of every joint matrix, [count][J][12] (row 3 is the constant 0 0 0 1: expand_3x4 adds it)."""
+        count = self.N - first if count is None else count
+        if out is None:
+            out = np.zeros((count, self.J, 12), np.float32)
+        fn = self.ctx.L.pcl_batch_download_palette3x4_async if asynchronous else self.ctx.L.pcl_batch_download_palette3x4
+        self.ctx._ck(fn(self.h, first, count, _f(out)))
+        return out
+
     def download_palette_static(self, first=0, count=None) -> np.ndarray:
         """pcl_batch_download_palette_static: same matrices, staged through the library's fixed device array
         (no device allocation; at most PCL_STATIC_EXPORT_MAX_BYTES per call)."""
@@ -307,6 +318,14 @@ class Batch:
         p, pitch, fps = _vp(), C.c_int32(), C.c_int32()
         self.ctx._ck(self.ctx.L.pcl_batch_palette_dev(self.h, C.byref(p), C.byref(pitch), C.byref(fps)))
         return p.value, pitch.value, fps.value
+
+
+def expand_3x4(m12: np.ndarray) -> np.ndarray:
+    """[..., 12] rows 0..2 -> [..., 16] AnimationResult matrices (row 3 = 0 0 0 1, core/math/matrix4.h:98-119)."""
+    out = np.zeros(m12.shape[:-1] + (16,), np.float32)
+    out[..., :12] = m12
+    out[..., 15] = 1.0
+    return out
 
 
 class Pool:

@@ -90,7 +90,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0;
     void*        h_small = nullptr;  // pinned staging of small synchronous palette read-backs
     bool         debug_sync = false; // PICCOLO_B200_DEBUG_SYNC=1: synchronise after every launch
     int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
@@ -110,6 +110,8 @@ struct pcl_batch
     float*    d_derived = nullptr;
     float4*   d_export  = nullptr;
     long long export_cap = 0; // instances
+    float4*   d_export12 = nullptr; // staging of the compact (3x4) read-back, export_mode 3
+    long long export12_cap = 0;
     float*      h_stage = nullptr;  // pinned [2][N*K] staging of pcl_batch_set_frame_async
     cudaEvent_t ev_stage = nullptr; // the last staging copy has left h_stage
     pcl_pool* pool = nullptr;     // d_palette points into this pool (not owned) when attached
@@ -550,6 +552,8 @@ extern "C"
             c->opt_lbs_inst_tile = v;
         else if (k == "lbs_cta_tile" && (v == 0 || v == 8 || v == 16 || v == 32))
             c->opt_lbs_cta_tile = v;
+        else if (k == "export_mode" && v >= 0 && v <= 3)
+            c->opt_export_mode = v;
         else
             return fail(c, PCL_ERR_INVALID, "pcl_set_option: unknown key or bad value: " + k);
         return PCL_OK;
@@ -981,7 +985,7 @@ extern "C"
             b->pool->attached--;
         else
             cudaFree(b->d_palette);
-        cudaFree(b->d_derived), cudaFree(b->d_export), cudaFree(b->d_order), cudaFree(b->d_ohist);
+        cudaFree(b->d_derived), cudaFree(b->d_export), cudaFree(b->d_export12), cudaFree(b->d_order), cudaFree(b->d_ohist);
         if (b->h_stage)
             cudaFreeHost(b->h_stage);
         if (b->ev_stage)
@@ -1719,6 +1723,80 @@ extern "C"
     int pcl_batch_download_palette_async(pcl_batch* b, int64_t first, int64_t count, float* host16)
     {
         return export_palette(b, first, count, host16, true);
+    }
+
+    // Compact read-back (rows 0..2).  The three ways the bytes can travel are kept selectable ("export_mode") because which
+    // one is best depends on the host link, not on the GPU; measurements in profiles/README.md.
+    static int export_palette3x4(pcl_batch* b, int64_t first, int64_t count, float* host12, bool async)
+    {
+        if (!b || !host12 || first < 0 || count < 1 || first + count > b->N)
+            return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_download_palette3x4: range outside the batch");
+        pcl_ctx* c = b->ctx;
+        if (!b->posed)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_download_palette3x4: pcl_batch_pose / pcl_batch_tick has not run");
+        PCL_CK(c, cudaSetDevice(c->device));
+        const SkelRec& s     = c->skels[b->skel];
+        const size_t   row   = (size_t)s.J * 48;
+        const size_t   bytes = (size_t)count * row;
+        int            mode  = c->opt_export_mode ? c->opt_export_mode : 1;
+        float4*        dev_view = nullptr; // device-side address of host12 when it is pinned
+        if (mode == 2)
+        {
+            cudaPointerAttributes at {};
+            if (cudaPointerGetAttributes(&at, host12) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+                dev_view = (float4*)at.devicePointer;
+            else
+            {
+                (void)cudaGetLastError();
+                mode = 3;
+            }
+        }
+        PCL_CK(c, cudaStreamWaitEvent(c->copy, c->ev_pose, 0));
+        const long long total = count * s.J * 3;
+        if (mode == 1)
+        {
+            // slots 1..J of every palette row are the J matrices in bones_map order: one 2-D copy, rows of J * 48 bytes
+            const char* src = reinterpret_cast<const char*>(b->d_palette) + (size_t)first * s.pitch * 48 + 48;
+            PCL_CK(c, cudaMemcpy2DAsync(host12, row, src, (size_t)s.pitch * 48, row, (size_t)count, cudaMemcpyDeviceToHost, c->copy));
+            PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy)); // the palette is being read until the copy is through
+            c->copy_pending = true;
+        }
+        else if (mode == 2)
+        {
+            export3x4_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, dev_view, first, count, s.J, s.pitch);
+            c->launches++;
+            PCL_POST_LAUNCH(c, c->copy, "export3x4_kernel (pinned destination)");
+            PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy));
+            c->copy_pending = true;
+        }
+        else
+        {
+            if (count > b->export12_cap)
+            {
+                PCL_CK(c, cudaStreamSynchronize(c->copy));
+                cudaFree(b->d_export12);
+                b->d_export12 = nullptr, b->export12_cap = 0;
+                PCL_CK(c, cudaMalloc((void**)&b->d_export12, bytes));
+                b->export12_cap = count;
+            }
+            export3x4_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, b->d_export12, first, count, s.J, s.pitch);
+            c->launches++;
+            PCL_POST_LAUNCH(c, c->copy, "export3x4_kernel");
+            PCL_CK(c, cudaEventRecord(c->ev_copy, c->copy)); // the next pose only waits for the kernel, not for the DMA
+            c->copy_pending = true;
+            PCL_CK(c, cudaMemcpyAsync(host12, b->d_export12, bytes, cudaMemcpyDeviceToHost, c->copy));
+        }
+        if (!async)
+            PCL_CK(c, cudaStreamSynchronize(c->copy));
+        return PCL_OK;
+    }
+    int pcl_batch_download_palette3x4_async(pcl_batch* b, int64_t first, int64_t count, float* host12)
+    {
+        return export_palette3x4(b, first, count, host12, true);
+    }
+    int pcl_batch_download_palette3x4(pcl_batch* b, int64_t first, int64_t count, float* host12)
+    {
+        return export_palette3x4(b, first, count, host12, false);
     }
 
     int pcl_batch_download_derived(pcl_batch* b, int64_t first, int64_t count, float* host10)

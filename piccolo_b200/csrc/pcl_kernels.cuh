@@ -898,6 +898,23 @@ namespace pcl
         out[t] = (r == 3) ? make_float4(0, 0, 0, 1) : palette[((size_t)(first + i) * pitch + b + 1) * 3 + r];
     }
 
+    // compact read-back: rows 0..2 only, [count][J][3] float4 (row 3 of an AnimationResult matrix is the constant 0 0 0 1 and is
+    // filled in on the host).  Per instance this is ONE contiguous run of J * 48 bytes on both sides (slots 1..J of the
+    // palette row), so consecutive threads read and write consecutive 16-byte units: whole 128-byte lines when `out` is a
+    // pinned host buffer written over PCIe.
+    __global__ void export3x4_kernel(const float4* __restrict__ palette, float4* __restrict__ out, long long first, long long count,
+                                     int J, int pitch)
+    {
+        const long long t     = (long long)blockIdx.x * blockDim.x + threadIdx.x; // one thread per float4
+        const int       per   = J * 3;
+        const long long total = count * per;
+        if (t >= total)
+            return;
+        const long long i = t / per;
+        const int       u = (int)(t - i * per);
+        out[t]            = __ldg(palette + (size_t)(first + i) * pitch * 3 + 3 + u);
+    }
+
     // -------------------------------------------------------------------------------------------
     // render hand-off: compact palette -> the per-draw-call joint SSBO of the reference's mesh passes,
     // joint_matrices[1024 * instance_in_draw + slot] (4x4 row-major, <= 64 instances per draw):

@@ -745,6 +745,47 @@ def test_async_palette_download_overlapping_skin_and_next_pose(ctx, player_dev, 
     sb.close(), b.close()
 
 
+@pytest.mark.parametrize("pinned_dst", [True, False])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_compact_3x4_download_all_modes(ctx, player_dev, player, mode, pinned_dst):
+    """pcl_batch_download_palette3x4(_async): rows 0..2 of every AnimationResult matrix, bit-identical to the 4x4 download
+    (whose row 3 is the constant 0 0 0 1), for every way the bytes can travel ("export_mode"), into pinned and pageable
+    memory, for sub-ranges, and overlapped with the skinning and the NEXT frame's pose like bench.py's end-to-end loop."""
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    mesh = A.make_player_mesh(player[0], V=4096, seed=2)
+    mh = ctx.upload_mesh(mesh, 58)
+    N = 5000
+    b = ctx.batch(skel, N, 1)
+    sb = ctx.skinbuf(mh, mesh.V, N, capi.PCL_SKIN_POS)
+    dst = ctx.pinned((N, 58, 12), np.float32) if pinned_dst else np.zeros((N, 58, 12), np.float32)
+    ph = np.random.default_rng(19).uniform(0, 1, (3, N)).astype(np.float32)
+    ctx.set_option("export_mode", mode)
+    try:
+        want = []
+        for r in range(3):
+            b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph[r])
+            b.pose()
+            want.append(b.download_palette())
+            assert np.array_equal(want[r][..., 12:], np.broadcast_to(np.float32([0, 0, 0, 1]), want[r][..., 12:].shape))
+            assert np.array_equal(capi.expand_3x4(b.download_palette3x4()), want[r])  # synchronous form
+            sub = b.download_palette3x4(first=1234, count=77)
+            assert np.array_equal(sub, want[r][1234:1311, :, :12])
+        for r in range(3):
+            b.set(phase=ph[r])
+            b.pose()
+            dst[...] = -1.0
+            b.download_palette3x4(out=dst, asynchronous=True)
+            b.skin(mh, sb)
+            b.set(phase=ph[(r + 1) % 3])  # the next frame is enqueued before the download has been waited for
+            b.pose()
+            ctx.sync()
+            assert np.array_equal(dst, want[r][..., :12]), "3x4 download saw the next frame's palette (mode %d, round %d)" % (mode, r)
+    finally:
+        ctx.set_option("export_mode", 0)
+        sb.close(), b.close()
+
+
 def test_render_handoff_layout(ctx, player_dev):
     """joint_matrices[1024 * instance_in_draw + slot], 64 instances per draw, slot 0 = identity, only J+1 slots touched
     (main_camera_pass.cpp:2284-2298; mesh_component.cpp:72-79)."""
