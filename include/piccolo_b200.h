@@ -165,6 +165,20 @@ int pcl_skinbuf_destroy(pcl_skinbuf* s);
  * slots [slot_first, slot_first+count).  Reads the palette of the last pcl_batch_pose / _tick. */
 int pcl_batch_skin(pcl_batch* b, pcl_mesh mesh, pcl_skinbuf* out, int64_t first, int64_t count, int64_t slot_first);
 
+/* One frame of a SMALL batch in ONE call - the reference's everyday case, a handful of characters each ticked once per
+ * frame (function/framework/object/object.cpp:41-50 -> component/animation/animation_component.cpp:17-25 ->
+ * component/mesh/mesh_component.cpp:68-79): sets the per-frame inputs of ALL instances ([N][K] arrays like pcl_batch_set;
+ * NULL = keep the previous frame's; weight, mask default to 1 / none), samples + poses them, and returns their
+ * AnimationResult rows (host12: [N][J][12], layout of pcl_batch_download_palette3x4) - one kernel launch and one
+ * synchronisation: inputs and rows live in a pinned block the kernel reads and writes in place.  host12 == NULL returns
+ * without waiting; pcl_batch_frame_result waits and copies the rows out.  The device palette is valid afterwards
+ * (pcl_batch_skin, pcl_batch_export_render...).  Inputs given here are separate from pcl_batch_set's device arrays;
+ * phases are advanced by the caller (as AnimationComponent::tick does on the host).  PCL_ERR_UNSUPPORTED when
+ * N * (K * 20 + J * 48) exceeds PCL_FRAME_MAX_BYTES. */
+#define PCL_FRAME_MAX_BYTES (64u << 20)
+int pcl_batch_frame(pcl_batch* b, const int32_t* clip_ids, const float* phase, const float* weight, const int32_t* mask_ids, float* host12);
+int pcl_batch_frame_result(pcl_batch* b, float* host12);
+
 /* ---- readback / interop ----------------------------------------------------------------------- */
 /* AnimationResult for instances [first, first+count): [count][J][16] floats, bones_map order, no
  * identity slot (resource/res_type/components/animation.h:12-29).  Synchronous. */

@@ -52,6 +52,8 @@ SIGNATURES = {
     "pcl_batch_advance": (C.c_int, [_vp, C.c_float, C.c_int32]),
     "pcl_batch_pose": (C.c_int, [_vp]),
     "pcl_batch_tick": (C.c_int, [_vp, C.c_float, C.c_int32]),
+    "pcl_batch_frame": (C.c_int, [_vp, _ip, _fp, _fp, _ip, _fp]),
+    "pcl_batch_frame_result": (C.c_int, [_vp, _fp]),
     "pcl_batch_keep_derived": (C.c_int, [_vp, C.c_int32]),
     "pcl_skinbuf_create": (C.c_int, [_vp, C.c_int32, _i64, C.c_int32, C.POINTER(_vp)]),
     "pcl_skinbuf_destroy": (C.c_int, [_vp]),
@@ -262,6 +264,21 @@ class Batch:
 
     def tick(self, dt, mode=PCL_ADVANCE_FIRST_ONLY):
         self.ctx._ck(self.ctx.L.pcl_batch_tick(self.h, C.c_float(dt), mode))
+
+    def frame(self, clip_ids=None, phase=None, weight=None, mask_ids=None, wait=True):
+        """pcl_batch_frame: set inputs + pose + read the AnimationResult rows back, one launch and one sync (small batches).
+        Returns [N][J][12] (wait=True) or None; frame_result() fetches it later."""
+        arrs = [_c32(clip_ids, np.int32), _c32(phase, np.float32), _c32(weight, np.float32), _c32(mask_ids, np.int32)]
+        for a in arrs:
+            assert a is None or a.size == self.N * self.K, "arrays must be [N][K]"
+        out = np.zeros((self.N, self.J, 12), np.float32) if wait else None
+        self.ctx._ck(self.ctx.L.pcl_batch_frame(self.h, _i(arrs[0]), _f(arrs[1]), _f(arrs[2]), _i(arrs[3]), _f(out)))
+        return out
+
+    def frame_result(self) -> np.ndarray:
+        out = np.zeros((self.N, self.J, 12), np.float32)
+        self.ctx._ck(self.ctx.L.pcl_batch_frame_result(self.h, _f(out)))
+        return out
 
     def attach_pool(self, pool: "Pool", first: int = 0):
         self.ctx._ck(self.ctx.L.pcl_batch_attach_pool(self.h, pool.h, int(first)))

@@ -64,6 +64,7 @@ namespace
 static __device__ __align__(256) unsigned char g_static_export[PCL_STATIC_EXPORT_MAX_BYTES];
 #define PCL_STATIC_MAX_DEVICES 64
 #define PCL_SMALL_EXPORT_BYTES (32u << 10) /* measured: ahead up to ~8 player instances, behind the DMA path from 32 */
+#define PCL_FRAME_DIRECT_BYTES (24u << 10) /* pcl_batch_frame: rows written by the kernel into pinned memory up to 8 player instances */
 static void* g_static_export_addr[PCL_STATIC_MAX_DEVICES]; // device address of the array, per device (0 = not looked up yet)
 
 // Which skeleton's step records currently sit in the device's __constant__ bank (pose_simple_kernel).  The bank is
@@ -114,6 +115,11 @@ struct pcl_batch
     long long export12_cap = 0;
     float*      h_stage = nullptr;  // pinned [2][N*K] staging of pcl_batch_set_frame_async
     cudaEvent_t ev_stage = nullptr; // the last staging copy has left h_stage
+    // pcl_batch_frame: one pinned, device-visible block = the frame's inputs in device layout ([K][N] x 4 arrays) + its result
+    // rows [N][J][12]; the pose kernel reads and writes it in place (no staging copies, no export kernel, no DMA)
+    unsigned char* h_io = nullptr;
+    cudaEvent_t    ev_frame = nullptr; // the last pcl_batch_frame's work is through
+    bool           frame_pending = false;
     pcl_pool* pool = nullptr;     // d_palette points into this pool (not owned) when attached
     int32_t*  d_order = nullptr;  // [N] frame-coherent visiting order of the pose kernel (allocated on first use)
     int32_t*  d_ohist = nullptr;  // [2][ORDER_MAX_BUCKETS] histogram (kept zero between launches) and scatter cursors
@@ -615,8 +621,8 @@ extern "C"
             StepRec&  r  = steps[st];
             r.joint = b, r.psrc = psrc[st], r.store = store[st];
             r.pstep = s.parent[b] < 0 ? -1 : step_of[s.parent[b]];
-            r.bpos = make_float4(bind_pos[3 * b], bind_pos[3 * b + 1], bind_pos[3 * b + 2], 0.f);
-            r.bscl = make_float4(bind_scl[3 * b], bind_scl[3 * b + 1], bind_scl[3 * b + 2], 0.f);
+            r.bA = make_float4(bind_pos[3 * b], bind_pos[3 * b + 1], bind_scl[3 * b], bind_scl[3 * b + 1]);
+            r.bC = make_float4(1.f, bind_scl[3 * b + 2], bind_pos[3 * b + 2], 0.f);
             // Node::setOrientation, node.cpp:71-85: NaN -> identity, else normalise (factor = 1/length; q*factor)
             float w = bind_rot[4 * b], x = bind_rot[4 * b + 1], y = bind_rot[4 * b + 2], z = bind_rot[4 * b + 3];
             if (std::isnan(w) || std::isnan(x) || std::isnan(y) || std::isnan(z))
@@ -626,7 +632,8 @@ extern "C"
                 float factor = 1.0f / std::sqrt(w * w + x * x + y * y + z * z);
                 w = w * factor, x = x * factor, y = y * factor, z = z * factor;
             }
-            r.brot = make_float4(w, x, y, z);
+            r.q01 = make_float4(w, x, y, z);
+            r.q23 = make_float4(-x, w, -z, y);
             const float* m = inv_bind + 16 * (size_t)b;
             r.ib0 = make_float4(m[0], m[1], m[2], m[3]);
             r.ib1 = make_float4(m[4], m[5], m[6], m[7]);
@@ -761,32 +768,36 @@ extern "C"
             if (convert[n] != -1 && next[n] >= 0)
                 simple = false;
         const int            Jp = (J + POSE_G - 1) / POSE_G * POSE_G + POSE_G;
-        std::vector<float4>  skeys;
-        std::vector<int32_t> shic;
+        std::vector<float4>   skeys;
+        std::vector<uint32_t> sanim;
         if (simple)
         {
             skeys.assign((size_t)Jp * F * 3, make_float4(0, 0, 0, 0));
-            shic.assign(Jp, -F);
+            sanim.assign((Jp + 31) / 32, 0u);
             for (int st = 0; st < Jp; st++)
             {
                 const int ch = st < J ? first[sk.order[st]] : -1;
+                if (ch >= 0)
+                    sanim[st >> 5] |= 1u << (st & 31);
                 for (int k = 0; k < F; k++)
                 {
-                    // {p.xyz, s.x} {q.wxyz} {s.y, s.z, -, -}; bones without a channel get the identity track
+                    // {p.x, p.y, s.x, s.y} {q.wxyz} {p.z, s.z, -, -}; bones without a channel get the identity track; beyond its
+                    // clamp (the carried-over prefix minimum, skeleton.cpp:75-87) a track continues with copies of the clamp key
                     float4 kp = make_float4(0, 0, 0, 0), kq = make_float4(1, 0, 0, 0), ks = make_float4(1, 1, 1, 0);
                     if (ch >= 0)
-                        kp = keys[((size_t)ch * F + k) * 3], kq = keys[((size_t)ch * F + k) * 3 + 1], ks = keys[((size_t)ch * F + k) * 3 + 2];
-                    skeys[((size_t)st * F + k) * 3 + 0] = make_float4(kp.x, kp.y, kp.z, ks.x);
+                    {
+                        const int kk = std::min(k, hic[ch]);
+                        kp = keys[((size_t)ch * F + kk) * 3], kq = keys[((size_t)ch * F + kk) * 3 + 1], ks = keys[((size_t)ch * F + kk) * 3 + 2];
+                    }
+                    skeys[((size_t)st * F + k) * 3 + 0] = make_float4(kp.x, kp.y, ks.x, ks.y);
                     skeys[((size_t)st * F + k) * 3 + 1] = kq;
-                    skeys[((size_t)st * F + k) * 3 + 2] = make_float4(ks.y, ks.z, 0.f, 0.f);
+                    skeys[((size_t)st * F + k) * 3 + 2] = make_float4(kp.z, ks.z, 0.f, 0.f);
                 }
-                if (ch >= 0)
-                    shic[st] = hic[ch];
             }
         }
-        // one device blob: keys | first | next | hi_clamp | step-ordered keys | step-ordered clamps
+        // one device blob: keys | first | next | hi_clamp | step-ordered keys | animated-step bits
         const size_t kb = keys.size() * sizeof(float4), fb = (size_t)J * 4, nb = next.size() * 4, hb = hic.size() * 4;
-        const size_t skb = skeys.size() * sizeof(float4), shb = shic.size() * 4;
+        const size_t skb = skeys.size() * sizeof(float4), shb = sanim.size() * 4;
         auto         up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const size_t total = up16(kb) + up16(fb) + up16(nb) + up16(hb) + up16(skb) + up16(shb) + 16;
         ClipHost     ch;
@@ -801,7 +812,7 @@ extern "C"
         if (simple)
         {
             PCL_CK(c, copy_h2d(c, d2, skeys.data(), skb));
-            PCL_CK(c, copy_h2d(c, d2 + up16(skb), shic.data(), shb));
+            PCL_CK(c, copy_h2d(c, d2 + up16(skb), sanim.data(), shb));
         }
         ch.rec.keys           = (const float4*)d;
         ch.rec.first_chan     = (const int32_t*)(d + up16(kb));
@@ -812,7 +823,7 @@ extern "C"
         ch.rec.C              = C;
         ch.rec.simple         = simple ? 1 : 0;
         ch.rec.keys_step      = simple ? (const float4*)d2 : nullptr;
-        ch.rec.hic_step       = simple ? (const int32_t*)(d2 + up16(skb)) : nullptr;
+        ch.rec.anim_step      = simple ? (const uint32_t*)(d2 + up16(skb)) : nullptr;
         ch.rec.bucket_base    = c->n_buckets;
         c->n_buckets += total_frame; // lo = floor(phase * (total_frame - 1)) is one of total_frame values
         sk.n_clips++;
@@ -990,6 +1001,10 @@ extern "C"
             cudaFreeHost(b->h_stage);
         if (b->ev_stage)
             cudaEventDestroy(b->ev_stage);
+        if (b->h_io)
+            cudaFreeHost(b->h_io);
+        if (b->ev_frame)
+            cudaEventDestroy(b->ev_frame);
         delete b;
         return PCL_OK;
     }
@@ -1264,7 +1279,18 @@ extern "C"
         return PCL_OK;
     }
 
-    static int launch_pose(pcl_batch* b, float dt, int32_t advance)
+    // where a launch takes its per-instance inputs from / additionally writes its result rows to (pcl_batch_frame)
+    struct FrameIO
+    {
+        const int32_t* clip_ids;
+        float*         phase;
+        const float*   weight;
+        const float*   len;
+        const int32_t* mask_ids;
+        float4*        out12;
+        bool           out12_written;
+    };
+    static int launch_pose(pcl_batch* b, float dt, int32_t advance, FrameIO* io = nullptr)
     {
         pcl_ctx* c = b->ctx;
         PCL_CK(c, cudaSetDevice(c->device));
@@ -1280,6 +1306,11 @@ extern "C"
         p.steps = s.d_steps, p.clips = c->d_clips, p.masks = s.d_masks;
         p.clip_ids = b->d_clip_ids, p.phase = b->d_phase, p.weight = b->d_weight, p.clip_len = b->d_len;
         p.mask_ids = (b->K > 1 && s.n_masks > 0) ? b->d_mask_ids : nullptr;
+        if (io)
+        {
+            p.clip_ids = io->clip_ids, p.phase = io->phase, p.weight = io->weight, p.clip_len = io->len;
+            p.mask_ids = (b->K > 1 && s.n_masks > 0) ? io->mask_ids : nullptr;
+        }
         p.palette = b->d_palette, p.derived = b->d_derived;
         p.N = b->N, p.J = s.J, p.pitch = s.pitch, p.nslot = s.nslot;
         p.n_steps_padded = (s.J + POSE_G - 1) / POSE_G * POSE_G;
@@ -1317,7 +1348,7 @@ extern "C"
         // (not when the palettes go to another GPU's pool: rows visited in random order over gigabytes of peer memory ran at
         // 69 GB/s against 350 GB/s in instance order, tools/pool_gather_check.py on two B200s)
         const bool remote = b->pool && (!b->pool->owner || b->pool->ctx->device != c->device);
-        bool sorted = simple && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
+        bool sorted = simple && !io && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
                       (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= 262144 && !remote));
         if (sorted)
         {
@@ -1347,9 +1378,11 @@ extern "C"
             const size_t smem_l = pose_l_smem_bytes(s.J);
             const bool   fits_l = simple && b->K == 1 && !sorted && s.d_sched && smem_l <= (size_t)c->max_smem_optin;
             const bool   small  = warps <= 2LL * c->sm_count; // measured: 20.7 us against 31-33 us up to 4 000 player instances, 29 against 32 at 8 000, level at 10 000
-            if (fits_l && (c->opt_pose_level == 1 || (c->opt_pose_level < 0 && small)))
+            if (fits_l && (c->opt_pose_level == 1 || (c->opt_pose_level < 0 && (small || io))))
             {
                 p.sched = s.d_sched, p.n_rounds = s.n_rounds;
+                if (io && io->out12)
+                    p.out12 = io->out12, io->out12_written = true;
                 { int rc__ = ensure_smem(c, (const void*)pose_level_kernel, smem_l); if (rc__) return rc__; }
                 pose_level_kernel<<<(unsigned)warps, POSE_L_WARPS * 32, smem_l, c->compute>>>(p);
                 c->launches++;
@@ -1414,6 +1447,117 @@ extern "C"
         if (!b || (mode != PCL_ADVANCE_FIRST_ONLY && mode != PCL_ADVANCE_ALL))
             return fail(b ? b->ctx : nullptr, PCL_ERR_INVALID, "pcl_batch_tick: bad mode");
         return launch_pose(b, dt, mode);
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // one frame of a SMALL batch in one call (the reference's everyday case: a handful of AnimationComponents)
+    // ------------------------------------------------------------------------------------------
+    static size_t frame_io_bytes(const pcl_batch* b, int J) { return (size_t)b->N * b->K * 4 * 5 + (size_t)b->N * J * 48 + 64; }
+
+    int pcl_batch_frame(pcl_batch* b, const int32_t* clip_ids, const float* phase, const float* weight, const int32_t* mask_ids, float* host12)
+    {
+        if (!b)
+            return PCL_ERR_INVALID;
+        pcl_ctx*       c = b->ctx;
+        const SkelRec& s = c->skels[b->skel];
+        if (frame_io_bytes(b, s.J) > (size_t)PCL_FRAME_MAX_BYTES)
+            return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_frame: the batch is too large for the one-call frame path (PCL_FRAME_MAX_BYTES); use pcl_batch_set_frame_async + pcl_batch_tick + pcl_batch_download_palette3x4_async");
+        PCL_CK(c, cudaSetDevice(c->device));
+        const size_t n = (size_t)b->N * b->K;
+        if (!b->h_io)
+        {
+            if (!clip_ids || !phase)
+                return fail(c, PCL_ERR_INVALID, "pcl_batch_frame: the first call on a batch must pass clip_ids and phase");
+            PCL_CK(c, cudaHostAlloc((void**)&b->h_io, frame_io_bytes(b, s.J), cudaHostAllocDefault)); // unified addressing: the device sees it
+            PCL_CK(c, cudaEventCreateWithFlags(&b->ev_frame, cudaEventDisableTiming));
+            float*   wl = reinterpret_cast<float*>(b->h_io) + 2 * n;
+            int32_t* mk = reinterpret_cast<int32_t*>(b->h_io) + 4 * n;
+            for (size_t i = 0; i < n; i++)
+                wl[i] = 1.f, wl[n + i] = 1.f, mk[i] = -1; // weight, clip length, mask: the defaults of pcl_batch_create
+        }
+        else if (b->frame_pending)
+        {
+            PCL_CK(c, cudaEventSynchronize(b->ev_frame)); // the previous frame's kernel has read its inputs and written its rows
+            b->frame_pending = false;
+        }
+        int32_t* h_clip  = reinterpret_cast<int32_t*>(b->h_io);
+        float*   h_phase = reinterpret_cast<float*>(b->h_io) + n;
+        float*   h_wgt   = reinterpret_cast<float*>(b->h_io) + 2 * n;
+        float*   h_len   = reinterpret_cast<float*>(b->h_io) + 3 * n;
+        int32_t* h_mask  = reinterpret_cast<int32_t*>(b->h_io) + 4 * n;
+        float4*  h_out   = reinterpret_cast<float4*>(b->h_io + ((n * 20 + 63) & ~(size_t)63));
+        const int       K = b->K;
+        const long long N = b->N;
+        for (long long i = 0; i < N; i++) // [N][K] -> the kernels' [K][N]
+            for (int k = 0; k < K; k++)
+            {
+                if (clip_ids)
+                {
+                    const int32_t v = clip_ids[i * K + k];
+                    if (v < 0 || v >= (int)c->clips.size() || c->clips[v].skel != b->skel)
+                        return fail(c, PCL_ERR_INVALID, "pcl_batch_frame: clip id does not belong to the batch's skeleton");
+                    h_clip[(size_t)k * N + i] = v;
+                }
+                if (phase)
+                    h_phase[(size_t)k * N + i] = phase[i * K + k];
+                if (weight)
+                    h_wgt[(size_t)k * N + i] = weight[i * K + k];
+                if (mask_ids)
+                {
+                    int32_t v = mask_ids[i * K + k];
+                    if (v >= 0)
+                    {
+                        if (v >= (int)c->masks.size() || c->masks[v].skel != b->skel)
+                            return fail(c, PCL_ERR_INVALID, "pcl_batch_frame: mask id does not belong to the batch's skeleton");
+                        v = c->masks[v].local;
+                    }
+                    else
+                        v = -1;
+                    h_mask[(size_t)k * N + i] = v;
+                }
+            }
+        // A few characters' rows are written by the pose kernel itself, straight into the pinned block (48-byte pieces over
+        // the host link: fine for kilobytes - one launch, no DMA set-up; measured 6 GB/s, so not beyond).  Larger frames leave
+        // through one strided DMA out of the device palette, like pcl_batch_download_palette3x4.
+        const bool direct = (size_t)N * s.J * 48 <= PCL_FRAME_DIRECT_BYTES;
+        FrameIO    io {h_clip, h_phase, h_wgt, h_len, h_mask, direct ? h_out : nullptr, false};
+        int        rc = launch_pose(b, 0.f, 0, &io);
+        if (rc != PCL_OK)
+            return rc;
+        if (!direct)
+        {
+            const size_t row = (size_t)s.J * 48;
+            PCL_CK(c, cudaMemcpy2DAsync(h_out, row, reinterpret_cast<const char*>(b->d_palette) + 48, (size_t)s.pitch * 48, row, (size_t)N,
+                                        cudaMemcpyDeviceToHost, c->compute));
+        }
+        else if (!io.out12_written) // the launcher could not use the kernel that writes the rows itself: one more small launch
+        {
+            const long long total = N * s.J * 3;
+            export3x4_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->compute>>>(b->d_palette, h_out, 0, N, s.J, s.pitch);
+            c->launches++;
+            PCL_POST_LAUNCH(c, c->compute, "export3x4_kernel (frame block)");
+        }
+        PCL_CK(c, cudaEventRecord(b->ev_frame, c->compute));
+        b->frame_pending = true;
+        return host12 ? pcl_batch_frame_result(b, host12) : PCL_OK;
+    }
+
+    int pcl_batch_frame_result(pcl_batch* b, float* host12)
+    {
+        if (!b || !host12)
+            return PCL_ERR_INVALID;
+        pcl_ctx* c = b->ctx;
+        if (!b->h_io)
+            return fail(c, PCL_ERR_INVALID, "pcl_batch_frame_result: pcl_batch_frame has not run");
+        if (b->frame_pending)
+        {
+            PCL_CK(c, cudaEventSynchronize(b->ev_frame));
+            b->frame_pending = false;
+        }
+        const SkelRec& s = c->skels[b->skel];
+        const size_t   n = (size_t)b->N * b->K;
+        std::memcpy(host12, b->h_io + ((n * 20 + 63) & ~(size_t)63), (size_t)b->N * s.J * 48);
+        return PCL_OK;
     }
 
     int pcl_batch_keep_derived(pcl_batch* b, int32_t enable)

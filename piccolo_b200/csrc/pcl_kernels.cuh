@@ -24,7 +24,11 @@ namespace pcl
         int32_t psrc;  // parent's derived TRS: -1 root, -2 result of the previous step (still in registers), >= 0 smem slot
         int32_t store; // smem slot to keep this bone's derived TRS in for later children, or -1
         int32_t pstep; // processing step of the parent (-1 root): pose_level_kernel's parent lookup
-        float4  bpos, brot, bscl;  // bind TRS (brot = normalised (w,x,y,z)), Node::m_initial_*
+        // bind TRS (Node::m_initial_*) laid out for the packed arithmetic of pcl_math.cuh:
+        float4  bA;    // (p.x, p.y, s.x, s.y)
+        float4  bC;    // (1, s.z, p.z, 0): local (p.z, s.z) = sampled (p.z, s.z) * (1, s.z) + (p.z, 0) in one packed fma
+        float4  q01;   // bind rotation (w, x, y, z), normalised as Node::setOrientation does
+        float4  q23;   // (-x, w, -z, y): helper pairs of the quaternion product with a constant left factor
         float4  ib0, ib1, ib2;     // inverse bind rows 0..2 (Node::m_inverse_Tpose)
     };
 
@@ -41,10 +45,13 @@ namespace pcl
         int32_t total_frame_m1;    // total_frame - 1
         int32_t C;
         int32_t simple;            // every bone is driven by at most one played channel: the step-ordered form below exists
-        // step-ordered form (pose_simple_kernel): one track per processing step, the identity track for bones no
-        // channel drives, so a key's address depends only on (step, frame) - no dependent loads on the hot path
-        const float4*  keys_step;  // [Jp][F][3]
-        const int32_t* hic_step;   // [Jp]  hi_clamp of the step's channel (>= 0), or -F for an identity track (clamp F-1)
+        // step-ordered form (pose_simple_kernel): one track of exactly F keys per processing step - the identity track for
+        // bones no channel drives, and every track CONTINUED WITH COPIES OF ITS KEY hi_clamp up to F keys.  Reading key
+        // min(frame, F - 1) of such a track returns what the clamp of skeleton.cpp:75-87 returns (beyond the clamp lo and hi
+        // name the same key, and interpolating a key with its copy gives the key back exactly), so the two key indices
+        // are computed ONCE per instance and a key's address depends on (step, instance) only - no clamp table on the hot path
+        const float4*   keys_step;  // [Jp][F][3]
+        const uint32_t* anim_step;  // [ceil(Jp / 32)] bit s: a played channel drives step s (blend path: bones no clip animates keep the bind pose)
         int32_t        bucket_base; // first (clip, frame) bucket of this clip in the context-wide numbering (order_* kernels)
         int32_t        pad_[3];
     };
@@ -61,6 +68,8 @@ namespace pcl
         const int32_t* mask_ids; // [K][N]  (-1 = all enabled)
         float4*        palette;  // [N][pitch][3]
         float*         derived;  // [N][J][10] or nullptr
+        float4*        out12;    // [N][J][3] rows 0..2 in bones_map order, or nullptr: pose_level_kernel writes the AnimationResult
+                                 // rows here as well (a pinned host block for pcl_batch_frame: no export kernel, no DMA)
         const int32_t* sched;    // [n_rounds][POSE_L_WARPS] step index or -1 (pose_level_kernel)
         const int32_t* order;    // [N] visiting order (frame-coherent, see order_* kernels) or nullptr = 0, 1, 2, ...
         long long      N;
@@ -72,7 +81,9 @@ namespace pcl
     constexpr int POSE_G = 4; // bones staged in shared memory between two coalesced palette flushes
 
     // per-warp dynamic shared memory, in floats
-    __host__ __device__ inline size_t pose_smem_floats_per_warp(int nslot) { return (size_t)nslot * 10 * 32 + 32 * (POSE_G * 12 + 4); }
+    constexpr int POSE_SLOT_FLOATS = 10 * 32; // one parked derived TRS: 5 pairs x 32 lanes (pose_simple / pose_level: [pair][lane] of 8 bytes)
+    // nslot parked parents + one slot holding the identity transform (the "parent" of a root in pose_simple_kernel)
+    __host__ __device__ inline size_t pose_smem_floats_per_warp(int nslot) { return (size_t)(nslot + 1) * POSE_SLOT_FLOATS + 32 * (POSE_G * 12 + 4); }
 
     struct SlotState // one clip slot of one instance, resident in registers
     {
@@ -120,7 +131,7 @@ namespace pcl
         const long long inst   = min(inst0 + lane, par.N - 1); // idle lanes shadow the last instance, never store
         const bool      active = (inst0 + lane) < par.N;
         float*          slots  = smem + (size_t)wib * pose_smem_floats_per_warp(par.nslot);
-        float*          stage  = slots + (size_t)par.nslot * 10 * 32;
+        float*          stage  = slots + (size_t)(par.nslot + 1) * POSE_SLOT_FLOATS;
         constexpr int   SROW   = POSE_G * 12 + 4; // floats per staged instance row (+4: conflict-free float4 columns)
 
         // ---- per-instance clip slot state (A1 + head of A3) -----------------------------------
@@ -172,10 +183,10 @@ namespace pcl
                 const StepRec* rec  = par.steps + s;
                 const int4     hdr  = __ldg(reinterpret_cast<const int4*>(rec));
                 const int      bone = hdr.x;
-                const float4   bp = __ldg(&rec->bpos), br = __ldg(&rec->brot), bs = __ldg(&rec->bscl);
+                const float4   bA = __ldg(&rec->bA), bC = __ldg(&rec->bC), br = __ldg(&rec->q01);
                 // resetSkeleton -> Node::resetToInitialPose, skeleton.cpp:45, node.cpp:197-206
                 TRS loc;
-                loc.p = make_float3(bp.x, bp.y, bp.z), loc.q = Quat {br.x, br.y, br.z, br.w}, loc.s = make_float3(bs.x, bs.y, bs.z);
+                loc.p = make_float3(bA.x, bA.y, bC.z), loc.q = Quat {br.x, br.y, br.z, br.w}, loc.s = make_float3(bA.z, bA.w, bC.y);
 
                 if (K == 1)
                 {
@@ -262,7 +273,7 @@ namespace pcl
                     TRS par_trs = prev;
                     if (hdr.y >= 0)
                     {
-                        const float* sp = slots + (size_t)hdr.y * 320 + lane;
+                        const float* sp = slots + (size_t)hdr.y * POSE_SLOT_FLOATS + lane;
                         par_trs.p = make_float3(sp[0], sp[32], sp[64]);
                         par_trs.q = Quat {sp[96], sp[128], sp[160], sp[192]};
                         par_trs.s = make_float3(sp[224], sp[256], sp[288]);
@@ -271,7 +282,7 @@ namespace pcl
                 }
                 if (hdr.z >= 0)
                 {
-                    float* sp = slots + (size_t)hdr.z * 320 + lane;
+                    float* sp = slots + (size_t)hdr.z * POSE_SLOT_FLOATS + lane;
                     sp[0] = der.p.x, sp[32] = der.p.y, sp[64] = der.p.z;
                     sp[96] = der.q.w, sp[128] = der.q.x, sp[160] = der.q.y, sp[192] = der.q.z;
                     sp[224] = der.s.x, sp[256] = der.s.y, sp[288] = der.s.z;
@@ -324,10 +335,11 @@ namespace pcl
     //     (q_bind * (1,0,0,0), s_bind * 1, p_bind + 0), so there is no per-bone branching
     //   - the palette flush uses the conflict-free row mapping of the LBS kernel with hoisted addressing
     // -------------------------------------------------------------------------------------------
-    constexpr int POSE_CMAX = 320; // bones whose step records fit the constant bank (320 * 112 B = 35 KB)
+    constexpr int POSE_CMAX = 320; // bones whose step records fit the constant bank (320 * 128 B = 40 KB)
     __constant__ StepRec c_steps[POSE_CMAX];
 
-    // A step-ordered key is 48 bytes: {p.x p.y p.z s.x} {q.w q.x q.y q.z} {s.y s.z - -}.  Only the first 40 are ever
+    // A step-ordered key is 48 bytes: {p.x p.y s.x s.y} {q.w q.x q.y q.z} {p.z s.z - -} - the pair layout of TRSP, so that
+    // the registers of the vector loads ARE the packed operands.  Only the first 40 are ever
     // loaded (128 + 128 + 64 bit), so no loaded register is dead: a dead lane of a vector load gets re-used by
     // ptxas as a scratch register at once, and the write-after-write hazard then stalls the warp for the full
     // load latency right behind the prefetch (seen as long_scoreboard on the first FMUL after the LDGs in
@@ -339,11 +351,22 @@ namespace pcl
     };
     struct SimpleSlot
     {
-        const float4*  keys;
-        const int32_t* hic;
-        int32_t        F, lo, hi, mask_off;
-        float          r, w;
+        const float4*   keys;
+        const uint32_t* anim;
+        uint32_t        F3, lo3, hi3; // keys per track, index of the lower / upper key of this instance: all in 16-byte units (x 3)
+        int32_t         mask_off;
+        float           r, w;
     };
+    // skeleton.cpp:52-55 and :75-87 for the step-ordered tracks (see ClipRec::keys_step)
+    __device__ __forceinline__ void slot_frames(SimpleSlot& st, float ph, int total_frame_m1, int F)
+    {
+        const float exact = ph * (float)total_frame_m1;
+        const int   fl = (int)floorf(exact), ce = (int)ceilf(exact);
+        st.r           = exact - (float)fl;
+        const int h    = max(min(ce, F - 1), 0);
+        const int l    = max(min(fl, h), 0);
+        st.F3 = (uint32_t)F * 3u, st.lo3 = (uint32_t)l * 3u, st.hi3 = (uint32_t)h * 3u;
+    }
     // `after` is an opaque zero derived from a value the caller has just computed.  Adding it to the address
     // pins the loads BEHIND that computation, i.e. behind the consumption of the keys requested one bone ago.
     __device__ __forceinline__ int opaque_zero(float v)
@@ -352,25 +375,79 @@ namespace pcl
         asm volatile("and.b32 %0, %1, 0;" : "=r"(z) : "r"(__float_as_int(v)));
         return z;
     }
-    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int hc, int after = 0)
+    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int after = 0)
     {
-        const int     h  = max(min(st.hi, hc), 0) + after;
-        const int     l  = max(min(st.lo, h), 0);
-        const float4* kl = st.keys + ((size_t)s * st.F + l) * 3;
-        const float4* kh = st.keys + ((size_t)s * st.F + h) * 3;
-        KeyPair       k;
+        const uint32_t base = (uint32_t)s * st.F3 + (uint32_t)after; // a clip's step-ordered copy is far below 2^32 units
+        const float4*  kl   = st.keys + (base + st.lo3);
+        const float4*  kh   = st.keys + (base + st.hi3);
+        KeyPair        k;
         k.a0 = __ldg(kl), k.q0 = __ldg(kl + 1), k.c0 = __ldg(reinterpret_cast<const float2*>(kl + 2));
         k.a1 = __ldg(kh), k.q1 = __ldg(kh + 1), k.c1 = __ldg(reinterpret_cast<const float2*>(kh + 2));
         return k;
     }
-    __device__ __forceinline__ void sample_keys(const KeyPair& k, float r, float3& P, float3& S, Quat& Q)
+    // (Tried and rejected: staging the keys with cp.async - LDGSTS, one 80-byte shared-memory cell per lane and clip, four bones
+    // in flight, completion per copy group instead of per scoreboard.  1 M instances 1.18 -> 2.04 ms: in the frame-coherent
+    // order the 32 lanes of a plain load share one or two addresses and coalesce into one request, the per-lane copies do not.)
+    // skeleton.cpp:88-95 on pairs: Vector3::lerp for position and scale, Quaternion::nLerp (shortest path) for the rotation
+    struct SampleP
     {
-        P = lerp3(make_float3(k.a0.x, k.a0.y, k.a0.z), make_float3(k.a1.x, k.a1.y, k.a1.z), r);
-        S = lerp3(make_float3(k.a0.w, k.c0.x, k.c0.y), make_float3(k.a1.w, k.c1.x, k.c1.y), r);
-        Q = qnlerp(r, Quat {k.q0.x, k.q0.y, k.q0.z, k.q0.w}, Quat {k.q1.x, k.q1.y, k.q1.z, k.q1.w});
+        f2    pxy, sxy, pzsz;
+        QuatP q;
+    };
+    __device__ __forceinline__ SampleP sample_keys(const KeyPair& k, float r)
+    {
+        SampleP s;
+        s.pxy  = lerp2(pk(k.a0.x, k.a0.y), pk(k.a1.x, k.a1.y), r);
+        s.sxy  = lerp2(pk(k.a0.z, k.a0.w), pk(k.a1.z, k.a1.w), r);
+        s.pzsz = lerp2(pk(k.c0.x, k.c0.y), pk(k.c1.x, k.c1.y), r);
+        s.q    = qnlerpp(r, QuatP {pk(k.q0.x, k.q0.y), pk(k.q0.z, k.q0.w)}, QuatP {pk(k.q1.x, k.q1.y), pk(k.q1.z, k.q1.w)});
+        return s;
     }
-    __device__ __forceinline__ int pick4(const int4& v, int g) { return g == 0 ? v.x : (g == 1 ? v.y : (g == 2 ? v.z : v.w)); }
-    __device__ __forceinline__ int hic_decode(int v) { return v < 0 ? -1 - v : v; } // identity tracks are stored as -F
+    // Node::resetToInitialPose + rotate(LOCAL) / scale / translate(AREN) (node.cpp:197-206,135-157,182-186,107-132) of one
+    // sampled (or blended) delta: q_l = q_bind * normalise(q), s_l = s_bind * s, p_l = p_bind + p
+    __device__ __forceinline__ TRSP local_pose(const StepRec& rec, f2 pxy, f2 sxy, f2 pzsz, const QuatP& q)
+    {
+        TRSP loc;
+        loc.q = qmul_constp(pk(rec.q01.x, rec.q01.y), pk(rec.q01.z, rec.q01.w), pk(rec.q23.x, rec.q23.y), pk(rec.q23.z, rec.q23.w), qnormalisep(q));
+        loc.pxy  = add2p(pk(rec.bA.x, rec.bA.y), pxy);
+        loc.sxy  = mul2p(pk(rec.bA.z, rec.bA.w), sxy);
+        loc.pzsz = fma2p(pzsz, pk(rec.bC.x, rec.bC.y), pk(rec.bC.z, rec.bC.w));
+        return loc;
+    }
+    __device__ __forceinline__ TRSP bind_pose(const StepRec& rec)
+    {
+        TRSP loc;
+        loc.q    = QuatP {pk(rec.q01.x, rec.q01.y), pk(rec.q01.z, rec.q01.w)};
+        loc.pxy  = pk(rec.bA.x, rec.bA.y);
+        loc.sxy  = pk(rec.bA.z, rec.bA.w);
+        loc.pzsz = pk(rec.bC.z, rec.bC.y);
+        return loc;
+    }
+    // parked derived transforms: five 8-byte pairs, [pair][lane] (consecutive lanes on consecutive 8-byte units: conflict-free
+    // 64-bit accesses that read and write the packed registers as they are)
+    __device__ __forceinline__ TRSP load_trs(const float* slot, int lane)
+    {
+        const f2* s2 = reinterpret_cast<const f2*>(slot) + lane;
+        TRSP      t;
+        t.pxy = s2[0], t.sxy = s2[32], t.pzsz = s2[64], t.q.wx = s2[96], t.q.yz = s2[128];
+        return t;
+    }
+    __device__ __forceinline__ void store_trs(float* slot, int lane, const TRSP& t)
+    {
+        f2* s2 = reinterpret_cast<f2*>(slot) + lane;
+        s2[0] = t.pxy, s2[32] = t.sxy, s2[64] = t.pzsz, s2[96] = t.q.wx, s2[128] = t.q.yz;
+    }
+    __device__ __forceinline__ TRSP identity_trs()
+    {
+        TRSP t;
+        t.pxy = pk(0.f, 0.f), t.sxy = pk(1.f, 1.f), t.pzsz = pk(0.f, 1.f), t.q = QuatP {pk(1.f, 0.f), pk(0.f, 0.f)};
+        return t;
+    }
+    __device__ __forceinline__ void store_derived(float* o, const TRSP& t)
+    {
+        o[0] = lo(t.pxy), o[1] = hi(t.pxy), o[2] = lo(t.pzsz), o[3] = lo(t.q.wx), o[4] = hi(t.q.wx);
+        o[5] = lo(t.q.yz), o[6] = hi(t.q.yz), o[7] = lo(t.sxy), o[8] = hi(t.sxy), o[9] = hi(t.pzsz);
+    }
 
     // MB = resident blocks per SM the register allocation is made for (__launch_bounds__): 2 -> 255 registers, 3 -> 168, 4 -> 128.
     // With IEEE sqrt / division in the normalisations (slow-path branches after every one of them) the kernel hid its latencies
@@ -378,8 +455,17 @@ namespace pcl
     // normalise (pcl_math.cuh) ptxas schedules across whole bones and the registers are worth more than the warps:
     // 1.36 / 1.40 / 1.44 ms, and 33 us instead of 50 us for 10 k instances.  Two clips per instance still prefer 12 warps for the
     // largest crowds (2.04 vs 2.23 ms at 1 M) and 8 below (0.236 vs 0.254 ms at 100 k); the launcher picks.
-#ifndef PCL_POSE_PREFETCH2
-#define PCL_POSE_PREFETCH2 1
+    // palette flush stores: 0 plain, 1 streaming (st.global.cs), 2 cache-global (st.global.cg).  Measured (tools/pose_bench.py,
+    // profiles/README.md): streaming stores -13 % at 100 k instances (K = 1 and K = 2), -4 % at 1 M; .cg within noise.
+#ifndef PCL_POSE_ST_MODE
+#define PCL_POSE_ST_MODE 1
+#endif
+#if PCL_POSE_ST_MODE == 1
+#define PCL_PST(p, v) __stcs((p), (v))
+#elif PCL_POSE_ST_MODE == 2
+#define PCL_PST(p, v) __stcg((p), (v))
+#else
+#define PCL_PST(p, v) (*(p) = (v))
 #endif
     constexpr int POSE_S_THREADS = 128;
     // SORTED: lane l of warp w works on instance order[32 w + l] instead of 32 w + l.  The order groups instances by the
@@ -402,8 +488,9 @@ namespace pcl
         const int       inst32 = (int)inst;
         const int       ni     = (int)min(32LL, par.N - inst0);
         float*          slots  = smem + (size_t)wib * pose_smem_floats_per_warp(par.nslot);
-        float*          stage  = slots + (size_t)par.nslot * 10 * 32;
+        float*          stage  = slots + (size_t)(par.nslot + 1) * POSE_SLOT_FLOATS;
         constexpr int   SROW   = POSE_G * 12 + 4;
+        store_trs(slots + (size_t)par.nslot * POSE_SLOT_FLOATS, lane, identity_trs()); // slot nslot: what a root composes with
 
         SimpleSlot st[K];
 #pragma unroll
@@ -419,9 +506,8 @@ namespace pcl
                 if (active)
                     par.phase[o] = ph;
             }
-            const float exact = ph * (float)cr.total_frame_m1; // skeleton.cpp:52-55
-            st[k].lo = (int)floorf(exact), st[k].hi = (int)ceilf(exact), st[k].r = exact - (float)st[k].lo;
-            st[k].keys = cr.keys_step, st[k].hic = cr.hic_step, st[k].F = cr.F;
+            slot_frames(st[k], ph, cr.total_frame_m1, cr.F);
+            st[k].keys = cr.keys_step, st[k].anim = cr.anim_step;
             st[k].w = (K > 1) ? __ldg(par.weight + o) : 1.0f;
             const int mid = (K > 1 && par.mask_ids) ? __ldg(par.mask_ids + o) : -1;
             st[k].mask_off = mid < 0 ? -1 : mid * par.J;
@@ -438,37 +524,49 @@ namespace pcl
         float4*   g_f2 = par.palette + (size_t)(inst0 + fa + fc4) * par.pitch * 3 + 8 + fd;
         const size_t rowstep = (size_t)par.pitch * 3 * 4; // float4 per 4 instances
         const size_t rowsz   = (size_t)par.pitch * 3;     // float4 per instance
+        // SORTED: staging row r belongs to the instance lane r works on.  The twelve rows this lane flushes are fixed for the
+        // whole kernel, so their instance numbers are fetched once, here, instead of with twelve shuffles per group
+        constexpr bool HOIST = SORTED && MB == 2; // (the 168- and 128-register forms have no room for twelve more registers)
+        uint32_t       frow[HOIST ? 12 : 1];
+        if (HOIST)
+        {
+#pragma unroll
+            for (int gq = 0; gq < 4; gq++)
+            {
+                frow[gq * 3 + 0] = (uint32_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8);
+                frow[gq * 3 + 1] = (uint32_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8 + 4);
+                frow[gq * 3 + 2] = (uint32_t)__shfl_sync(0xffffffffu, inst32, fa + fc4 + gq * 8);
+            }
+        }
 
-        TRS prev;
-        prev.p = make_float3(0, 0, 0), prev.q = Quat {1, 0, 0, 0}, prev.s = make_float3(1, 1, 1);
+        TRSP prev = identity_trs(); // derived transform of the previous step = the parent of a chain's next bone
 
-        // software pipeline: clamp values one group ahead, keys one bone ahead (register budget allows it for K <= 2)
+        // software pipeline: keys one bone ahead (register budget allows it for K <= 2)
         constexpr bool PREFETCH = K <= 2;
         // One clip per instance and the 255-register form: keys TWO bones ahead (two rotating buffers; POSE_G is even, so a
         // bone's buffer is its position in the group modulo 2) - one bone's worth of work did not cover a miss to L2
-        constexpr int  PD = (PCL_POSE_PREFETCH2 && K == 1 && MB == 2) ? 2 : 1;
-        int4    hic_cur[K], hic_nxt[K];
-        KeyPair nk[PREFETCH ? K * PD : 1];
+        constexpr int  PD = (K == 1 && MB == 2) ? 2 : 1;
+        KeyPair  nk[PREFETCH ? K * PD : 1];
+        uint32_t amask[K]; // K > 1: which of the current 32 steps each clip animates
 #pragma unroll
         for (int k = 0; k < K; k++)
         {
-            hic_cur[k] = __ldg(reinterpret_cast<const int4*>(st[k].hic));
-            hic_nxt[k] = hic_cur[k];
+            amask[k] = 0xffffffffu;
             if (PREFETCH)
             {
-                nk[k] = fetch_keys(st[k], 0, hic_decode(hic_cur[k].x));
+                nk[k] = fetch_keys(st[k], 0);
                 if (PD == 2)
-                    nk[K + k] = fetch_keys(st[k], 1, hic_decode(hic_cur[k].y));
+                    nk[K + k] = fetch_keys(st[k], 1);
             }
         }
 
         for (int s0 = 0; s0 < par.n_steps_padded; s0 += POSE_G)
         {
-            if (s0 + POSE_G < par.n_steps_padded)
+            if (K > 1 && (s0 & 31) == 0)
             {
 #pragma unroll
                 for (int k = 0; k < K; k++)
-                    hic_nxt[k] = __ldg(reinterpret_cast<const int4*>(st[k].hic + s0 + POSE_G));
+                    amask[k] = __ldg(st[k].anim + (s0 >> 5));
             }
             bool contiguous = true; // the group's palette slots are consecutive (always, unless the upload re-ordered the bones)
 #pragma unroll
@@ -481,37 +579,26 @@ namespace pcl
                 const int      bone = rec.joint;
                 contiguous          = contiguous && (bone == c_steps[s0].joint + g);
                 KeyPair ck[K];
-                int     hcur[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
-                {
-                    hcur[k] = pick4(hic_cur[k], g);
-                    ck[k]   = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s, hic_decode(hcur[k]));
-                }
+                    ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s);
                 // this bone's samples first (they consume the keys requested one bone ago) ...
-                float3 P[K], S[K];
-                Quat   Q[K];
+                SampleP sm[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
-                    sample_keys(ck[k], st[k].r, P[k], S[k], Q[k]);
+                    sm[k] = sample_keys(ck[k], st[k].r);
                 // ... then the next bone's keys are requested; they land while the rest of this bone is computed
                 if (PREFETCH && s + PD < par.J)
                 {
 #pragma unroll
                     for (int k = 0; k < K; k++)
-                        nk[(PD == 2 ? (g & 1) * K : 0) + k] =
-                            fetch_keys(st[k], s + PD, hic_decode(g + PD < POSE_G ? pick4(hic_cur[k], g + PD) : pick4(hic_nxt[k], g + PD - POSE_G)),
-                                       opaque_zero(Q[k].w));
+                        nk[(PD == 2 ? (g & 1) * K : 0) + k] = fetch_keys(st[k], s + PD, opaque_zero(lo(sm[k].q.wx)));
                 }
-                TRS loc; // resetSkeleton -> Node::resetToInitialPose, skeleton.cpp:45, node.cpp:197-206
-                loc.p = make_float3(rec.bpos.x, rec.bpos.y, rec.bpos.z), loc.q = Quat {rec.brot.x, rec.brot.y, rec.brot.z, rec.brot.w};
-                loc.s = make_float3(rec.bscl.x, rec.bscl.y, rec.bscl.z);
+                TRSP loc;
                 if (K == 1)
                 {
-                    // skeleton.cpp:88-100; rotate(LOCAL) node.cpp:135-157, scale :182-186, translate(AREN) :107-132
-                    loc.q = qmul(loc.q, qnormalise(Q[0]));
-                    loc.s = loc.s * S[0];
-                    loc.p = loc.p + P[0];
+                    // skeleton.cpp:88-100 on top of Node::resetToInitialPose (skeleton.cpp:45)
+                    loc = local_pose(rec, sm[0].pxy, sm[0].sxy, sm[0].pzsz, sm[0].q);
                 }
                 else
                 {
@@ -524,79 +611,50 @@ namespace pcl
                         en[k] = st[k].mask_off < 0 ? true : (__ldg(par.masks + st[k].mask_off + bone) != 0);
                         if (en[k])
                             wsum += st[k].w;
-                        touched |= hcur[k] >= 0;
+                        touched |= ((amask[k] >> (s & 31)) & 1u) != 0;
                     }
-                    TRS  acc;
-                    Quat qref {1, 0, 0, 0};
-                    bool any = false;
-                    acc.p = make_float3(0, 0, 0), acc.q = Quat {0, 0, 0, 0}, acc.s = make_float3(0, 0, 0);
+                    // One instruction stream for every mix of contributing and gated clips: a clip that does not contribute enters
+                    // with weight 0 (x + 0 * d = x exactly), the first contributing one becomes the sign reference (selects)
+                    f2    accA = pk(0.f, 0.f), accB = accA, accC = accA;
+                    QuatP accq {accA, accA}, qref {pk(1.f, 0.f), accA};
+                    bool  any = false;
+                    const bool live = fabsf(wsum) >= 0.0001f;
 #pragma unroll
                     for (int k = 0; k < K; k++)
                     {
                         const float wn = en[k] ? (PCL_EXACT_NORMALISE ? st[k].w / wsum : fdiv_nobranch(st[k].w, wsum)) : 0.f; // animation_system.cpp:117-149
-                        TRS         d; // an identity track samples to the identity delta, exactly
-                        d.p = P[k], d.s = S[k], d.q = Q[k];
-                        if (fabsf(wsum) >= 0.0001f && wn != 0.f)
-                        {
-                            if (!any)
-                            {
-                                qref  = d.q;
-                                acc.p = wn * d.p, acc.s = wn * d.s, acc.q = qscale(d.q, wn);
-                                any   = true;
-                            }
-                            else
-                            {
-                                const float sg = (qdot(d.q, qref) < 0.0f) ? -wn : wn;
-                                acc.p = acc.p + wn * d.p, acc.s = acc.s + wn * d.s;
-                                acc.q = Quat {acc.q.w + d.q.w * sg, acc.q.x + d.q.x * sg, acc.q.y + d.q.y * sg, acc.q.z + d.q.z * sg};
-                            }
-                        }
+                        // (an identity track samples to the identity delta, exactly)
+                        const bool  ok = live && wn != 0.f;
+                        const float we = ok ? wn : 0.f;
+                        const float sg = (any && qdotp(sm[k].q, qref) < 0.0f) ? -we : we;
+                        accA = fma2p(sm[k].pxy, bc(we), accA), accB = fma2p(sm[k].sxy, bc(we), accB), accC = fma2p(sm[k].pzsz, bc(we), accC);
+                        accq = QuatP {fma2p(sm[k].q.wx, bc(sg), accq.wx), fma2p(sm[k].q.yz, bc(sg), accq.yz)};
+                        const bool first = ok && !any;
+                        qref.wx = first ? sm[k].q.wx : qref.wx, qref.yz = first ? sm[k].q.yz : qref.yz;
+                        any |= ok;
                     }
                     if (any && touched)
-                    {
-                        loc.q = qmul(loc.q, qnormalise(acc.q));
-                        loc.s = loc.s * acc.s;
-                        loc.p = loc.p + acc.p;
-                    }
+                        loc = local_pose(rec, accA, accB, accC, accq);
+                    else
+                        loc = bind_pose(rec);
                 }
                 // m_bones[i].update(), skeleton.cpp:110-113 -> Node::updateDerivedTransform node.cpp:32-65
-                TRS der;
-                if (rec.psrc == -1)
-                    der = loc;
-                else
-                {
-                    TRS par_trs = prev;
-                    if (rec.psrc >= 0)
-                    {
-                        const float* sp = slots + (size_t)rec.psrc * 320 + lane;
-                        par_trs.p = make_float3(sp[0], sp[32], sp[64]);
-                        par_trs.q = Quat {sp[96], sp[128], sp[160], sp[192]};
-                        par_trs.s = make_float3(sp[224], sp[256], sp[288]);
-                    }
-                    der = compose(par_trs, loc);
-                }
+                // (one code path on purpose: a parent fetched from its slot - for a root, the identity in slot nslot - REPLACES
+                // `prev` in place, and a root goes through the same composition with the normalisation switched off; selecting
+                // between register sets cost ~30 copies per bone)
+                if (rec.psrc != -2)
+                    prev = load_trs(slots + (size_t)(rec.psrc == -1 ? par.nslot : rec.psrc) * POSE_SLOT_FLOATS, lane);
+                prev = composep(prev, loc, rec.psrc == -1);
+                const TRSP& der = prev;
                 if (rec.store >= 0)
-                {
-                    float* sp = slots + (size_t)rec.store * 320 + lane;
-                    sp[0] = der.p.x, sp[32] = der.p.y, sp[64] = der.p.z;
-                    sp[96] = der.q.w, sp[128] = der.q.x, sp[160] = der.q.y, sp[192] = der.q.z;
-                    sp[224] = der.s.x, sp[256] = der.s.y, sp[288] = der.s.z;
-                }
-                prev = der;
+                    store_trs(slots + (size_t)rec.store * POSE_SLOT_FLOATS, lane, der);
                 if (par.derived && active)
-                {
-                    float* o = par.derived + ((size_t)inst * par.J + bone) * 10;
-                    o[0] = der.p.x, o[1] = der.p.y, o[2] = der.p.z, o[3] = der.q.w, o[4] = der.q.x;
-                    o[5] = der.q.y, o[6] = der.q.z, o[7] = der.s.x, o[8] = der.s.y, o[9] = der.s.z;
-                }
+                    store_derived(par.derived + ((size_t)inst * par.J + bone) * 10, der);
                 float4 r0, r1, r2; // outputAnimationResult, skeleton.cpp:119-156
-                palette_rows(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                palette_rowsp(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
                 float4* row = reinterpret_cast<float4*>(stage + (size_t)lane * SROW + g * 12);
                 row[0] = r0, row[1] = r1, row[2] = r2;
             }
-#pragma unroll
-            for (int k = 0; k < K; k++)
-                hic_cur[k] = hic_nxt[k];
             __syncwarp();
             if (contiguous && ni == 32 && s0 + POSE_G <= par.J)
             {
@@ -605,21 +663,28 @@ namespace pcl
 #pragma unroll
                 for (int gq = 0; gq < 4; gq++)
                 {
-                    if (SORTED)
+                    if (SORTED && !HOIST)
                     {
-                        // staging row r belongs to the instance lane r works on
                         const size_t i0 = (size_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8);
                         const size_t i1 = (size_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8 + 4);
                         const size_t i2 = (size_t)__shfl_sync(0xffffffffu, inst32, fa + fc4 + gq * 8);
-                        par.palette[i0 * rowsz + off + fb]     = *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW);
-                        par.palette[i1 * rowsz + off + fb]     = *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW);
-                        par.palette[i2 * rowsz + off + 8 + fd] = *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW);
+                        PCL_PST(par.palette + i0 * rowsz + off + fb, *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW));
+                        PCL_PST(par.palette + i1 * rowsz + off + fb, *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW));
+                        PCL_PST(par.palette + i2 * rowsz + off + 8 + fd, *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW));
+                    }
+                    else if (SORTED)
+                    {
+                        float4* gb0 = par.palette + off + fb;
+                        float4* gb2 = par.palette + off + 8 + fd;
+                        PCL_PST(gb0 + (size_t)frow[gq * 3 + 0] * rowsz, *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW));
+                        PCL_PST(gb0 + (size_t)frow[gq * 3 + 1] * rowsz, *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW));
+                        PCL_PST(gb2 + (size_t)frow[gq * 3 + 2] * rowsz, *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW));
                     }
                     else
                     {
-                        g_f0[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW);
-                        g_f0[off + (2 * gq + 1) * rowstep] = *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW);
-                        g_f2[off + (2 * gq) * rowstep]     = *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW);
+                        PCL_PST(g_f0 + off + (2 * gq) * rowstep, *reinterpret_cast<const float4*>(stage + s_f0 + gq * 8 * SROW));
+                        PCL_PST(g_f0 + off + (2 * gq + 1) * rowstep, *reinterpret_cast<const float4*>(stage + s_f0 + (gq * 8 + 4) * SROW));
+                        PCL_PST(g_f2 + off + (2 * gq) * rowstep, *reinterpret_cast<const float4*>(stage + s_f2 + gq * 8 * SROW));
                     }
                 }
             }
@@ -656,7 +721,7 @@ namespace pcl
     // SMs idle (the launcher uses it up to ~3 CTAs per SM), because at narrow levels most warps wait.
     // -------------------------------------------------------------------------------------------
     constexpr int POSE_L_WARPS = 8;
-    __host__ __device__ inline size_t pose_l_smem_bytes(int J) { return (size_t)J * 10 * 32 * sizeof(float); }
+    __host__ __device__ inline size_t pose_l_smem_bytes(int J) { return (size_t)J * POSE_SLOT_FLOATS * sizeof(float); }
 
     __global__ void __launch_bounds__(POSE_L_WARPS * 32) pose_level_kernel(const PoseParams par)
     {
@@ -673,10 +738,9 @@ namespace pcl
             ph += par.dt / __ldg(par.clip_len + inst); // animation_component.cpp:19-21
             ph -= floorf(ph);
         }
-        const float exact = ph * (float)cr.total_frame_m1; // skeleton.cpp:52-55
-        SimpleSlot  st;
-        st.lo = (int)floorf(exact), st.hi = (int)ceilf(exact), st.r = exact - (float)st.lo;
-        st.keys = cr.keys_step, st.hic = cr.hic_step, st.F = cr.F, st.w = 1.0f, st.mask_off = -1;
+        SimpleSlot st;
+        slot_frames(st, ph, cr.total_frame_m1, cr.F);
+        st.keys = cr.keys_step, st.anim = cr.anim_step, st.w = 1.0f, st.mask_off = -1;
         float4* pal = par.palette + (size_t)inst * par.pitch * 3;
         if (warp == 0 && active)
         {
@@ -686,61 +750,41 @@ namespace pcl
         if (warp == 0 && active && par.advance != 0)
             par.phase[inst] = ph;
 
-        // software pipeline over the warp's own rounds: keys one round ahead, clamp values two rounds ahead (each is a dependent
-        // global load; a round of arithmetic covers one of them)
+        // software pipeline over the warp's own rounds: keys one round ahead
         const int32_t* my = par.sched + warp;
         int            s_cur = __ldg(my), s_nxt = par.n_rounds > 1 ? __ldg(my + POSE_L_WARPS) : -1;
-        int            h_nxt = s_nxt >= 0 ? __ldg(st.hic + s_nxt) : 0;
-        KeyPair        k_cur = fetch_keys(st, max(s_cur, 0), hic_decode(__ldg(st.hic + max(s_cur, 0))));
+        KeyPair        k_cur = fetch_keys(st, max(s_cur, 0));
         for (int r = 0; r < par.n_rounds; r++)
         {
             const int     s = s_cur;
             const KeyPair k = k_cur;
-            // next round's keys, the round after's clamp value
             const int s_nn = r + 2 < par.n_rounds ? __ldg(my + (r + 2) * POSE_L_WARPS) : -1;
             if (s_nxt >= 0)
-                k_cur = fetch_keys(st, s_nxt, hic_decode(h_nxt));
-            h_nxt = s_nn >= 0 ? __ldg(st.hic + s_nn) : 0;
+                k_cur = fetch_keys(st, s_nxt);
             s_cur = s_nxt, s_nxt = s_nn;
             if (s >= 0)
             {
                 const StepRec& rec = c_steps[s];
-                float3         P, S;
-                Quat           Q;
-                sample_keys(k, st.r, P, S, Q);
-                TRS loc; // Node::resetToInitialPose + rotate(LOCAL) / scale / translate(AREN), as in pose_simple_kernel
-                loc.p = make_float3(rec.bpos.x, rec.bpos.y, rec.bpos.z), loc.q = Quat {rec.brot.x, rec.brot.y, rec.brot.z, rec.brot.w};
-                loc.s = make_float3(rec.bscl.x, rec.bscl.y, rec.bscl.z);
-                loc.q = qmul(loc.q, qnormalise(Q));
-                loc.s = loc.s * S;
-                loc.p = loc.p + P;
-                TRS der;
-                if (rec.pstep < 0)
-                    der = loc;
-                else
-                {
-                    const float* sp = smem + (size_t)rec.pstep * 320 + lane;
-                    TRS          pt;
-                    pt.p = make_float3(sp[0], sp[32], sp[64]);
-                    pt.q = Quat {sp[96], sp[128], sp[160], sp[192]};
-                    pt.s = make_float3(sp[224], sp[256], sp[288]);
-                    der  = compose(pt, loc);
-                }
-                float* dp = smem + (size_t)s * 320 + lane;
-                dp[0] = der.p.x, dp[32] = der.p.y, dp[64] = der.p.z;
-                dp[96] = der.q.w, dp[128] = der.q.x, dp[160] = der.q.y, dp[192] = der.q.z;
-                dp[224] = der.s.x, dp[256] = der.s.y, dp[288] = der.s.z;
+                const SampleP  sm  = sample_keys(k, st.r);
+                // Node::resetToInitialPose + rotate(LOCAL) / scale / translate(AREN), as in pose_simple_kernel
+                const TRSP loc = local_pose(rec, sm.pxy, sm.sxy, sm.pzsz, sm.q);
+                TRSP par_trs = identity_trs();
+                if (rec.pstep >= 0)
+                    par_trs = load_trs(smem + (size_t)rec.pstep * POSE_SLOT_FLOATS, lane);
+                const TRSP der = composep(par_trs, loc, rec.pstep < 0);
+                store_trs(smem + (size_t)s * POSE_SLOT_FLOATS, lane, der);
                 if (active)
                 {
                     const int bone = rec.joint;
                     if (par.derived)
-                    {
-                        float* o = par.derived + ((size_t)inst * par.J + bone) * 10;
-                        o[0] = der.p.x, o[1] = der.p.y, o[2] = der.p.z, o[3] = der.q.w, o[4] = der.q.x;
-                        o[5] = der.q.y, o[6] = der.q.z, o[7] = der.s.x, o[8] = der.s.y, o[9] = der.s.z;
-                    }
+                        store_derived(par.derived + ((size_t)inst * par.J + bone) * 10, der);
                     float4 r0, r1, r2;
-                    palette_rows(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                    palette_rowsp(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                    if (par.out12)
+                    {
+                        float4* o = par.out12 + ((size_t)inst * par.J + bone) * 3;
+                        o[0] = r0, o[1] = r1, o[2] = r2;
+                    }
                     float4* row = pal + (size_t)(bone + 1) * 3;
                     row[0] = r0, row[1] = r1, row[2] = r2;
                 }

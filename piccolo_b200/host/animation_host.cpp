@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <tuple>
+#include <algorithm>
 
 namespace Piccolo
 {
@@ -35,7 +36,14 @@ namespace Piccolo
         pcl_ctx*    g_ctx       = nullptr;
         bool        g_ctx_tried = false;
         std::string g_ctx_error;
+        bool        g_blend_extension = false;
     } // namespace
+    namespace detail
+    {
+        void destroyPoseGroups();
+    }
+    void Runtime::enableBlendExtension(bool on) { g_blend_extension = on; }
+    bool Runtime::blendExtensionEnabled() { return g_blend_extension; }
 
     pcl_ctx* Runtime::context()
     {
@@ -55,6 +63,7 @@ namespace Piccolo
     const char* Runtime::lastError() { return g_ctx ? pcl_last_error(g_ctx) : g_ctx_error.c_str(); }
     void        Runtime::shutdown()
     {
+        detail::destroyPoseGroups();
         AnimationManager::clearCaches();
         if (g_ctx)
             pcl_destroy(g_ctx);
@@ -156,7 +165,41 @@ namespace Piccolo
         std::map<std::tuple<pcl_skel, std::string, std::string>, pcl_clip> g_dev_clips;
         std::map<std::pair<pcl_skel, std::string>, pcl_mask>               g_dev_masks;
         std::map<std::pair<pcl_skel, uint64_t>, pcl_clip>                  g_dev_clips_by_content;
+        std::map<uint64_t, pcl_skel>                                       g_dev_skels_by_content;
+        uint64_t fnv1a(uint64_t h, const void* p, size_t n)
+        {
+            const unsigned char* b = (const unsigned char*)p;
+            for (size_t i = 0; i < n; i++)
+                h = (h ^ b[i]) * 1099511628211ull;
+            return h;
+        }
     } // namespace
+
+    // Every AnimationComponent of a level names the same few skeleton files: one device copy per distinct CONTENT (what
+    // pcl_upload_skeleton reads), so that components share step records, clips and masks - and the kernels' constant bank
+    // is not rewritten when two characters take turns.
+    pcl_skel AnimationManager::deviceSkeleton(const SkeletonData& d)
+    {
+        uint64_t h = 1469598103934665603ull;
+        const int32_t flags[2] = {d.is_flat, d.in_topological_order};
+        h = fnv1a(h, flags, sizeof(flags));
+        for (const RawBone& b : d.bones_map)
+        {
+            const int32_t ip[2] = {b.index, b.parent_index};
+            h = fnv1a(h, ip, sizeof(ip));
+            h = fnv1a(h, &b.binding_pose.m_position, sizeof(Vector3));
+            h = fnv1a(h, &b.binding_pose.m_rotation, sizeof(Quaternion));
+            h = fnv1a(h, &b.binding_pose.m_scale, sizeof(Vector3));
+            h = fnv1a(h, &b.tpose_matrix.v0, 64);
+        }
+        auto it = g_dev_skels_by_content.find(h);
+        if (it != g_dev_skels_by_content.end())
+            return it->second;
+        pcl_skel s = uploadSkeleton(d);
+        if (s >= 0)
+            g_dev_skels_by_content.emplace(h, s);
+        return s;
+    }
 
     template<typename T, typename F>
     static std::shared_ptr<T> tryLoad(std::map<std::string, std::shared_ptr<T>>& cache, const std::string& path, F load)
@@ -314,29 +357,168 @@ namespace Piccolo
     void AnimationManager::clearCaches()
     {
         m_skeleton_definition_cache.clear(), m_animation_data_cache.clear(), m_animation_skeleton_map_cache.clear(), m_skeleton_mask_cache.clear();
-        g_dev_clips.clear(), g_dev_masks.clear(), g_dev_clips_by_content.clear();
+        g_dev_clips.clear(), g_dev_masks.clear(), g_dev_clips_by_content.clear(), g_dev_skels_by_content.clear();
     }
 
     // ---------------------------------------------------------------------------------------------
-    // Skeleton (function/animation/skeleton.cpp) - a batch of one
+    // PoseGroup: the hidden batch behind all AnimationComponents of one (skeleton, clip count)
+    //
+    // The reference ticks every GObject's AnimationComponent in turn, each tick a complete pose on the CPU
+    // (function/framework/object/object.cpp:41-50).  One launch + one synchronisation per character would cost more than the
+    // reference's 18 us per tick, so components only RECORD their frame inputs here; the first result anybody asks for
+    // (MeshComponent::tick reads getResult(), mesh_component.cpp:75) poses every recorded member with ONE pcl_batch_frame
+    // call.  Results are identical to the batch-of-one path: an instance's pose does not depend on batch composition.
+    // ---------------------------------------------------------------------------------------------
+    namespace detail
+    {
+        struct PoseGroup
+        {
+            pcl_skel   skel = -1;
+            int        K = 1, J = 0;
+            pcl_batch* batch = nullptr;
+            int64_t    capacity = 0;
+            bool       dirty = false, derived = false;
+            std::vector<Skeleton*> members; // slot -> owner, nullptr = free
+            std::vector<int32_t>   clip, mask;
+            std::vector<float>     phase, weight;
+            std::vector<float>     rows; // [capacity][J][12] of the last flush
+
+            int acquire(Skeleton* who)
+            {
+                for (size_t i = 0; i < members.size(); i++)
+                    if (!members[i])
+                    {
+                        members[i] = who;
+                        return (int)i;
+                    }
+                members.push_back(who);
+                const size_t n = members.size() * K;
+                if (clip.size() < n)
+                    clip.resize(n, -1), mask.resize(n, -1), phase.resize(n, 0.f), weight.resize(n, 1.f);
+                return (int)members.size() - 1;
+            }
+            void release(int slot)
+            {
+                if (slot >= 0 && slot < (int)members.size())
+                    members[slot] = nullptr;
+            }
+            void record(int slot, const int32_t* c, const float* ph, const float* w, const int32_t* m)
+            {
+                for (int k = 0; k < K; k++)
+                    clip[(size_t)slot * K + k] = c[k], phase[(size_t)slot * K + k] = ph[k], weight[(size_t)slot * K + k] = w[k], mask[(size_t)slot * K + k] = m[k];
+                dirty = true;
+            }
+            bool flush()
+            {
+                if (!dirty && batch)
+                    return true;
+                pcl_ctx* c = Runtime::context();
+                if (!c || members.empty())
+                    return false;
+                if ((int64_t)members.size() > capacity) // grow: batches have a fixed size
+                {
+                    if (batch)
+                        pcl_batch_destroy(batch), batch = nullptr;
+                    // as many instances as there are components (a frame poses all of them): 1, 2, 4, 8, then multiples of 8
+                    int64_t want = 1;
+                    while (want < (int64_t)members.size() && want < 8)
+                        want *= 2;
+                    if (want < (int64_t)members.size())
+                        want = ((int64_t)members.size() + 7) / 8 * 8;
+                    capacity = want;
+                    if (pcl_batch_create(c, skel, capacity, K, &batch) != PCL_OK)
+                    {
+                        batch = nullptr, capacity = 0;
+                        return false;
+                    }
+                    if (derived)
+                        pcl_batch_keep_derived(batch, 1);
+                }
+                // slots nobody has recorded into yet (free, or not ticked so far) pose some valid clip at phase 0
+                int32_t any_clip = -1;
+                for (int32_t v : clip)
+                    if (v >= 0)
+                    {
+                        any_clip = v;
+                        break;
+                    }
+                if (any_clip < 0)
+                    return false;
+                const size_t n = (size_t)capacity * K;
+                if (clip.size() < n)
+                    clip.resize(n, -1), mask.resize(n, -1), phase.resize(n, 0.f), weight.resize(n, 1.f);
+                for (size_t i = 0; i < n; i++)
+                    if (clip[i] < 0)
+                        clip[i] = any_clip, mask[i] = -1, phase[i] = 0.f, weight[i] = 1.f;
+                rows.resize((size_t)capacity * J * 12);
+                if (pcl_batch_frame(batch, clip.data(), phase.data(), weight.data(), mask.data(), rows.data()) != PCL_OK)
+                    return false;
+                dirty = false;
+                for (Skeleton* m : members)
+                    if (m)
+                        m->m_derived_stale = true;
+                return true;
+            }
+        };
+        namespace
+        {
+            std::map<std::pair<pcl_skel, int>, PoseGroup*> g_groups;
+        }
+        PoseGroup* poseGroup(pcl_skel skel, int K, int J)
+        {
+            auto key = std::make_pair(skel, K);
+            auto it  = g_groups.find(key);
+            if (it != g_groups.end())
+                return it->second;
+            PoseGroup* g = new PoseGroup();
+            g->skel = skel, g->K = K, g->J = J;
+            g_groups.emplace(key, g);
+            return g;
+        }
+        void destroyPoseGroups()
+        {
+            for (auto& kv : g_groups)
+            {
+                for (Skeleton* m : kv.second->members)
+                    if (m)
+                        m->m_group = nullptr, m->m_slot = -1;
+                if (kv.second->batch)
+                    pcl_batch_destroy(kv.second->batch);
+                delete kv.second;
+            }
+            g_groups.clear();
+        }
+    } // namespace detail
+
+    // ---------------------------------------------------------------------------------------------
+    // Skeleton (function/animation/skeleton.cpp)
     // ---------------------------------------------------------------------------------------------
     Skeleton::~Skeleton()
     {
+        leaveGroup();
         if (m_batch)
             pcl_batch_destroy(m_batch);
         delete[] m_bones;
     }
 
+    void Skeleton::leaveGroup()
+    {
+        if (m_group)
+            m_group->release(m_slot);
+        m_group = nullptr, m_slot = -1;
+    }
+
     void Skeleton::buildSkeleton(const SkeletonData& def)
     {
         m_is_flat = def.is_flat;
+        leaveGroup();
         if (m_batch)
             pcl_batch_destroy(m_batch), m_batch = nullptr, m_batch_k = 0;
         delete[] m_bones;
         m_bones = nullptr, m_bone_count = 0, m_skel = -1;
         if (!m_is_flat || !def.in_topological_order)
             return; // skeleton.cpp:24-28
-        pcl_skel s = uploadSkeleton(def);
+        pcl_skel s = AnimationManager::deviceSkeleton(def);
         if (s < 0)
             return;
         m_skel       = s;
@@ -344,7 +526,8 @@ namespace Piccolo
         m_bones      = new Bone[m_bone_count];
         std::vector<int32_t> parent(m_bone_count);
         pcl_skeleton_parents(Runtime::context(), m_skel, parent.data());
-        m_bind_trs.assign((size_t)m_bone_count * 10, 0.f);
+        m_index.resize(m_bone_count);
+        pcl_skeleton_indices(Runtime::context(), m_skel, m_index.data());
         for (int i = 0; i < m_bone_count; i++)
         {
             const RawBone& d = def.bones_map[i];
@@ -381,13 +564,13 @@ namespace Piccolo
         m_batch_k = k;
     }
 
-    // skeleton.cpp:39-117.  clip_count == 1 (all the reference executes): clip 0 with weight forced to 1.
-    // clip_count in 2..4: the documented blend extension, with the masks and raw weights the blend state names.
+    // skeleton.cpp:39-117: clip 0 with weight forced to 1, whatever clip_count says (:46, :63-64).  With
+    // Runtime::enableBlendExtension(true), clip_count in 2..4 blends with the masks and raw weights the blend state names.
     void Skeleton::applyAnimation(const BlendStateWithClipData& bs)
     {
         if (!m_bones || m_skel < 0)
             return;
-        int K = bs.clip_count;
+        int K = Runtime::blendExtensionEnabled() ? bs.clip_count : 1;
         if (K < 1 || K > 4 || (size_t)K > bs.blend_clip.size() || (size_t)K > bs.blend_anim_skel_map.size() || (size_t)K > bs.blend_ratio.size())
             K = (bs.blend_clip.empty() || bs.blend_anim_skel_map.empty() || bs.blend_ratio.empty()) ? 0 : 1;
         if (K == 0)
@@ -405,40 +588,83 @@ namespace Piccolo
             weight[k] = (K > 1 && bs.source_weight.size() > (size_t)k) ? bs.source_weight[k] : 1.f;
             mask[k]   = (K > 1 && bs.source_mask_path.size() > (size_t)k) ? AnimationManager::deviceMask(m_skel, bs.source_mask_path[k]) : -1;
         }
+        applyResolved(K, clip, phase, weight, mask);
+    }
+
+    void Skeleton::applyResolved(int K, const int32_t* clip, const float* phase, const float* weight, const int32_t* mask)
+    {
+        if (m_grouped)
+        {
+            if (m_group && m_group->K != K)
+                leaveGroup();
+            if (!m_group)
+            {
+                m_group = detail::poseGroup(m_skel, K, m_bone_count);
+                m_slot  = m_group->acquire(this);
+            }
+            m_group->record(m_slot, clip, phase, weight, mask);
+            m_derived_stale = true;
+            return;
+        }
         ensureBatch(K);
         if (!m_batch)
             return;
-        if (pcl_batch_set(m_batch, 0, 1, clip, phase, weight, nullptr, mask) != PCL_OK)
-            return;
-        pcl_batch_pose(m_batch);
+        pcl_batch_frame(m_batch, clip, phase, weight, mask, nullptr); // asynchronous: outputAnimationResult waits for the rows
         m_derived_stale = true;
+    }
+
+    // Matrix4x4::toMatrix4x4_ (core/math/matrix4.h:98-119) of an affine product: rows 0..2 come from the device, row 3 is 0 0 0 1
+    void Skeleton::fillResult(const float* rows12, AnimationResult& r) const
+    {
+        r.node.resize(m_bone_count);
+        for (int i = 0; i < m_bone_count; i++)
+        {
+            r.node[i].index = m_index[i];
+            float* m = &r.node[i].transform.v0;
+            std::memcpy(m, rows12 + (size_t)i * 12, 48);
+            m[12] = 0.f, m[13] = 0.f, m[14] = 0.f, m[15] = 1.f;
+        }
     }
 
     AnimationResult Skeleton::outputAnimationResult()
     {
         AnimationResult r;
-        if (!m_bones || !m_batch)
+        if (!m_bones)
             return r;
-        std::vector<float>   mats((size_t)m_bone_count * 16);
-        std::vector<int32_t> idx(m_bone_count);
-        if (pcl_batch_download_palette(m_batch, 0, 1, mats.data()) != PCL_OK)
-            return r;
-        pcl_skeleton_indices(Runtime::context(), m_skel, idx.data());
-        r.node.resize(m_bone_count);
-        for (int i = 0; i < m_bone_count; i++)
+        if (m_grouped)
         {
-            r.node[i].index = idx[i];
-            std::memcpy(&r.node[i].transform.v0, &mats[(size_t)i * 16], 64);
+            if (m_group && m_group->flush())
+                fillResult(m_group->rows.data() + (size_t)m_slot * m_bone_count * 12, r);
+            return r;
         }
+        if (!m_batch)
+            return r;
+        std::vector<float> rows((size_t)m_bone_count * 12);
+        if (pcl_batch_frame_result(m_batch, rows.data()) == PCL_OK)
+            fillResult(rows.data(), r);
         return r;
     }
 
     void Skeleton::refreshDerived()
     {
-        if (!m_derived_stale || !m_batch || !m_bones)
+        if (!m_derived_stale || !m_bones)
             return;
         std::vector<float> d((size_t)m_bone_count * 10);
-        if (pcl_batch_download_derived(m_batch, 0, 1, d.data()) != PCL_OK)
+        if (m_grouped)
+        {
+            if (!m_group)
+                return;
+            if (!m_group->derived) // first LevelDebugger-style reader of this group: keep derived transforms from now on
+            {
+                m_group->derived = true;
+                if (m_group->batch)
+                    pcl_batch_keep_derived(m_group->batch, 1);
+                m_group->dirty = true;
+            }
+            if (!m_group->flush() || pcl_batch_download_derived(m_group->batch, m_slot, 1, d.data()) != PCL_OK)
+                return;
+        }
+        else if (!m_batch || pcl_batch_download_derived(m_batch, 0, 1, d.data()) != PCL_OK)
             return;
         for (int i = 0; i < m_bone_count; i++)
         {
@@ -468,8 +694,14 @@ namespace Piccolo
         m_parent_object   = parent_object;
         auto skeleton_res = AnimationManager::tryLoadSkeleton(m_animation_res.skeleton_file_path);
         m_skeleton.buildSkeleton(*skeleton_res);
+        m_skeleton.m_grouped = true; // components pose together (detail::PoseGroup)
+        m_resolved_paths.clear();
     }
 
+    // animation_component.cpp:17-25.  The phase advances exactly as there; what the reference then does in
+    // getBlendStateWithClipData (four map look-ups AND a deep copy of every clip and map, animation_system.cpp:104,108) is
+    // reduced to the look-ups, and those to a comparison of the path strings once the handles are known; the pose itself is
+    // recorded and computed when the result is first read.
     void AnimationComponent::tick(float delta_time)
     {
         BlendState& bs = m_animation_res.blend_state;
@@ -477,12 +709,66 @@ namespace Piccolo
             return;
         bs.blend_ratio[0] += (delta_time / bs.blend_clip_file_length[0]);
         bs.blend_ratio[0] -= std::floor(bs.blend_ratio[0]);
-        m_skeleton.applyAnimation(AnimationManager::getBlendStateWithClipData(bs));
-        m_animation_res.animation_result = m_skeleton.outputAnimationResult();
+        if (!m_skeleton.m_bones || m_skeleton.m_skel < 0)
+            return;
+        int K = Runtime::blendExtensionEnabled() ? bs.clip_count : 1;
+        if (K < 1 || K > 4 || (size_t)K > bs.blend_clip_file_path.size() || (size_t)K > bs.blend_anim_skel_map_path.size() || (size_t)K > bs.blend_ratio.size())
+            K = (bs.blend_clip_file_path.empty() || bs.blend_anim_skel_map_path.empty()) ? 0 : 1;
+        if (K == 0)
+            return;
+        // resolve (and cache) the device handles of the paths this blend state names; a tick whose paths have not changed
+        // only compares strings
+        static const std::string no_mask;
+        bool same = m_resolved_paths.size() == 3 * (size_t)K;
+        for (int k = 0; k < K && same; k++)
+        {
+            const std::string& mp = (K > 1 && bs.blend_mask_file_path.size() > (size_t)k) ? bs.blend_mask_file_path[k] : no_mask;
+            same = m_resolved_paths[3 * k] == bs.blend_clip_file_path[k] && m_resolved_paths[3 * k + 1] == bs.blend_anim_skel_map_path[k] &&
+                   m_resolved_paths[3 * k + 2] == mp;
+        }
+        if (!same)
+        {
+            m_resolved_paths.clear();
+            for (int k = 0; k < K; k++)
+            {
+                const std::string& mp = (K > 1 && bs.blend_mask_file_path.size() > (size_t)k) ? bs.blend_mask_file_path[k] : no_mask;
+                m_clip[k] = AnimationManager::deviceClip(m_skeleton.m_skel, bs.blend_clip_file_path[k], bs.blend_anim_skel_map_path[k]);
+                m_mask[k] = mp.empty() ? -1 : AnimationManager::deviceMask(m_skeleton.m_skel, mp);
+                if (m_clip[k] < 0)
+                {
+                    m_resolved_paths.clear();
+                    return;
+                }
+                m_resolved_paths.push_back(bs.blend_clip_file_path[k]);
+                m_resolved_paths.push_back(bs.blend_anim_skel_map_path[k]);
+                m_resolved_paths.push_back(mp);
+            }
+        }
+        float phase[4], weight[4];
+        for (int k = 0; k < K; k++)
+        {
+            phase[k]  = bs.blend_ratio[k];
+            weight[k] = (K > 1 && bs.blend_weight.size() > (size_t)k) ? bs.blend_weight[k] : 1.f;
+        }
+        m_skeleton.applyResolved(K, m_clip, phase, weight, m_mask);
+        m_result_stale = true;
     }
 
-    const AnimationResult& AnimationComponent::getResult() const { return m_animation_res.animation_result; }
-    const Skeleton&        AnimationComponent::getSkeleton() const { return m_skeleton; }
+    const AnimationResult& AnimationComponent::getResult() const
+    {
+        if (m_result_stale)
+        {
+            // (the grouped path fills the component's own vector in place: no allocation per character and frame)
+            if (m_skeleton.m_grouped && m_skeleton.m_group && m_skeleton.m_group->flush())
+                m_skeleton.fillResult(m_skeleton.m_group->rows.data() + (size_t)m_skeleton.m_slot * m_skeleton.m_bone_count * 12,
+                                      m_animation_res.animation_result);
+            else
+                m_animation_res.animation_result = m_skeleton.outputAnimationResult();
+            m_result_stale = false;
+        }
+        return m_animation_res.animation_result;
+    }
+    const Skeleton& AnimationComponent::getSkeleton() const { return m_skeleton; }
 
     // ---------------------------------------------------------------------------------------------
     // AnimationBatch
@@ -503,7 +789,7 @@ namespace Piccolo
         auto def = AnimationManager::tryLoadSkeleton(res.skeleton_file_path);
         if (!def->is_flat || !def->in_topological_order)
             return false;
-        m_skel = uploadSkeleton(*def);
+        m_skel = AnimationManager::deviceSkeleton(*def);
         if (m_skel < 0)
             return false;
         const BlendState& bs = res.blend_state;
@@ -559,8 +845,17 @@ namespace Piccolo
     void AnimationBatch::getResults(int64_t first, int64_t count, std::vector<float>& mats) const
     {
         mats.assign((size_t)count * m_j * 16, 0.f);
-        if (m_batch)
-            pcl_batch_download_palette(m_batch, first, count, mats.data());
+        if (!m_batch)
+            return;
+        // rows 0..2 cross the host link (48 B per bone), row 3 = 0 0 0 1 is filled in here (matrix4.h:98-119)
+        std::vector<float> rows((size_t)count * m_j * 12);
+        if (pcl_batch_download_palette3x4(m_batch, first, count, rows.data()) != PCL_OK)
+            return;
+        for (size_t e = 0; e < (size_t)count * m_j; e++)
+        {
+            std::memcpy(&mats[e * 16], &rows[e * 12], 48);
+            mats[e * 16 + 15] = 1.f;
+        }
     }
     AnimationResult AnimationBatch::getResult(int64_t i) const
     {

@@ -190,6 +190,12 @@ namespace Piccolo
         void cacheStore(const std::string& full_path, const MeshData& v);
     } // namespace detail
 
+    namespace detail
+    {
+        struct PoseGroup;
+        void destroyPoseGroups();
+    }
+
     // ---- function/animation/node.h (the read side LevelDebugger uses) -------------------------------
     class Node
     {
@@ -247,16 +253,28 @@ namespace Piccolo
 
     private:
         friend class AnimationComponent;
+        friend struct detail::PoseGroup;
+        friend void detail::destroyPoseGroups();
         bool       m_is_flat {false};
         int        m_bone_count {0};
         Bone*      m_bones {nullptr};
         pcl_skel   m_skel {-1};
-        pcl_batch* m_batch {nullptr};
-        int        m_batch_k {0};
-        bool       m_derived_stale {true};
-        std::vector<float> m_bind_trs; // [J][10], for resetSkeleton
+        // Where the pose is computed.  A Skeleton used on its own (the reference's applyAnimation -> outputAnimationResult
+        // pair) owns a batch of one; a Skeleton that belongs to an AnimationComponent shares ONE hidden batch with every
+        // other component of the same skeleton and clip count (detail::PoseGroup): applyAnimation then only records the
+        // frame's inputs, and the first result anybody asks for poses the whole group with one launch and one read-back.
+        pcl_batch*         m_batch {nullptr};
+        int                m_batch_k {0};
+        bool               m_grouped {false};
+        detail::PoseGroup* m_group {nullptr};
+        int                m_slot {-1};
+        bool               m_derived_stale {true};
+        std::vector<int32_t> m_index; // AnimationResultElement::index per bone (getID() + 1)
         void ensureBatch(int k);
         void refreshDerived();
+        void leaveGroup();
+        void applyResolved(int K, const int32_t* clip, const float* phase, const float* weight, const int32_t* mask);
+        void fillResult(const float* rows12, AnimationResult& out) const;
     };
 
     // ---- function/animation/animation_system.h ------------------------------------------------------
@@ -280,6 +298,7 @@ namespace Piccolo
         static pcl_clip deviceClip(pcl_skel skel, const std::string& clip_path, const std::string& map_path);
         static pcl_mask deviceMask(pcl_skel skel, const std::string& mask_path);
         static pcl_clip deviceClipFromData(pcl_skel skel, const AnimationClip& clip, const AnimSkelMap& map);
+        static pcl_skel deviceSkeleton(const SkeletonData& def); // one upload per distinct skeleton content
         static void     clearCaches(); // tests
     };
 
@@ -292,6 +311,12 @@ namespace Piccolo
         static pcl_ctx*    context();
         static const char* lastError();
         static void        shutdown();
+        // The reference plays clip 0 with weight 1 whatever clip_count says (skeleton.cpp:46,63-64), and so do Skeleton and
+        // AnimationComponent here by default.  Switching the blend extension on makes them blend clip_count = 2..4 clips
+        // with the blend state's weights and masks (DESIGN.md A4 - no reference behaviour to compare with).  AnimationBatch,
+        // which has no counterpart in the reference, always blends.
+        static void enableBlendExtension(bool on);
+        static bool blendExtensionEnabled();
     };
 
     // ---- function/framework/component (only what this path needs) ------------------------------------
@@ -321,8 +346,12 @@ namespace Piccolo
         const AnimationComponentRes& getAnimationRes() const { return m_animation_res; }
 
     protected:
-        AnimationComponentRes m_animation_res;
-        Skeleton              m_skeleton;
+        mutable AnimationComponentRes m_animation_res; // animation_result is filled in when it is first asked for after a tick
+        mutable Skeleton              m_skeleton;
+        mutable bool                  m_result_stale {false};
+        // handles resolved from the blend state's paths, re-resolved only when a path changes (no per-tick clip copies)
+        std::vector<std::string> m_resolved_paths;
+        int32_t                  m_clip[4] {-1, -1, -1, -1}, m_mask[4] {-1, -1, -1, -1};
     };
 
     // ---- crowd form: N AnimationComponents that share a skeleton, one launch per tick ----------------

@@ -5,7 +5,10 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
+#include <chrono>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -236,6 +239,124 @@ static int cmd_batch(int argc, char** argv)
     return 0;
 }
 
+// n AnimationComponents of one level, driven like GObject::tick drives them: every frame all components tick, then every
+// consumer (MeshComponent::tick, mesh_component.cpp:75) reads its result.  Dumps every component's phases and results after
+// `ticks` frames, the derived transforms of the last one, and a stand-alone Skeleton's answer for component 0's inputs.
+static int cmd_multi(int argc, char** argv)
+{
+    if (argc < 8)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    auto        res   = AnimationLoader().loadAnimationComponentRes(argv[3]);
+    const int   n     = std::atoi(argv[4]);
+    const int   ticks = std::atoi(argv[5]);
+    const float dt    = (float)std::atof(argv[6]);
+    g_out             = fopen(argv[7], "wb");
+    {
+        std::vector<std::unique_ptr<AnimationComponent>> comps;
+        for (int i = 0; i < n; i++)
+        {
+            comps.emplace_back(new AnimationComponent());
+            AnimationComponentRes r = *res;
+            r.blend_state.blend_ratio[0] = (float)i / (float)n;
+            comps.back()->setAnimationRes(r);
+            comps.back()->postLoadResource(std::weak_ptr<GObject>());
+        }
+        for (int t = 0; t < ticks; t++)
+        {
+            for (auto& c : comps)
+                c->tick(dt);
+            for (auto& c : comps)
+                (void)c->getResult();
+        }
+        std::vector<float> phases;
+        for (int i = 0; i < n; i++)
+        {
+            phases.push_back(comps[i]->getAnimationRes().blend_state.blend_ratio[0]);
+            putResult(100 + i, comps[i]->getResult());
+        }
+        putf(1, phases);
+        const Skeleton&    sk    = comps[n - 1]->getSkeleton();
+        const Bone*        bones = sk.getBones();
+        std::vector<float> der;
+        for (int i = 0; i < sk.getBonesCount(); i++)
+        {
+            const Vector3&    p = bones[i]._getDerivedPosition();
+            const Quaternion& q = bones[i]._getDerivedOrientation();
+            const Vector3&    s = bones[i]._getDerivedScale();
+            der.insert(der.end(), {p.x, p.y, p.z, q.w, q.x, q.y, q.z, s.x, s.y, s.z});
+        }
+        putf(2, der);
+        // the reference's own pair of calls on a Skeleton used directly
+        Skeleton solo;
+        solo.buildSkeleton(*AnimationManager::tryLoadSkeleton(res->skeleton_file_path));
+        solo.applyAnimation(AnimationManager::getBlendStateWithClipData(comps[0]->getAnimationRes().blend_state));
+        putResult(3, solo.outputAnimationResult());
+        // a component that joins late and one that leaves: slots are recycled, the others' results do not move
+        if (n > 1)
+            comps.erase(comps.begin() + n / 2);
+        comps.emplace_back(new AnimationComponent());
+        comps.back()->setAnimationRes(*res);
+        comps.back()->postLoadResource(std::weak_ptr<GObject>());
+        for (auto& c : comps)
+            c->tick(0.f);
+        putResult(4, comps[0]->getResult());
+        putResult(5, comps.back()->getResult());
+        std::printf("multi ok n=%d\n", n);
+    }
+    fclose(g_out);
+    std::fflush(stdout);
+    Runtime::shutdown();
+    return 0;
+}
+
+// per-frame cost of n components through the drop-in classes: n x tick, then n x getResult (wall clock)
+static int cmd_latency(int argc, char** argv)
+{
+    if (argc < 6)
+        return 2;
+    AnimationLoader::setAssetRoot(argv[2]);
+    auto      res    = AnimationLoader().loadAnimationComponentRes(argv[3]);
+    const int n      = std::atoi(argv[4]);
+    const int frames = std::atoi(argv[5]);
+    {
+        std::vector<std::unique_ptr<AnimationComponent>> comps;
+        for (int i = 0; i < n; i++)
+        {
+            comps.emplace_back(new AnimationComponent());
+            AnimationComponentRes r = *res;
+            r.blend_state.blend_ratio[0] = (float)i / (float)n;
+            comps.back()->setAnimationRes(r);
+            comps.back()->postLoadResource(std::weak_ptr<GObject>());
+        }
+        double sink = 0;
+        auto   frame = [&]() {
+            for (auto& c : comps)
+                c->tick(1.f / 60.f);
+            for (auto& c : comps)
+                sink += c->getResult().node[7].transform.v3;
+        };
+        for (int t = 0; t < 50; t++)
+            frame();
+        std::vector<double> us;
+        for (int t = 0; t < frames; t++)
+        {
+            auto t0 = std::chrono::steady_clock::now();
+            frame();
+            us.push_back(std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count());
+        }
+        std::sort(us.begin(), us.end());
+        double mean = 0;
+        for (double x : us)
+            mean += x;
+        std::printf("{\"components\": %d, \"frames\": %d, \"us_per_frame_median\": %.2f, \"us_per_frame_mean\": %.2f, \"us_per_frame_p90\": %.2f, \"sink\": %.3f}\n",
+                    n, frames, us[us.size() / 2], mean / us.size(), us[us.size() * 9 / 10], sink);
+    }
+    std::fflush(stdout);
+    Runtime::shutdown();
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
     if (argc < 2)
@@ -250,5 +371,9 @@ int main(int argc, char** argv)
         return cmd_tick(argc, argv);
     if (!std::strcmp(argv[1], "batch"))
         return cmd_batch(argc, argv);
+    if (!std::strcmp(argv[1], "multi"))
+        return cmd_multi(argc, argv);
+    if (!std::strcmp(argv[1], "latency"))
+        return cmd_latency(argc, argv);
     return 2;
 }

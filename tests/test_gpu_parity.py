@@ -786,6 +786,58 @@ def test_compact_3x4_download_all_modes(ctx, player_dev, player, mode, pinned_ds
         sb.close(), b.close()
 
 
+@pytest.mark.parametrize("N,K", [(1, 1), (8, 1), (100, 1), (1000, 1), (5, 2)])
+def test_one_call_frame_for_small_batches(ctx, player, oracle, N, K):
+    """pcl_batch_frame: inputs + pose + AnimationResult rows in one call (one launch, one sync) for a handful of characters.
+    Rows match the oracle and the regular set / pose / download path; NULL inputs keep the previous frame's; the device
+    palette is the one a following pcl_batch_skin reads; the asynchronous form returns the same rows later."""
+    from piccolo_b200 import capi
+    sk, cl, am, mk = player
+    clips = [cl, A.make_variant_clip(cl, 17, seed=1234)]
+    skel = ctx.upload_skeleton(sk)
+    ids = np.int32([ctx.upload_clip(skel, c, am) for c in clips])
+    rng = np.random.default_rng(100 + N)
+    pick = rng.integers(0, 2, (N, K)).astype(np.int32)
+    if K == 2:
+        pick[:, 1] = 1 - pick[:, 0]
+    ph = rng.uniform(0, 1, (2, N, K)).astype(np.float32)
+    w = rng.uniform(0.2, 1, (N, K)).astype(np.float32)
+    b, b2 = ctx.batch(skel, N, K), ctx.batch(skel, N, K)
+    try:
+        sv, ocl = oracle.skeleton(sk), [oracle.clip(c, am) for c in clips]
+        l0 = ctx.launch_count()
+        rows = b.frame(clip_ids=ids[pick], phase=ph[0], weight=w if K > 1 else None)
+        assert ctx.launch_count() - l0 == (2 if (K > 1 and N <= 8) else 1)  # K = 1: the pose kernel writes the rows itself or a DMA fetches them
+        ref = oracle.pose_batch(sv, ocl, pick, ph[0], weight=w if K > 1 else None)
+        assert_mats_close(capi.expand_3x4(rows), ref, tol=MAT_TOL if K == 1 else 2e-5)
+        b2.set(clip_ids=ids[pick], phase=ph[0], weight=w if K > 1 else None)
+        b2.pose()
+        assert np.abs(b2.download_palette3x4() - rows).max() <= 2e-6
+        assert np.array_equal(b.download_palette3x4(), rows)  # the device palette is this frame's
+        # second frame: only the phases change; asynchronous form
+        assert b.frame(phase=ph[1], wait=False) is None
+        rows2 = b.frame_result()
+        ref2 = oracle.pose_batch(sv, ocl, pick, ph[1], weight=w if K > 1 else None)
+        assert_mats_close(capi.expand_3x4(rows2), ref2, tol=MAT_TOL if K == 1 else 2e-5)
+        with pytest.raises(capi.PclError):
+            b.frame(clip_ids=np.full((N, K), 10 ** 6, np.int32), phase=ph[0])
+    finally:
+        b.close(), b2.close()
+
+
+def test_one_call_frame_refuses_large_batches(ctx, player_dev):
+    from piccolo_b200 import capi
+    skel, clip = player_dev
+    N = 30000  # 30 000 x 58 x 48 B > PCL_FRAME_MAX_BYTES
+    b = ctx.batch(skel, N, 1)
+    try:
+        with pytest.raises(capi.PclError) as e:
+            b.frame(clip_ids=np.full((N, 1), clip, np.int32), phase=np.zeros((N, 1), np.float32))
+        assert e.value.code == -3
+    finally:
+        b.close()
+
+
 def test_render_handoff_layout(ctx, player_dev):
     """joint_matrices[1024 * instance_in_draw + slot], 64 instances per draw, slot 0 = identity, only J+1 slots touched
     (main_camera_pass.cpp:2284-2298; mesh_component.cpp:72-79)."""

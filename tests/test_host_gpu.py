@@ -65,3 +65,37 @@ def test_animation_batch_crowd(player, tmp_path, clip_count):
         rp, rn, rt = orc.lbs(mesh, orc.palette_slots(d["2"].reshape(N, 58, 16)[N - 8 + i]))
         assert np.abs(pos[i] - rp).max() <= 1e-4 * max(1.0, np.abs(rp).max())
         assert np.abs(d["5"].reshape(8, mesh.V, 6)[i][:, :3] - rn).max() <= 1e-4
+
+
+@pytest.mark.parametrize("n", [1, 8, 100])
+def test_components_of_a_level_pose_together(player, tmp_path, n):
+    """The reference's own call pattern (object.cpp:41-50: every GObject ticks its AnimationComponent, then
+    mesh_component.cpp:75 reads getResult()): n components record their ticks and the first getResult() of a frame poses all
+    of them in one launch.  Every component's phases are bit-exact, its result matches the oracle, a stand-alone Skeleton
+    driven with the reference's pair of calls gives the same matrices, and components joining / leaving do not disturb
+    the others."""
+    from oracle import pyoracle as O
+    sk, cl, am, mk = player
+    urls = H.write_player_tree(str(tmp_path), player, sparse=True)
+    ticks, dt = 7, 1 / 60
+    out = tmp_path / "multi.bin"
+    r = H.run(["multi", tmp_path, urls["object"], n, ticks, dt, out])
+    assert r.returncode == 0 and "multi ok" in r.stdout, r.stderr + r.stdout
+    d = H.read_dump(out)
+    orc = O.Oracle()
+    ph = (np.arange(n, dtype=np.float32) / np.float32(n))
+    for _ in range(ticks):
+        ph = np.float32([orc.advance(p, np.float32(dt), np.float32(0.76666998863220215)) for p in ph])
+    assert np.array_equal(d["1"], ph)  # animation_component.cpp:19-21, bit-exact
+    sv, cv = orc.skeleton(sk), orc.clip(cl, am)
+    ref, der = orc.pose_batch(sv, [cv], np.zeros((n, 1), np.int32), ph, derived=True)
+    for i in range(n):
+        assert np.array_equal(d["%di" % (100 + i)], np.arange(1, 59))
+        m = d[str(100 + i)].reshape(58, 16)
+        assert np.array_equal(m[:, 12:], np.tile(np.float32([0, 0, 0, 1]), (58, 1)))
+        assert_mats_close(m, ref[i])
+    assert np.abs(d["2"].reshape(58, 10) - der[n - 1]).max() <= 1e-5  # LevelDebugger's view of the last component
+    assert np.abs(d["3"].reshape(58, 16) - d["100"].reshape(58, 16)).max() <= 2e-6  # stand-alone Skeleton, same inputs
+    assert np.array_equal(d["4"], d["100"])  # component 0 after another one left and a new one joined (dt = 0 tick)
+    ref0 = orc.pose_batch(sv, [cv], np.zeros((1, 1), np.int32), np.float32([0.0]))
+    assert_mats_close(d["5"].reshape(58, 16), ref0[0])  # the late joiner, phase 0

@@ -1,7 +1,12 @@
 #!/usr/bin/env python
-"""stdin: bench.py output; prints the last JSON line's key numbers prefixed by argv[1:]."""
-import json, sys
-line = [l for l in sys.stdin.read().splitlines() if l.startswith("{")]
+"""bench_line.py FILE [label...]: prints the key numbers of the last JSON line of a bench.py output file.
+(Takes a file, never stdin: a tool that waits on an empty stdin hangs a GPU box until the call's limit.)"""
+import json, os, sys
+if len(sys.argv) < 2 or not os.path.exists(sys.argv[1]):
+    print("usage: bench_line.py FILE [label...]")
+    sys.exit(2)
+line = [l for l in open(sys.argv[1]).read().splitlines() if l.startswith("{")]
+sys.argv = sys.argv[:1] + sys.argv[2:]
 if not line:
     print(" ".join(sys.argv[1:]), "NO JSON LINE")
     sys.exit(0)
