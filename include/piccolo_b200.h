@@ -282,7 +282,9 @@ int pcl_batch_push_to_pool(pcl_batch* b, pcl_pool* pool, int64_t first);
  * "lbs_warps" (0 = auto, 8, 12: resident warps per SM of the crowd kernel); "lbs_vsplit" (0 = auto);
  * "lbs_inst_tile" (0 = auto, <= 16; lane-per-vertex kernels only); "lbs_cta_tile" (0 = auto, 32, 16, 8: instances per
  * CTA of variant 3 - auto takes the largest whose palettes fit in shared memory: 32 up to 82 bones, 16 up to ~165, 8 up to ~340);
- * "export_mode" (0 = auto, 1, 2, 3: see pcl_batch_download_palette3x4_async).
+ * "export_mode" (0 = auto, 1, 2, 3: see pcl_batch_download_palette3x4_async); "lbs_compact" (-1 = auto: when whole palettes
+ * would force variant 3 below 32 instances per CTA, 0 = never, 1 = whenever it fits: variant 3 keeps, per instance, only the
+ * palette rows the current block of 1024 vertices references).
  * PCL_ERR_INVALID for unknown keys. */
 int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
 

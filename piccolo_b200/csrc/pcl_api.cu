@@ -53,6 +53,13 @@ namespace
         VRec*   d_vrec = nullptr;        // lane = instance form: slot-stable influences, see lbs_inst_kernel
         VRec*   d_vrec_cta[3] = {nullptr, nullptr, nullptr}; // the same packed along lbs_cta_kernel's visiting order for S = 1, 2, 4
                                          // vertex streams per warp (built on first use: which S runs depends on the skeleton)
+        // compact form of lbs_cta_kernel (see LbsCParams::blk_sc): per block of LBS_C_BLK_VERTS vertices the palette slots it
+        // references, and record streams carrying block-local row numbers; blk_mmax < 0 = not analysed yet
+        VRec*     d_vrec_blk[3]  = {nullptr, nullptr, nullptr};
+        uint16_t* d_blk_slots    = nullptr;
+        int32_t*  d_blk_cnt      = nullptr;
+        int32_t   blk_mmax = -1, blk_cap = 0, n_blocks = 0;
+        std::vector<std::vector<uint16_t>> h_blk_slots;
         std::vector<float>  h_pos, h_nrm, h_tan; // gated, padded host copies the record streams are packed from
         std::vector<int4>   h_idx;
         std::vector<float4> h_w;
@@ -91,7 +98,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0, opt_lbs_compact = -1;
     void*        h_small = nullptr;  // pinned staging of small synchronous palette read-backs
     bool         debug_sync = false; // PICCOLO_B200_DEBUG_SYNC=1: synchronise after every launch
     int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
@@ -344,6 +351,92 @@ namespace
         return upload(c, &m.d_vrec_cta[si], hvc);
     }
 
+    // Which palette slots does each block of LBS_C_BLK_VERTS consecutive vertices reference?  (Once per mesh; decides whether the
+    // compact form of lbs_cta_kernel pays: a coherent 256-bone character touches a few dozen bones per 1024 vertices.)
+    int analyse_blocks(pcl_ctx* c, MeshRec& m)
+    {
+        if (m.blk_mmax >= 0)
+            return PCL_OK;
+        const int nb = (m.Vp + LBS_C_BLK_VERTS - 1) / LBS_C_BLK_VERTS + 1; // + 1: a record stage may overrun into a padding block
+        m.h_blk_slots.assign(nb, {});
+        int mmax = 1;
+        for (int b = 0; b < nb; b++)
+        {
+            std::vector<char> used((size_t)m.max_slot + 1, 0);
+            for (size_t v = (size_t)b * LBS_C_BLK_VERTS; v < (size_t)(b + 1) * LBS_C_BLK_VERTS && v < (size_t)m.V; v++)
+            {
+                const int   id[4] = {m.h_idx[v].x, m.h_idx[v].y, m.h_idx[v].z, m.h_idx[v].w};
+                const float w[4]  = {m.h_w[v].x, m.h_w[v].y, m.h_w[v].z, m.h_w[v].w};
+                for (int k = 0; k < 4; k++)
+                    if (w[k] != 0.f)
+                        used[id[k]] = 1;
+            }
+            used[0] = 1; // slot 0 (the identity) is what gated and padding influences name
+            for (int sl = 0; sl <= m.max_slot; sl++)
+                if (used[sl])
+                    m.h_blk_slots[b].push_back((uint16_t)sl);
+            mmax = std::max(mmax, (int)m.h_blk_slots[b].size());
+        }
+        m.n_blocks = nb, m.blk_cap = mmax;
+        std::vector<uint16_t> flat((size_t)nb * mmax, 0);
+        std::vector<int32_t>  cnt(nb);
+        for (int b = 0; b < nb; b++)
+        {
+            cnt[b] = (int32_t)m.h_blk_slots[b].size();
+            std::copy(m.h_blk_slots[b].begin(), m.h_blk_slots[b].end(), flat.begin() + (size_t)b * mmax);
+        }
+        int rc;
+        if ((rc = upload(c, &m.d_blk_slots, flat)) || (rc = upload(c, &m.d_blk_cnt, cnt)))
+            return rc;
+        m.blk_mmax = mmax;
+        return PCL_OK;
+    }
+
+    // the record stream of ensure_vrec_cta with block-local row numbers: at every block start each (warp, stream) sequence starts
+    // cold (all four slots reload, resident bones forgotten)
+    int ensure_vrec_cta_compact(pcl_ctx* c, MeshRec& m, int T)
+    {
+        const int si = T == 32 ? 0 : (T == 16 ? 1 : 2);
+        if (m.d_vrec_blk[si])
+            return PCL_OK;
+        const size_t      scv  = (size_t)lbs_c_scv(T);
+        const size_t      bsc  = LBS_C_BLK_VERTS / scv; // superchunks per block
+        const size_t      n_sc = ((size_t)m.Vp + scv - 1) / scv;
+        const size_t      pad  = (size_t)lbs_c_rsc(T);
+        std::vector<VRec> hvc((n_sc + pad) * scv);
+        std::memset(hvc.data(), 0, hvc.size() * sizeof(VRec));
+        for (size_t vw = 0; vw < scv / LBS_C_VPW; vw++)
+        {
+            int  cw[4] = {0, 0, 0, 0};
+            VRec last {}; // the previously visited record, in GLOBAL slot numbers (what the reload masks are derived from)
+            bool have_last = false;
+            for (size_t sc = 0; sc < n_sc + pad; sc++)
+            {
+                const size_t blk = std::min<size_t>(sc / bsc, (size_t)m.n_blocks - 1);
+                if (sc % bsc == 0)
+                    cw[0] = cw[1] = cw[2] = cw[3] = 0, have_last = false; // slot 0 is in every block's list
+                const std::vector<uint16_t>& list = m.h_blk_slots[blk];
+                auto loc = [&list](uint32_t off3) -> uint32_t {
+                    const uint16_t slot = (uint16_t)(off3 / 3u);
+                    auto           it   = std::lower_bound(list.begin(), list.end(), slot);
+                    return (it != list.end() && *it == slot) ? (uint32_t)(it - list.begin()) * 3u : 0u;
+                };
+                for (int j = 0; j < LBS_C_VPW; j++)
+                {
+                    const size_t v = sc * scv + vw * LBS_C_VPW + j;
+                    VRec         g {};
+                    pack_vrec(m, g, v, cw, have_last ? &last : nullptr);
+                    last = g, have_last = true;
+                    // global slot numbers -> rows of this block's list
+                    g.i01  = loc(g.i01 & 0xffffu) | (loc(g.i01 >> 16) << 16);
+                    g.i23  = loc(g.i23 & 0xffffu) | (loc(g.i23 >> 16) << 16);
+                    hvc[v] = g;
+                }
+            }
+        }
+        return upload(c, &m.d_vrec_blk[si], hvc);
+    }
+
     bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size(); }
 
     // 2-D tensor map over a skinned stream [capacity][row_floats], box = 32 rows x 32 floats (128 B), 128-byte swizzle.
@@ -465,7 +558,7 @@ extern "C"
         for (auto& cl : c->clips)
             cudaFree(cl.d_blob);
         for (auto& m : c->meshes)
-            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec), cudaFree(m.d_vrec_cta[0]), cudaFree(m.d_vrec_cta[1]), cudaFree(m.d_vrec_cta[2]);
+            cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec), cudaFree(m.d_vrec_cta[0]), cudaFree(m.d_vrec_cta[1]), cudaFree(m.d_vrec_cta[2]), cudaFree(m.d_vrec_blk[0]), cudaFree(m.d_vrec_blk[1]), cudaFree(m.d_vrec_blk[2]), cudaFree(m.d_blk_slots), cudaFree(m.d_blk_cnt);
         cudaFree(c->d_clips);
         for (void* p : c->host_allocs)
             cudaFreeHost(p);
@@ -560,6 +653,8 @@ extern "C"
             c->opt_lbs_cta_tile = v;
         else if (k == "export_mode" && v >= 0 && v <= 3)
             c->opt_export_mode = v;
+        else if (k == "lbs_compact" && v >= -1 && v <= 1)
+            c->opt_lbs_compact = v;
         else
             return fail(c, PCL_ERR_INVALID, "pcl_set_option: unknown key or bad value: " + k);
         return PCL_OK;
@@ -1655,6 +1750,24 @@ extern "C"
             for (int cand = 32; cand >= 8 && !cT; cand >>= 1)
                 if ((c->opt_lbs_cta_tile == 0 || c->opt_lbs_cta_tile == cand) && lbs_c_smem_bytes(prow, nt, 2, cand) <= (size_t)c->max_smem_optin)
                     cT = cand;
+            // ... or, when whole palettes force a small tile, the compact form: per block of 1024 vertices only the rows that block
+            // references (a coherent 256-bone character: a few dozen), which brings the tile back to 32 or 16 instances
+            bool compact = false;
+            int  prow_c  = prow;
+            if (m.max_slot * 3 <= 0xffff && out->has_tmaps && c->opt_lbs_compact != 0 && (cT < 32 || c->opt_lbs_compact == 1))
+            {
+                MeshRec& mm = c->meshes[mesh];
+                { int rc__ = analyse_blocks(c, mm); if (rc__) return rc__; }
+                prow_c  = (mm.blk_mmax * 3) | 1;
+                int cTc = 0;
+                for (int cand = 32; cand >= 8 && !cTc; cand >>= 1)
+                    if ((c->opt_lbs_cta_tile == 0 || c->opt_lbs_cta_tile == cand) && lbs_c_smem_bytes(prow_c, nt, 2, cand) <= (size_t)c->max_smem_optin)
+                        cTc = cand;
+                if (cTc > cT || (c->opt_lbs_compact == 1 && cTc >= cT && cTc > 0))
+                    compact = true, cT = cTc;
+                else
+                    prow_c = prow;
+            }
             const bool fits3 = cT && m.max_slot * 3 <= 0xffff && out->has_tmaps;
             if (var < 0)
             {
@@ -1667,8 +1780,8 @@ extern "C"
             {
                 if (!fits3)
                     return fail(c, PCL_ERR_UNSUPPORTED, "pcl_batch_skin: lbs_variant 3 needs 8 palettes in shared memory and tensor maps");
-                const int    ctiles = lbs_c_smem_bytes(prow, nt, 3, cT) <= (size_t)c->max_smem_optin ? 3 : 2;
-                const size_t smem_c = lbs_c_smem_bytes(prow, nt, ctiles, cT);
+                const int    ctiles = lbs_c_smem_bytes(prow_c, nt, 3, cT) <= (size_t)c->max_smem_optin ? 3 : 2;
+                const size_t smem_c = lbs_c_smem_bytes(prow_c, nt, ctiles, cT);
                 const int    ti     = cT == 32 ? 0 : (cT == 16 ? 1 : 2);
                 const long long full = (count + cT - 1) / cT; // tiles; the last one may be ragged
                 // rows the stores may touch: the ring's capacity for whole tiles; for a ragged last tile, maps of this launch's
@@ -1684,11 +1797,13 @@ extern "C"
                 }
                 {
                     MeshRec& mm = c->meshes[mesh];
-                    { int rc__ = ensure_vrec_cta(c, mm, cT); if (rc__) return rc__; }
+                    { int rc__ = compact ? ensure_vrec_cta_compact(c, mm, cT) : ensure_vrec_cta(c, mm, cT); if (rc__) return rc__; }
                     LbsCParams q {};
-                    q.vrec = mm.d_vrec_cta[ti], q.palette = b->d_palette;
+                    q.vrec = compact ? mm.d_vrec_blk[ti] : mm.d_vrec_cta[ti], q.palette = b->d_palette;
+                    if (compact)
+                        q.blk_sc = LBS_C_BLK_VERTS / lbs_c_scv(cT), q.blk_cap = mm.blk_cap, q.blk_slots = mm.d_blk_slots, q.blk_cnt = mm.d_blk_cnt;
                     q.first = first, q.slot_first = slot_first, q.count = count, q.n_tiles = (int32_t)full;
-                    q.Vp = m.Vp, q.n_sc = (m.Vp + lbs_c_scv(cT) - 1) / lbs_c_scv(cT), q.pitch = s.pitch, q.prow = prow;
+                    q.Vp = m.Vp, q.n_sc = (m.Vp + lbs_c_scv(cT) - 1) / lbs_c_scv(cT), q.pitch = s.pitch, q.prow = prow_c;
                     int vs = c->opt_lbs_vsplit;
                     if (vs == 0)
                     {
@@ -1708,6 +1823,12 @@ extern "C"
                         }
                     }
                     q.vsplit = std::max(1, std::min(vs, q.n_sc));
+                    q.per_sc = (q.n_sc + q.vsplit - 1) / q.vsplit;
+                    if (compact) // runs start on block boundaries
+                    {
+                        q.per_sc = (q.per_sc + q.blk_sc - 1) / q.blk_sc * q.blk_sc;
+                        q.vsplit = (q.n_sc + q.per_sc - 1) / q.per_sc;
+                    }
                     const unsigned grid = (unsigned)(full * q.vsplit);
 #define PCL_LAUNCH_LBSC(NT_, TL_, T_)                                                                                        \
     {                                                                                                                       \

@@ -1588,6 +1588,7 @@ namespace pcl
     constexpr int LBS_C_TILE_BYTES_POS = 3 * 32 * 128;     // per staging tile: 32 lanes x 4 vertices x 8 warps x 12 B
     constexpr int LBS_C_TILE_BYTES_NT  = 6 * 32 * 128;
     constexpr int LBS_C_RSTAGE_BYTES   = 8192;             // one vertex-record stage (128 records)
+    constexpr int LBS_C_BLK_VERTS      = 1024;             // compact form: vertices per block (32 / 16 / 8 superchunks for T = 32 / 16 / 8)
     // A tile holds T = 32, 16 or 8 INSTANCES; a warp then carries S = 32 / T vertex streams side by side (lanes
     // [st*T, st*T+T) = the T instances of stream st), which is what lets skeletons whose 32 palettes do not fit in shared
     // memory (more than 82 bones) still use this kernel: 16 palettes fit up to ~165 bones, 8 up to ~340.
@@ -1622,6 +1623,13 @@ namespace pcl
         const float4* palette; // [N][pitch][3]
         long long     first, slot_first, count; // count need not be a multiple of T: see the last tile below
         int32_t       n_tiles, Vp, n_sc, pitch, prow, vsplit;
+        int32_t       per_sc;  // superchunks per CTA (a multiple of blk_sc in the compact form)
+        // compact form (big skeletons, coherent meshes): instead of whole palettes the CTA keeps, per instance, only the rows
+        // the current BLOCK of LBS_C_BLK_VERTS vertices references; the records carry block-local row numbers
+        int32_t         blk_sc;    // superchunks per block, 0 = whole palettes
+        int32_t         blk_cap;   // row stride of blk_slots
+        const uint16_t* blk_slots; // [n_blocks][blk_cap] palette slots of each block, ascending
+        const int32_t*  blk_cnt;   // [n_blocks]
     };
 
     template<bool NT, int LBS_C_TILES, int T>
@@ -1648,11 +1656,12 @@ namespace pcl
         uint64_t*      rbar  = bars + 1;
 
         // this CTA's run of superchunks
-        const int per  = (par.n_sc + par.vsplit - 1) / par.vsplit;
+        const int per  = par.per_sc;
         const int s_lo = split * per, s_hi = min(par.n_sc, s_lo + per);
         if (s_lo >= s_hi)
             return;
-        const int n_steps = s_hi - s_lo;
+        const int  n_steps = s_hi - s_lo;
+        const bool compact = par.blk_sc != 0;
         // named barriers: 1 + b = tile b full (compute arrives, store warp syncs); 1 + TILES + b = tile b empty (store arrives, compute syncs)
 
         if (tid == 0)
@@ -1669,13 +1678,16 @@ namespace pcl
             // ---------------- store / load warp ----------------
             if (lane == 0)
             {
-                const uint32_t row_bytes = (uint32_t)par.pitch * 48;
-                mbar_expect_tx(&bars[0], row_bytes * T);
-                // a ragged last tile: the missing instances shadow the last real one; their rows lie beyond the row count of
-                // the tensor maps the launcher built for this launch, so the stores drop them
-                for (int i = 0; i < T; i++)
-                    tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + min(i0 + i, par.count - 1)) * par.pitch * 3, row_bytes,
-                             &bars[0]);
+                if (!compact)
+                {
+                    const uint32_t row_bytes = (uint32_t)par.pitch * 48;
+                    mbar_expect_tx(&bars[0], row_bytes * T);
+                    // a ragged last tile: the missing instances shadow the last real one; their rows lie beyond the row count of
+                    // the tensor maps the launcher built for this launch, so the stores drop them
+                    for (int i = 0; i < T; i++)
+                        tma_load(pal_s + (size_t)i * par.prow, par.palette + (size_t)(par.first + min(i0 + i, par.count - 1)) * par.pitch * 3,
+                                 row_bytes, &bars[0]);
+                }
                 for (int st = 0; st < LBS_C_RSTAGES && st * RSC < n_steps; st++)
                 {
                     mbar_expect_tx(&rbar[st], LBS_C_RSTAGE_BYTES);
@@ -1721,15 +1733,22 @@ namespace pcl
         }
 
         // ---------------- compute warps ----------------
-        mbar_wait(&bars[0], 0);
         const int     row  = lane % T;          // instance within the tile
         const int     vw   = warp * S + lane / T; // virtual warp: which 4 vertices of every superchunk
         const float4* prow = pal_s + (size_t)row * par.prow;
         float4 m[4][3];
+        if (!compact)
         {
+            mbar_wait(&bars[0], 0);
             const uint4 d = __ldg(reinterpret_cast<const uint4*>(&par.vrec[(size_t)s_lo * SCV + vw * LBS_C_VPW].w3));
             lbs_i_load(m[0], prow, d.y & 0xffffu), lbs_i_load(m[1], prow, d.y >> 16);
             lbs_i_load(m[2], prow, d.z & 0xffffu), lbs_i_load(m[3], prow, d.z >> 16);
+        }
+        else
+        {
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                m[k][0] = m[k][1] = m[k][2] = make_float4(0.f, 0.f, 0.f, 0.f); // every stream's first record of a block reloads all four
         }
         // swizzled staging offsets of this lane for the 16-byte units its virtual warp owns: positions: units 3 vw .. 3 vw + 2,
         // normal+tangent: units 6 vw .. 6 vw + 5; unit U -> sub-tile U >> 3, chunk (U & 7) ^ (row & 7)
@@ -1749,6 +1768,48 @@ namespace pcl
         for (int s = 0; s < n_steps; s++)
         {
             const int b = s % LBS_C_TILES;
+            if (compact && ((s_lo + s) % par.blk_sc) == 0)
+            {
+                // A new block of vertices: bring in, for each of the tile's instances, the palette rows this block references
+                // (a few dozen of a big skeleton's hundreds: what lets 32 instances share a CTA where 32 whole palettes would
+                // not fit).  The compute warps copy them - 48-byte rows from all over each instance's palette, far too many and
+                // too small for bulk copies - between two rendezvous: nobody still reads the old rows, nobody reads half-written
+                // new ones.  ~60 KB per ~1.2 MB of output: a bubble of a few percent.
+                const int       blk  = (s_lo + s) / par.blk_sc;
+                const uint16_t* list = par.blk_slots + (size_t)blk * par.blk_cap;
+                const int       nu   = __ldg(par.blk_cnt + blk) * 3; // 16-byte units per instance
+                // where this lane's units come from is the same for every instance: looked up once (up to 8 units per lane:
+                // 82 rows x 3 units is the most a tile of 32 holds), then every row copy is a burst of independent loads
+                constexpr int GU = 8;
+                int           goff[GU];
+#pragma unroll
+                for (int k = 0; k < GU; k++)
+                {
+                    const int u = lane + 32 * k, q = u / 3;
+                    goff[k]     = u < nu ? (int)__ldg(list + q) * 3 + (u - q * 3) : -1;
+                }
+                named_sync(1 + 2 * LBS_C_TILES, LBS_C_WARPS * 32);
+                for (int inst = warp; inst < T; inst += LBS_C_WARPS)
+                {
+                    const float4* src = par.palette + (size_t)(par.first + min(i0 + inst, par.count - 1)) * par.pitch * 3;
+                    float4*       dst = pal_s + (size_t)inst * par.prow;
+                    float4        v[GU];
+#pragma unroll
+                    for (int k = 0; k < GU; k++)
+                        if (goff[k] >= 0)
+                            v[k] = __ldg(src + goff[k]);
+#pragma unroll
+                    for (int k = 0; k < GU; k++)
+                        if (goff[k] >= 0)
+                            dst[lane + 32 * k] = v[k];
+                    for (int u = lane + 32 * GU; u < nu; u += 32) // (tiles of 16 / 8 instances can hold more rows)
+                    {
+                        const int q = u / 3;
+                        dst[u]      = __ldg(src + (int)__ldg(list + q) * 3 + (u - q * 3));
+                    }
+                }
+                named_sync(1 + 2 * LBS_C_TILES, LBS_C_WARPS * 32);
+            }
             const int ridx = s / RSC, rsub = s - ridx * RSC, rst = ridx % LBS_C_RSTAGES;
             if (rsub == 0)
                 mbar_wait(&rbar[rst], (uint32_t)(ridx / LBS_C_RSTAGES) & 1);

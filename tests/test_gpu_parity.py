@@ -561,13 +561,49 @@ def test_lbs_crowd_kernels_on_mid_sized_skeletons(ctx, oracle, J, variant):
     N = 192 + (J % 7)  # ragged against 32 / 16 / 8 for some J
     ph = np.random.default_rng(J).uniform(0, 1, N).astype(np.float32)
     if (J > 82 and variant == 2) or J >= 400:
-        with pytest.raises(capi.PclError) as e:
-            _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
-        assert e.value.code == -3
-        ctx.set_option("lbs_variant", -1)
-        return
+        ctx.set_option("lbs_compact", 0)  # whole palettes only: 400 bones x 8 instances do not fit
+        try:
+            with pytest.raises(capi.PclError) as e:
+                _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
+            assert e.value.code == -3
+        finally:
+            ctx.set_option("lbs_variant", -1), ctx.set_option("lbs_compact", -1)
+        if variant == 2:
+            return  # (variant 3 goes on: the compact form below takes a coherent 400-bone mesh)
     pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, capi.PCL_SKIN_POS_NRM_TAN, variant)
     _check_skin(oracle, mesh, pal[::37], pos[::37], nt[::37])
+
+
+@pytest.mark.parametrize("J,V,N,compact", [(58, 4100, 70, 1), (120, 9000, 45, 1), (256, 20000, 37, -1), (256, 20000, 64, 1), (400, 6000, 33, -1)])
+@pytest.mark.parametrize("flags_nt", [True, False])
+def test_lbs_compact_form_block_local_palette_rows(ctx, oracle, J, V, N, compact, flags_nt):
+    """lbs_cta_kernel's compact form: per block of 1024 vertices the CTA keeps only the palette rows that block references
+    and the records carry block-local row numbers.  Forced on skeletons whose whole palettes would fit too (player-sized, 120
+    bones), chosen automatically for coherent 256- and 400-bone characters; ragged instance counts, vertex counts that are
+    not a multiple of a block, both output sets; every result against the oracle and against the whole-palette kernels."""
+    from piccolo_b200 import capi
+    sk = A.make_synthetic_skeleton(J, branching=2, seed=J) if J != 58 else A.load_player()[0]
+    cl, am = (A.make_synthetic_clip(sk, 12, seed=J + 1) if J != 58 else A.load_player()[1:3])
+    mesh = A.make_coherent_mesh(sk, V=V, seed=J)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    mh = ctx.upload_mesh(mesh, J)
+    ph = np.random.default_rng(J + N).uniform(0, 1, N).astype(np.float32)
+    flags = capi.PCL_SKIN_POS_NRM_TAN if flags_nt else capi.PCL_SKIN_POS
+    ctx.set_option("lbs_compact", compact)
+    try:
+        pos, nt, pal = _skin(ctx, skel, clip, mh, mesh.V, N, ph, flags, 3)
+    finally:
+        ctx.set_option("lbs_compact", -1)
+    sel = sorted({0, N - 1, N // 2, N // 3})
+    _check_skin(oracle, mesh, pal[sel], pos[sel], nt[sel] if nt is not None else None)
+    if J <= 340:  # the whole-palette form of the same kernel (another tile size for the big skeletons): same sums, slot order may differ
+        ctx.set_option("lbs_compact", 0)
+        try:
+            pos0, nt0, _ = _skin(ctx, skel, clip, mh, mesh.V, N, ph, flags, 3)
+        finally:
+            ctx.set_option("lbs_compact", -1)
+        assert np.abs(pos0 - pos).max() <= 1e-5 * max(1.0, float(np.abs(pos0).max()))
 
 
 @pytest.mark.parametrize("cta_tile", [16, 8])
