@@ -251,6 +251,109 @@ def host_link_ceiling(torch, local, nbytes, barrier, max_over_ranks, reps=6):
         return None
 
 
+def palette_pool_check(grp, ctx, capi, skel, clip, n_total=200000, steps=5):
+    """SURVEY.md 8f.4 with the driver watching (world >= 2, outside every timed region): all ranks pose their shard of one crowd
+    into a palette pool on rank 0's GPU - once with the copy engine (pose locally, push), once attached (the pose kernel's
+    stores travel over NVLink) - and rank 0 compares the gathered rows, bit for bit, with its own pose of the whole crowd.
+    Every rank reaches every barrier whatever happens locally (errors are agreed on with a max-reduction before each step
+    that needs a peer), so a failure here costs this entry, not the bench line."""
+    from piccolo_b200.sharding import shard_range, open_gathered_pool
+    res, state = {"instances": n_total, "world": grp.world}, {"bad": 0.0, "why": ""}
+
+    def guarded(fn):
+        if state["bad"]:
+            return None
+        try:
+            return fn()
+        except Exception as e:  # noqa: BLE001
+            state["bad"], state["why"] = 1.0, "%s: %s" % (type(e).__name__, str(e)[:160])
+            return None
+
+    def agree():
+        state["bad"] = grp.max(state["bad"])
+        return not state["bad"]
+
+    ph = np.modf(np.arange(n_total, dtype=np.float64) * 0.6180339887)[0].astype(np.float32)
+    first, count = shard_range(n_total, grp.world, grp.rank)
+    b = guarded(lambda: ctx.batch(skel, count, 1))
+    guarded(lambda: b.set(clip_ids=np.full((count, 1), clip, np.int32), phase=ph[first:first + count]))
+    pool = None
+    try:
+        pool = open_gathered_pool(grp, ctx, skel, n_total, consumer=0)  # (holds a broadcast: every rank calls it)
+    except Exception as e:  # noqa: BLE001
+        state["bad"], state["why"] = 1.0, "%s: %s" % (type(e).__name__, str(e)[:160])
+    pushed = got = None
+    if agree():
+        def timed(fn):
+            for _ in range(2):
+                fn()
+            ctx.sync()
+            ctx.timer_begin()
+            for _ in range(steps):
+                fn()
+            return ctx.timer_end() / steps
+        ms_local = guarded(lambda: timed(b.pose))
+        ms_push = guarded(lambda: timed(lambda: (b.pose(), b.push_to_pool(pool, first))))
+        guarded(ctx.sync)
+        grp.barrier()
+        if grp.rank == 0:
+            def fetch():
+                view = ctx.batch(skel, n_total, 1)
+                try:
+                    view.attach_pool(pool, 0)
+                    view.adopt_palettes()
+                    return view.download_palette3x4()
+                finally:
+                    view.close()
+            pushed = guarded(fetch)
+        grp.barrier()
+        guarded(lambda: b.attach_pool(pool, first))
+        ms_att = guarded(lambda: timed(b.pose))
+        guarded(ctx.sync)
+        grp.barrier()  # every producer's stores have landed
+        if grp.rank == 0:
+            got = guarded(fetch)
+
+            def whole():
+                w = ctx.batch(skel, n_total, 1)
+                try:
+                    w.set(clip_ids=np.full((n_total, 1), clip, np.int32), phase=ph)
+                    w.pose()
+                    return w.download_palette3x4()
+                finally:
+                    w.close()
+            ref = guarded(whole)
+            if not state["bad"]:
+                res["identical"] = bool(np.array_equal(got, ref)) and bool(np.array_equal(pushed, ref))
+        grp.barrier()
+        ms = [grp.max(x if x is not None else 0.0) for x in (ms_local, ms_push, ms_att)]
+        remote = (n_total - count) * 60 * 48 / max(grp.world - 1, 1)  # bytes one producer sends
+        if not state["bad"] and all(ms):
+            res.update({"pose_ms_local_target": round(ms[0], 4), "pose_plus_push_ms": round(ms[1], 4), "pose_ms_attached": round(ms[2], 4),
+                        "attached_GBps_per_producer": round(remote / ms[2] / 1e6, 1), "pushed_GBps_per_producer": round(remote / ms[1] / 1e6, 1)})
+    if b is not None:
+        try:
+            b.close()
+        except Exception:  # noqa: BLE001
+            pass
+    grp.barrier()
+    if pool is not None and grp.rank != 0:
+        try:
+            pool.close()  # unmap before the owner frees
+        except Exception:  # noqa: BLE001
+            pass
+    grp.barrier()
+    if pool is not None and grp.rank == 0:
+        try:
+            pool.close()
+        except Exception:  # noqa: BLE001
+            pass
+    agree()
+    if state["bad"]:
+        res["error"] = state["why"] or "a peer rank failed"
+    return res
+
+
 def bind_to_gpu_numa_node(local):
     """Pin this rank's host threads (and thereby its pinned-buffer pages) to the CPUs nearest its GPU: with 8 ranks
     downloading 371 MB per step each, cross-socket traffic otherwise halves the end-to-end number."""
@@ -367,8 +470,12 @@ def run_ours(args):
 
     tr = profiled_traffic()
     if tr and tr.get("instances_per_launch") == chunks[0][1] and tr.get("vertices") == mesh.V:
-        roofline["traffic"] = tr["dram_bytes_per_launch"]
-        roofline["traffic_source"] = tr["source"]
+        from piccolo_b200.build import kernel_sha16
+        if tr.get("kernel_sha16") == kernel_sha16():  # a capture of OTHER kernel sources says nothing about this run
+            roofline["traffic"] = tr["dram_bytes_per_launch"]
+            roofline["traffic_source"] = tr["source"]
+        else:
+            roofline["traffic_note"] = "profiles/lbs_traffic.json was captured on other kernel sources (hash %s); not reported" % tr.get("kernel_sha16")
 
     # ---- end to end through the C ABI with host buffers -------------------------------------------
     for _ in range(max(1, args.warmup // 2)):
@@ -392,6 +499,9 @@ def run_ours(args):
         sb.close()  # give the 14.7 GB ring back first
         sb = None
         others = other_configs(ctx, capi, grp, sk, cl, am, mk, skel, c0, peak, with_cpu=(world == 1 and not args.no_cpu_baseline))
+        if world >= 2:
+            others = others or {}
+            others["palette_pool"] = palette_pool_check(grp, ctx, capi, skel, c0)
 
     total = N * world
     out = {

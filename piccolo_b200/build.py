@@ -26,6 +26,16 @@ def _newer(target, sources):
     return any(os.path.getmtime(s) > t for s in sources)
 
 
+def kernel_sha16() -> str:
+    """Hash of the CUDA sources the library is built from: ties a profile (profiles/lbs_traffic.json) to the kernels it measured."""
+    import hashlib
+    h = hashlib.sha256()
+    csrc = os.path.join(PKG, "csrc")
+    for f in sorted(os.listdir(csrc)):
+        h.update(open(os.path.join(csrc, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
     csrc = os.path.join(PKG, "csrc")
     srcs = [os.path.join(csrc, f) for f in sorted(os.listdir(csrc))] + [os.path.join(ROOT, "include", "piccolo_b200.h")]
