@@ -5,6 +5,7 @@
 #include "pcl_kernels.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <climits>
 #include <cmath>
 #include <cstdio>
@@ -19,7 +20,8 @@ using namespace pcl;
 
 namespace
 {
-    std::string g_create_error;
+    // pcl_create failures of concurrent threads: the text is per thread (pcl_last_error(NULL) reads the caller's own)
+    thread_local std::string g_create_error;
 
     struct SkelRec
     {
@@ -72,7 +74,7 @@ static __device__ __align__(256) unsigned char g_static_export[PCL_STATIC_EXPORT
 #define PCL_STATIC_MAX_DEVICES 64
 #define PCL_SMALL_EXPORT_BYTES (32u << 10) /* measured: ahead up to ~8 player instances, behind the DMA path from 32 */
 #define PCL_FRAME_DIRECT_BYTES (24u << 10) /* pcl_batch_frame: rows written by the kernel into pinned memory up to 8 player instances */
-static void* g_static_export_addr[PCL_STATIC_MAX_DEVICES]; // device address of the array, per device (0 = not looked up yet)
+static std::atomic<void*> g_static_export_addr[PCL_STATIC_MAX_DEVICES]; // device address of the array, per device (0 = not looked up yet)
 
 // Which skeleton's step records currently sit in the device's __constant__ bank (pose_simple_kernel).  The bank is
 // per device, shared by every context on it.
@@ -216,7 +218,16 @@ namespace
     {
         PCL_CK(c, cudaMalloc((void**)dptr, std::max<size_t>(h.size(), 1) * sizeof(T)));
         if (!h.empty())
-            PCL_CK(c, copy_h2d(c, *dptr, h.data(), h.size() * sizeof(T)));
+        {
+            const cudaError_t e = copy_h2d(c, *dptr, h.data(), h.size() * sizeof(T));
+            if (e != cudaSuccess) // nothing of a failed upload stays behind
+            {
+                cudaFree(*dptr);
+                *dptr = nullptr;
+                (void)cudaGetLastError();
+                return fail(c, PCL_ERR_CUDA, std::string("upload: ") + cudaGetErrorString(e));
+            }
+        }
         return PCL_OK;
     }
 
@@ -446,7 +457,8 @@ namespace
     {
         typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                       const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-        static encode_fn encode = nullptr;
+        static std::atomic<encode_fn> encode_slot {nullptr}; // contexts may be driven from different threads
+        encode_fn                     encode = encode_slot.load(std::memory_order_acquire);
         if (!encode)
         {
             void*                           fn = nullptr;
@@ -457,6 +469,7 @@ namespace
                 return false;
             }
             encode = (encode_fn)fn;
+            encode_slot.store(encode, std::memory_order_release);
         }
         if (row_floats >= (1LL << 32) || capacity >= (1LL << 32))
             return false;
@@ -764,7 +777,10 @@ extern "C"
             }
             s.n_rounds = (int32_t)(sched.size() / POSE_L_WARPS);
             if ((rc = upload(c, &s.d_sched, sched)) != PCL_OK)
+            {
+                cudaFree(s.d_steps), cudaFree(s.d_sched);
                 return rc;
+            }
         }
         c->skels.push_back(std::move(s));
         *out = (pcl_skel)c->skels.size() - 1;
@@ -802,6 +818,17 @@ extern "C"
             return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: bad argument");
         if (node_count > C)
             return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: node_count exceeds the number of channels");
+        if (total_frame < 1)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: total_frame < 1");
+        if (convert_len > 0 && !convert)
+            return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: convert == NULL");
+        {
+            long long np = 0, nr = 0, ns = 0;
+            for (int n = 0; n < C; n++)
+                np += std::max(key_counts[3 * n], 0), nr += std::max(key_counts[3 * n + 1], 0), ns += std::max(key_counts[3 * n + 2], 0);
+            if ((np > 0 && !pos) || (nr > 0 && !rot) || (ns > 0 && !scl))
+                return fail(c, PCL_ERR_INVALID, "pcl_upload_clip: a key array is NULL although its tracks have keys");
+        }
         PCL_CK(c, cudaSetDevice(c->device));
         const int J   = c->skels[skel].J;
         const int NCH = std::min(node_count, convert_len); // skeleton.cpp:57-59
@@ -898,16 +925,21 @@ extern "C"
         ClipHost     ch;
         ch.skel = skel;
         PCL_CK(c, cudaMalloc(&ch.d_blob, total));
-        unsigned char* d = (unsigned char*)ch.d_blob;
-        PCL_CK(c, copy_h2d(c, d, keys.data(), kb));
-        PCL_CK(c, copy_h2d(c, d + up16(kb), first.data(), fb));
-        PCL_CK(c, copy_h2d(c, d + up16(kb) + up16(fb), next.data(), nb));
-        PCL_CK(c, copy_h2d(c, d + up16(kb) + up16(fb) + up16(nb), hic.data(), hb));
+        unsigned char* d  = (unsigned char*)ch.d_blob;
         unsigned char* d2 = d + up16(kb) + up16(fb) + up16(nb) + up16(hb);
-        if (simple)
         {
-            PCL_CK(c, copy_h2d(c, d2, skeys.data(), skb));
-            PCL_CK(c, copy_h2d(c, d2 + up16(skb), sanim.data(), shb));
+            cudaError_t e = copy_h2d(c, d, keys.data(), kb);
+            if (e == cudaSuccess) e = copy_h2d(c, d + up16(kb), first.data(), fb);
+            if (e == cudaSuccess) e = copy_h2d(c, d + up16(kb) + up16(fb), next.data(), nb);
+            if (e == cudaSuccess) e = copy_h2d(c, d + up16(kb) + up16(fb) + up16(nb), hic.data(), hb);
+            if (e == cudaSuccess && simple) e = copy_h2d(c, d2, skeys.data(), skb);
+            if (e == cudaSuccess && simple) e = copy_h2d(c, d2 + up16(skb), sanim.data(), shb);
+            if (e != cudaSuccess) // nothing of a failed upload stays behind
+            {
+                cudaFree(ch.d_blob);
+                (void)cudaGetLastError();
+                return fail(c, PCL_ERR_CUDA, std::string("pcl_upload_clip: ") + cudaGetErrorString(e));
+            }
         }
         ch.rec.keys           = (const float4*)d;
         ch.rec.first_chan     = (const int32_t*)(d + up16(kb));
@@ -959,8 +991,17 @@ extern "C"
             PCL_CK(c, cudaStreamSynchronize(c->compute));
             PCL_CK(c, cudaMalloc((void**)&nd, (size_t)ncap * s.J * 4));
             if (s.n_masks)
-                PCL_CK(c, cudaMemcpyAsync(nd, s.d_masks, (size_t)s.n_masks * s.J * 4, cudaMemcpyDeviceToDevice, c->compute));
-                PCL_CK(c, cudaStreamSynchronize(c->compute));
+            {
+                cudaError_t e = cudaMemcpyAsync(nd, s.d_masks, (size_t)s.n_masks * s.J * 4, cudaMemcpyDeviceToDevice, c->compute);
+                if (e == cudaSuccess)
+                    e = cudaStreamSynchronize(c->compute);
+                if (e != cudaSuccess)
+                {
+                    cudaFree(nd);
+                    (void)cudaGetLastError();
+                    return fail(c, PCL_ERR_CUDA, std::string("pcl_upload_mask: ") + cudaGetErrorString(e));
+                }
+            }
             cudaFree(s.d_masks);
             s.d_masks = nd, s.cap_masks = ncap;
         }
@@ -1415,18 +1456,19 @@ extern "C"
         int             wpb = c->opt_pose_wpb;
         if (wpb == 0) // enough blocks for every SM first, then larger blocks
             wpb = warps >= 8LL * 4 * c->sm_count ? 4 : (warps >= 8LL * 2 * c->sm_count ? 2 : 1);
-        while (wpb > 1 && per_warp * wpb > (size_t)c->max_smem_optin)
+        const size_t steps_smem = PCL_POSE_STEPS_SMEM ? (size_t)s.J * sizeof(StepRec) : 0; // (pose_simple_kernel's copy of the step records)
+        while (wpb > 1 && per_warp * wpb + steps_smem > (size_t)c->max_smem_optin)
             wpb >>= 1;
         // step-ordered kernel when every clip of this skeleton has that form and the step records fit the constant bank
         const bool simple = c->opt_pose_generic == 0 && s.J <= POSE_CMAX && s.n_clips > 0 && s.n_simple == s.n_clips &&
-                            c->device < PCL_STATIC_MAX_DEVICES;
+                            c->device < PCL_STATIC_MAX_DEVICES && per_warp + steps_smem <= (size_t)c->max_smem_optin;
         if (simple)
             wpb = std::min(wpb, POSE_S_THREADS / 32);
-        const size_t   smem = per_warp * wpb;
+        const size_t   smem = per_warp * wpb + (simple && PCL_POSE_STEPS_SMEM ? (size_t)s.J * sizeof(StepRec) : 0);
         const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
         // the bank's contents must stay put from the upload until this launch is enqueued
         std::unique_lock<std::mutex> bank_lock(g_const_mu, std::defer_lock);
-        if (simple)
+        if (simple && !PCL_POSE_STEPS_SMEM)
         {
             bank_lock.lock();
             ConstOwner& own = g_const_owner[c->device];
@@ -1470,7 +1512,7 @@ extern "C"
         }
         // small one-clip crowds: the level-parallel kernel (8 warps share 32 instances), while it leaves no SM oversubscribed
         {
-            const size_t smem_l = pose_l_smem_bytes(s.J);
+            const size_t smem_l = pose_l_smem_bytes(s.J, s.n_rounds);
             const bool   fits_l = simple && b->K == 1 && !sorted && s.d_sched && smem_l <= (size_t)c->max_smem_optin;
             const bool   small  = warps <= 2LL * c->sm_count; // measured: 20.7 us against 31-33 us up to 4 000 player instances, 29 against 32 at 8 000, level at 10 000
             if (fits_l && (c->opt_pose_level == 1 || (c->opt_pose_level < 0 && (small || io))))
@@ -1479,7 +1521,7 @@ extern "C"
                 if (io && io->out12)
                     p.out12 = io->out12, io->out12_written = true;
                 { int rc__ = ensure_smem(c, (const void*)pose_level_kernel, smem_l); if (rc__) return rc__; }
-                pose_level_kernel<<<(unsigned)warps, POSE_L_WARPS * 32, smem_l, c->compute>>>(p);
+                pose_level_kernel<<<(unsigned)warps, POSE_L_WARPS * 64, smem_l, c->compute>>>(p);
                 c->launches++;
                 PCL_POST_LAUNCH(c, c->compute, "pose_level_kernel");
                 PCL_CK(c, cudaEventRecord(c->ev_pose, c->compute));
@@ -2216,13 +2258,15 @@ extern "C"
         // One-time set-up per device, with that device current: in host code `g_static_export` is only a
         // stand-in for the symbol, not an address the GPU understands, so ask the runtime where this
         // device's copy of the array lives and hand THAT pointer to the kernel.
-        if (!g_static_export_addr[c->device])
+        // (Contexts may be driven from different threads: the slot is atomic; two first callers both look the address up and
+        // store the same value.)
+        void* addr = g_static_export_addr[c->device].load(std::memory_order_acquire);
+        if (!addr)
         {
-            void* p = nullptr;
-            PCL_CK(c, cudaGetSymbolAddress(&p, g_static_export));
-            g_static_export_addr[c->device] = p;
+            PCL_CK(c, cudaGetSymbolAddress(&addr, g_static_export));
+            g_static_export_addr[c->device].store(addr, std::memory_order_release);
         }
-        float4* staging = reinterpret_cast<float4*>(g_static_export_addr[c->device]);
+        float4* staging = reinterpret_cast<float4*>(addr);
         PCL_CK(c, cudaStreamWaitEvent(c->copy, c->ev_pose, 0));
         const long long total = count * s.J * 4; // every float4 of the range is overwritten: nothing to clear
         export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->copy>>>(b->d_palette, staging, first, count, s.J, s.pitch);

@@ -472,6 +472,12 @@ namespace pcl
     // (clip, frame) their phase falls in, so the 32 key gathers of a warp collapse onto one or two addresses (broadcast)
     // instead of up to 32 cache lines; every instance is still computed by exactly the same instruction sequence and
     // written to its own palette row, so the result does not depend on the order.
+    // where the step records are read from: 0 = the constant bank, 1 = a copy in shared memory (made by the block, coalesced,
+    // at its start - what pose_level_kernel does).  Measured (tools/pose_bench.py, K = 1 / K = 2): shared memory 29.0 / 41.2 us
+    // against 30.0 / 41.3 at 10 k instances, but 147 / 207 us against 134 / 191 at 100 k and level at 1 M: the constant bank stays.
+#ifndef PCL_POSE_STEPS_SMEM
+#define PCL_POSE_STEPS_SMEM 0
+#endif
     template<int K, bool SORTED, int MB>
     __global__ void __launch_bounds__(POSE_S_THREADS, MB) pose_simple_kernel(const PoseParams par)
     {
@@ -480,6 +486,19 @@ namespace pcl
         const int       wib   = threadIdx.x >> 5;
         const long long wglob = (long long)blockIdx.x * (blockDim.x >> 5) + wib;
         const long long inst0 = wglob * 32;
+#if PCL_POSE_STEPS_SMEM
+        const StepRec* s_steps = reinterpret_cast<const StepRec*>(smem + (size_t)(blockDim.x >> 5) * pose_smem_floats_per_warp(par.nslot));
+        {
+            const int4* src = reinterpret_cast<const int4*>(par.steps);
+            int4*       dst = reinterpret_cast<int4*>(const_cast<StepRec*>(s_steps));
+            for (int i = threadIdx.x; i < par.J * (int)(sizeof(StepRec) / 16); i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            __syncthreads();
+        }
+#define PCL_STEP(s_) s_steps[s_]
+#else
+#define PCL_STEP(s_) c_steps[s_]
+#endif
         if (inst0 >= par.N)
             return;
         const bool      active = (inst0 + lane) < par.N;
@@ -575,9 +594,9 @@ namespace pcl
                 const int s = s0 + g;
                 if (s >= par.J)
                     break;
-                const StepRec& rec  = c_steps[s];
+                const StepRec& rec  = PCL_STEP(s);
                 const int      bone = rec.joint;
-                contiguous          = contiguous && (bone == c_steps[s0].joint + g);
+                contiguous          = contiguous && (bone == PCL_STEP(s0).joint + g);
                 KeyPair ck[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
@@ -659,7 +678,7 @@ namespace pcl
             if (contiguous && ni == 32 && s0 + POSE_G <= par.J)
             {
                 // 32 rows x 12 units, conflict-free (see lbs_i_flush12); the group's 4 slots are 12 consecutive units
-                const size_t off = (size_t)(c_steps[s0].joint + 1) * 3;
+                const size_t off = (size_t)(PCL_STEP(s0).joint + 1) * 3;
 #pragma unroll
                 for (int gq = 0; gq < 4; gq++)
                 {
@@ -700,7 +719,7 @@ namespace pcl
                     const int s  = s0 + g;
                     const size_t irow = SORTED ? (size_t)__shfl_sync(0xffffffffu, inst32, il & 31) : (size_t)(inst0 + il);
                     if (s < par.J && il < ni)
-                        par.palette[(irow * par.pitch + c_steps[s].joint + 1) * 3 + (rm - g * 3)] =
+                        par.palette[(irow * par.pitch + PCL_STEP(s).joint + 1) * 3 + (rm - g * 3)] =
                             *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
                 }
             }
@@ -720,17 +739,77 @@ namespace pcl
     // operation order per bone as the other pose kernels - the results are bit-identical; only worth it while the crowd leaves
     // SMs idle (the launcher uses it up to ~3 CTAs per SM), because at narrow levels most warps wait.
     // -------------------------------------------------------------------------------------------
-    constexpr int POSE_L_WARPS = 8;
-    __host__ __device__ inline size_t pose_l_smem_bytes(int J) { return (size_t)J * POSE_SLOT_FLOATS * sizeof(float); }
+    // POSE_L_WARPS "derive" warps take one bone of the current level each per round (sample, local pose, composition with
+    // the parent, result parked in shared memory for the children); as many "palette" warps trail ONE ROUND behind and turn
+    // the parked transforms into palette rows (Transform::getMatrix x inverse bind, the stores to global memory, the derived
+    // read-back) - a third of a bone's instructions, none of which a child waits for, off the chain of rounds.
+    // 12 + 12 warps: the player's widest levels (10 bones) take one round each, 13 rounds in all instead of 16.
+    constexpr int POSE_L_WARPS = 12;
+    // shared memory: parked transforms [J] | the skeleton's step records [J] | the schedule [n_rounds][POSE_L_WARPS]
+    __host__ __device__ inline size_t pose_l_smem_bytes(int J, int n_rounds)
+    {
+        return (size_t)J * POSE_SLOT_FLOATS * sizeof(float) + (size_t)J * sizeof(StepRec) + (((size_t)n_rounds * POSE_L_WARPS * 4 + 15) & ~(size_t)15);
+    }
 
-    __global__ void __launch_bounds__(POSE_L_WARPS * 32) pose_level_kernel(const PoseParams par)
+    __global__ void __launch_bounds__(POSE_L_WARPS * 64) pose_level_kernel(const PoseParams par)
     {
         extern __shared__ __align__(16) float smem[];
         const int       lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         const long long inst0 = (long long)blockIdx.x * 32;
         const bool      active = (inst0 + lane) < par.N;
         const long long inst   = min(inst0 + lane, par.N - 1); // idle lanes shadow the last instance, never store
+        float4*         pal    = par.palette + (size_t)inst * par.pitch * 3;
+        // The step records and the schedule are copied into shared memory first (coalesced, once): a round's look-ups are then
+        // shared-memory broadcasts.  Read through the constant bank, a CTA that is alone on its SM - one character, the
+        // reference's everyday case - paid a constant-cache miss per round, most of a round's time.
+        StepRec* s_steps = reinterpret_cast<StepRec*>(smem + (size_t)par.J * POSE_SLOT_FLOATS);
+        int32_t* s_sched = reinterpret_cast<int32_t*>(s_steps + par.J);
+        {
+            const int4* src = reinterpret_cast<const int4*>(par.steps);
+            int4*       dst = reinterpret_cast<int4*>(s_steps);
+            for (int i = threadIdx.x; i < par.J * (int)(sizeof(StepRec) / 16); i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            for (int i = threadIdx.x; i < par.n_rounds * POSE_L_WARPS; i += blockDim.x)
+                s_sched[i] = __ldg(par.sched + i);
+        }
 
+        if (warp >= POSE_L_WARPS)
+        {
+            // ---------------- palette warps ----------------
+            const int32_t* my = s_sched + (warp - POSE_L_WARPS);
+            if (warp == POSE_L_WARPS && active)
+            {
+                pal[0] = make_float4(1, 0, 0, 0), pal[1] = make_float4(0, 1, 0, 0), pal[2] = make_float4(0, 0, 1, 0); // slot 0 = identity
+            }
+            __syncthreads(); // (the phase hand-over of the derive warps)
+            int s_prev = -1;
+            for (int r = 0; r <= par.n_rounds; r++)
+            {
+                const int s = s_prev;
+                s_prev      = r < par.n_rounds ? my[r * POSE_L_WARPS] : -1;
+                if (s >= 0 && active)
+                {
+                    const StepRec& rec  = s_steps[s];
+                    const int      bone = rec.joint;
+                    const TRSP     der  = load_trs(smem + (size_t)s * POSE_SLOT_FLOATS, lane);
+                    if (par.derived)
+                        store_derived(par.derived + ((size_t)inst * par.J + bone) * 10, der);
+                    float4 r0, r1, r2; // outputAnimationResult, skeleton.cpp:119-156
+                    palette_rowsp(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                    if (par.out12)
+                    {
+                        float4* o = par.out12 + ((size_t)inst * par.J + bone) * 3;
+                        o[0] = r0, o[1] = r1, o[2] = r2;
+                    }
+                    float4* row = pal + (size_t)(bone + 1) * 3;
+                    row[0] = r0, row[1] = r1, row[2] = r2;
+                }
+                __syncthreads();
+            }
+            return;
+        }
+
+        // ---------------- derive warps ----------------
         const ClipRec cr = par.clips[__ldg(par.clip_ids + inst)];
         float         ph = par.phase[inst];
         if (par.advance != 0)
@@ -741,53 +820,32 @@ namespace pcl
         SimpleSlot st;
         slot_frames(st, ph, cr.total_frame_m1, cr.F);
         st.keys = cr.keys_step, st.anim = cr.anim_step, st.w = 1.0f, st.mask_off = -1;
-        float4* pal = par.palette + (size_t)inst * par.pitch * 3;
-        if (warp == 0 && active)
-        {
-            pal[0] = make_float4(1, 0, 0, 0), pal[1] = make_float4(0, 1, 0, 0), pal[2] = make_float4(0, 0, 1, 0); // slot 0 = identity
-        }
         __syncthreads(); // every warp has read the old phase before warp 0 replaces it
         if (warp == 0 && active && par.advance != 0)
             par.phase[inst] = ph;
 
         // software pipeline over the warp's own rounds: keys one round ahead
-        const int32_t* my = par.sched + warp;
-        int            s_cur = __ldg(my), s_nxt = par.n_rounds > 1 ? __ldg(my + POSE_L_WARPS) : -1;
+        const int32_t* my = s_sched + warp;
+        int            s_cur = my[0], s_nxt = par.n_rounds > 1 ? my[POSE_L_WARPS] : -1;
         KeyPair        k_cur = fetch_keys(st, max(s_cur, 0));
-        for (int r = 0; r < par.n_rounds; r++)
+        for (int r = 0; r <= par.n_rounds; r++)
         {
             const int     s = s_cur;
             const KeyPair k = k_cur;
-            const int s_nn = r + 2 < par.n_rounds ? __ldg(my + (r + 2) * POSE_L_WARPS) : -1;
+            const int s_nn = r + 2 < par.n_rounds ? my[(r + 2) * POSE_L_WARPS] : -1;
             if (s_nxt >= 0)
                 k_cur = fetch_keys(st, s_nxt);
             s_cur = s_nxt, s_nxt = s_nn;
             if (s >= 0)
             {
-                const StepRec& rec = c_steps[s];
+                const StepRec& rec = s_steps[s];
                 const SampleP  sm  = sample_keys(k, st.r);
                 // Node::resetToInitialPose + rotate(LOCAL) / scale / translate(AREN), as in pose_simple_kernel
                 const TRSP loc = local_pose(rec, sm.pxy, sm.sxy, sm.pzsz, sm.q);
                 TRSP par_trs = identity_trs();
                 if (rec.pstep >= 0)
                     par_trs = load_trs(smem + (size_t)rec.pstep * POSE_SLOT_FLOATS, lane);
-                const TRSP der = composep(par_trs, loc, rec.pstep < 0);
-                store_trs(smem + (size_t)s * POSE_SLOT_FLOATS, lane, der);
-                if (active)
-                {
-                    const int bone = rec.joint;
-                    if (par.derived)
-                        store_derived(par.derived + ((size_t)inst * par.J + bone) * 10, der);
-                    float4 r0, r1, r2;
-                    palette_rowsp(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
-                    if (par.out12)
-                    {
-                        float4* o = par.out12 + ((size_t)inst * par.J + bone) * 3;
-                        o[0] = r0, o[1] = r1, o[2] = r2;
-                    }
-                    float4* row = pal + (size_t)(bone + 1) * 3;
-                    row[0] = r0, row[1] = r1, row[2] = r2;
-                }
+                store_trs(smem + (size_t)s * POSE_SLOT_FLOATS, lane, composep(par_trs, loc, rec.pstep < 0));
             }
             __syncthreads();
         }

@@ -922,6 +922,18 @@ def test_upload_errors(ctx, player):
     cl.rot_keys[7] = cl.rot_keys[7][:0]
     with pytest.raises(capi.PclError):
         ctx.upload_clip(skel, cl, am)
+    sk, cl, am, mk = A.load_player()
+    cl.total_frame = 0  # would shrink the frame buckets of the coherent order and index out of them
+    with pytest.raises(capi.PclError) as e:
+        ctx.upload_clip(skel, cl, am)
+    assert e.value.code == -1 and "total_frame" in str(e.value)
+    import ctypes as C
+    counts = np.ones((1, 3), np.int32)  # one channel with one key per track, but no key arrays
+    conv = np.zeros(1, np.int32)
+    out = C.c_int32()
+    rc = ctx.L.pcl_upload_clip(ctx.h, skel, 2, 1, 1, counts.ctypes.data_as(C.POINTER(C.c_int32)), None, None, None, 1,
+                               conv.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(out))
+    assert rc == -1
     mesh = A.make_player_mesh(sk, V=100)
     mesh.bind_idx[0, 0] = 59
     with pytest.raises(capi.PclError):

@@ -49,6 +49,32 @@ def test_static_download_matches_regular_download_twice_in_a_row(player):
         with pytest.raises(capi.PclError) as e:
             b.download_palette_static(0, limit + 1)
         assert e.value.code == -3 and "PCL_STATIC_EXPORT_MAX_BYTES" in str(e.value)
+
+        # the point of the entry point: once its one-time address look-up is behind it, no call - served or refused - takes
+        # or returns a single byte of device memory (a version that quietly fell back to a cudaMalloc'ed buffer would)
+        import torch
+        torch.cuda.init()
+        ctx.sync()
+        free0 = torch.cuda.mem_get_info(0)[0]
+        for k in range(6):
+            part = b.download_palette_static(100 * k, limit - 200 * k)
+            assert np.array_equal(part, b.download_palette_static(100 * k, limit - 200 * k))
+            with pytest.raises(capi.PclError):
+                b.download_palette_static(0, limit + 1 + k)
+            assert torch.cuda.mem_get_info(0)[0] == free0, "device memory changed hands in call %d" % k
+
+        # a second context on the same GPU shares the one array (and its address): same matrices through it
+        ctx2 = capi.Context(0)
+        try:
+            skel2 = ctx2.upload_skeleton(sk)
+            clip2 = ctx2.upload_clip(skel2, cl, am)
+            b2 = ctx2.batch(skel2, 500, 1)
+            b2.set(clip_ids=np.full((500, 1), clip2, np.int32), phase=ph[:500])
+            b2.pose()
+            assert np.array_equal(b2.download_palette_static(0, 500), b2.download_palette(0, 500))
+            b2.close()
+        finally:
+            ctx2.close()
         b.close()
     finally:
         ctx.close()
