@@ -1464,7 +1464,7 @@ extern "C"
                             c->device < PCL_STATIC_MAX_DEVICES && per_warp + steps_smem <= (size_t)c->max_smem_optin;
         if (simple)
             wpb = std::min(wpb, POSE_S_THREADS / 32);
-        const size_t   smem = per_warp * wpb + (simple && PCL_POSE_STEPS_SMEM ? (size_t)s.J * sizeof(StepRec) : 0);
+        size_t         smem = per_warp * wpb + (simple && PCL_POSE_STEPS_SMEM ? (size_t)s.J * sizeof(StepRec) : 0);
         const unsigned grid = (unsigned)((warps + wpb - 1) / wpb);
         // the bank's contents must stay put from the upload until this launch is enqueued
         std::unique_lock<std::mutex> bank_lock(g_const_mu, std::defer_lock);
@@ -1509,6 +1509,8 @@ extern "C"
             c->launches += 3;
             PCL_POST_LAUNCH(c, c->compute, "order_*_kernel");
             p.order = b->d_order;
+            if (b->K == 1)
+                smem += (size_t)wpb * pose_wkeys_floats(s.J) * 4; // the warps' bucket keys (pose_simple_kernel<1, true, *>)
         }
         // small one-clip crowds: the level-parallel kernel (8 warps share 32 instances), while it leaves no SM oversubscribed
         {

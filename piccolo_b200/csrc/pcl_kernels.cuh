@@ -85,6 +85,11 @@ namespace pcl
     // nslot parked parents + one slot holding the identity transform (the "parent" of a root in pose_simple_kernel)
     __host__ __device__ inline size_t pose_smem_floats_per_warp(int nslot) { return (size_t)(nslot + 1) * POSE_SLOT_FLOATS + 32 * (POSE_G * 12 + 4); }
 
+    // frame-coherent one-clip launches: a warp whose 32 instances fall into ONE (clip, frame) bucket - 98 % of the warps of a large
+    // sorted crowd - copies that bucket's two keys of every bone into shared memory once (J x 96 bytes) and reads them back as
+    // broadcasts: no global load is left in its bone loop
+    __host__ __device__ inline size_t pose_wkeys_floats(int J) { return (size_t)J * 24; }
+
     struct SlotState // one clip slot of one instance, resident in registers
     {
         const float4*  keys;
@@ -506,9 +511,11 @@ namespace pcl
         const long long inst   = SORTED ? (long long)__ldg(par.order + visit) : visit;
         const int       inst32 = (int)inst;
         const int       ni     = (int)min(32LL, par.N - inst0);
-        float*          slots  = smem + (size_t)wib * pose_smem_floats_per_warp(par.nslot);
+        constexpr bool  WKEYS  = K == 1 && SORTED; // see pose_wkeys_floats
+        float*          slots  = smem + (size_t)wib * (pose_smem_floats_per_warp(par.nslot) + (WKEYS ? pose_wkeys_floats(par.J) : 0));
         float*          stage  = slots + (size_t)(par.nslot + 1) * POSE_SLOT_FLOATS;
         constexpr int   SROW   = POSE_G * 12 + 4;
+        float4*         wkeys  = reinterpret_cast<float4*>(stage + 32 * SROW); // [J][6] float4: lower key, upper key of every step
         store_trs(slots + (size_t)par.nslot * POSE_SLOT_FLOATS, lane, identity_trs()); // slot nslot: what a root composes with
 
         SimpleSlot st[K];
@@ -552,14 +559,39 @@ namespace pcl
 #pragma unroll
             for (int gq = 0; gq < 4; gq++)
             {
-                frow[gq * 3 + 0] = (uint32_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8);
-                frow[gq * 3 + 1] = (uint32_t)__shfl_sync(0xffffffffu, inst32, fa + gq * 8 + 4);
-                frow[gq * 3 + 2] = (uint32_t)__shfl_sync(0xffffffffu, inst32, fa + fc4 + gq * 8);
+#ifdef PCL_POSE_WRAP_ROWS /* experiment: all palette rows land in a small, L2-resident window - is the kernel bound by where it writes? */
+#define PCL_WRAP(x) ((x) & (PCL_POSE_WRAP_ROWS - 1))
+#else
+#define PCL_WRAP(x) (x)
+#endif
+                frow[gq * 3 + 0] = (uint32_t)PCL_WRAP(__shfl_sync(0xffffffffu, inst32, fa + gq * 8));
+                frow[gq * 3 + 1] = (uint32_t)PCL_WRAP(__shfl_sync(0xffffffffu, inst32, fa + gq * 8 + 4));
+                frow[gq * 3 + 2] = (uint32_t)PCL_WRAP(__shfl_sync(0xffffffffu, inst32, fa + fc4 + gq * 8));
             }
         }
 
         TRSP prev = identity_trs(); // derived transform of the previous step = the parent of a chain's next bone
 
+        // one bucket for the whole warp?  Then its keys come from shared memory (copied here, coalesced, in one burst)
+        bool uni = false;
+        if (WKEYS)
+        {
+            // (all three exchanges before any comparison: a short-circuited && would keep lanes out of a full-mask shuffle)
+            const unsigned long long kp  = reinterpret_cast<unsigned long long>(st[0].keys);
+            const unsigned long long kp0 = __shfl_sync(0xffffffffu, kp, 0);
+            const uint32_t           lo0 = __shfl_sync(0xffffffffu, st[0].lo3, 0), hi0 = __shfl_sync(0xffffffffu, st[0].hi3, 0);
+            const bool               same = (kp == kp0) & (st[0].lo3 == lo0) & (st[0].hi3 == hi0);
+            uni = __all_sync(0xffffffffu, same) != 0;
+            if (uni)
+            {
+                for (int i = lane; i < par.J * 6; i += 32)
+                {
+                    const int sI = i / 6, u = i - sI * 6;
+                    wkeys[i]     = __ldg(st[0].keys + ((uint32_t)sI * st[0].F3 + (u < 3 ? st[0].lo3 + u : st[0].hi3 + (u - 3))));
+                }
+                __syncwarp();
+            }
+        }
         // software pipeline: keys one bone ahead (register budget allows it for K <= 2)
         constexpr bool PREFETCH = K <= 2;
         // One clip per instance and the 255-register form: keys TWO bones ahead (two rotating buffers; POSE_G is even, so a
@@ -571,7 +603,7 @@ namespace pcl
         for (int k = 0; k < K; k++)
         {
             amask[k] = 0xffffffffu;
-            if (PREFETCH)
+            if (PREFETCH && !uni)
             {
                 nk[k] = fetch_keys(st[k], 0);
                 if (PD == 2)
@@ -601,13 +633,20 @@ namespace pcl
 #pragma unroll
                 for (int k = 0; k < K; k++)
                     ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s);
+                if (WKEYS && uni)
+                {
+                    const float4* wk = wkeys + s * 6; // the same address for all lanes: broadcast reads
+                    const float4  t0 = wk[2], t1 = wk[5];
+                    ck[0].a0 = wk[0], ck[0].q0 = wk[1], ck[0].c0 = make_float2(t0.x, t0.y);
+                    ck[0].a1 = wk[3], ck[0].q1 = wk[4], ck[0].c1 = make_float2(t1.x, t1.y);
+                }
                 // this bone's samples first (they consume the keys requested one bone ago) ...
                 SampleP sm[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
                     sm[k] = sample_keys(ck[k], st[k].r);
                 // ... then the next bone's keys are requested; they land while the rest of this bone is computed
-                if (PREFETCH && s + PD < par.J)
+                if (PREFETCH && !uni && s + PD < par.J)
                 {
 #pragma unroll
                     for (int k = 0; k < K; k++)
