@@ -134,7 +134,8 @@ def other_configs(ctx, capi, grp, sk, cl, am, mk, skel, clip0, peak, with_cpu):
       configs[3]  1 M-instance crowd, 8 mixed clips, random phases, pose only, SHARDED over all ranks (strong scaling:
                   every rank poses shard_range(1 000 000, world, rank); time = max over ranks, barrier-bracketed)
       configs[4]  256 joints x 49 998 vertices LBS stress: the sweep N in {1, 8, 64, 512, 4096} x {POS, POS+NRM+TAN}
-                  on the random-binding mesh (worst case) and on a coherent mesh                 (rank 0)
+                  on three meshes: random bindings (worst case), every vertex bound to its four NEAREST bones (coherent in
+                  space), every vertex bound along its limb (bone, parent, grandparent, child: a painted character)   (rank 0)
     Parity for the same arrays at the same sizes: tests/test_gpu_full_size.py."""
     from piccolo_b200 import workloads as W
     from piccolo_b200.sharding import shard_range
@@ -196,7 +197,7 @@ def other_configs(ctx, capi, grp, sk, cl, am, mk, skel, clip0, peak, with_cpu):
     # config 5 sweep
     if rank == 0:
         sweep = {}
-        for label, coherent in (("random_bindings", False), ("coherent_mesh", True)):
+        for label, coherent in (("random_bindings", False), ("coherent_mesh", True), ("limb_bound_mesh", "chain")):
             sk5, cl5, am5, mesh5 = W.config5_assets(coherent)
             s5 = ctx.upload_skeleton(sk5)
             c5 = ctx.upload_clip(s5, cl5, am5)

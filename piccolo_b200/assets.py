@@ -375,7 +375,7 @@ def make_variant_clip(base: AnimationClip, frames: int, seed: int, max_deg: floa
     return AnimationClip(frames, base.node_count, list(base.names), pk, rk, sk, list(base.node_map), base.skeleton_file_path)
 
 
-def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42, full4: bool = False) -> MeshData:
+def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42, full4: bool = False, chain: bool = False) -> MeshData:
     """Synthetic stand-in for the missing robot.mesh_bind.json: a tessellated tube
     (capsule side) around every bone, emitted as FULLY EXPANDED triangles in strip order - three vertices per
     triangle, index_buffer[i] == i, which is the only case in which the reference's per-index binding upload is
@@ -434,6 +434,27 @@ def make_player_mesh(skel: SkeletonData, V: int = 16380, seed: int = 42, full4: 
         nearest[v0:v0 + 8192] = np.argsort(d, axis=1, kind="stable")[:, :4]
         dn[v0:v0 + 8192] = np.take_along_axis(d, nearest[v0:v0 + 8192], 1)
     on = (dn <= 1.6 * dn[:, :1] + 1e-9) | full4
+    if chain:
+        # bind every vertex to the bones AROUND the tube it lies on - that bone, its parent, its grandparent and its first
+        # child - which is how skinning weights are painted on a real character (influences follow the limb, not a sphere
+        # in space); inverse-distance weights, all four non-zero
+        first_child = np.full(J, -1)
+        for b in range(J - 1, 0, -1):
+            if par[b] != b:
+                first_child[par[b]] = b
+        owner = np.repeat(np.arange(J), per * 3)[:V]
+        owner = np.concatenate([owner, np.full(V - len(owner), owner[-1] if len(owner) else 0)])
+        cand = np.stack([owner, par[owner], par[par[owner]], np.where(first_child[owner] >= 0, first_child[owner], par[par[par[owner]]])], 1)
+        for v_, row in enumerate(cand):  # four DISTINCT bones: near the root the chain folds onto itself
+            seen = []
+            for b in row:
+                while int(b) in seen:
+                    b = (int(b) + 1) % J
+                seen.append(int(b))
+            cand[v_] = seen
+        nearest = cand
+        dn = np.linalg.norm(pos[:, None, :] - P[nearest], axis=2)
+        on = np.ones_like(dn, bool)
     idx = np.where(on, nearest + 1, 0).astype(np.int32)
     w = np.where(on, 1.0 / (dn + 1e-3), 0.0).astype(F32)
     uv = rng.uniform(0, 1, size=(V, 2))
@@ -444,6 +465,12 @@ def make_coherent_mesh(skel: SkeletonData, V: int = 49998, seed: int = 11) -> Me
     """A character-like mesh for any skeleton: make_player_mesh's tubes around the bones, every vertex bound to its FOUR
     nearest bones with non-zero inverse-distance weights (config 5 asks for 4 non-zero weights per vertex)."""
     return make_player_mesh(skel, V=V, seed=seed, full4=True)
+
+
+def make_chain_bound_mesh(skel: SkeletonData, V: int = 49998, seed: int = 11) -> MeshData:
+    """make_player_mesh's tubes with every vertex bound to the bones around its tube (bone, parent, grandparent, first child):
+    four non-zero weights that change only where the mesh moves on to another bone, like a painted character."""
+    return make_player_mesh(skel, V=V, seed=seed, chain=True)
 
 
 def make_synthetic_skeleton(J: int = 256, branching: int = 3, seed: int = 5) -> SkeletonData:

@@ -1868,9 +1868,26 @@ extern "C"
                     }
                     q.vsplit = std::max(1, std::min(vs, q.n_sc));
                     q.per_sc = (q.n_sc + q.vsplit - 1) / q.vsplit;
-                    if (compact) // runs start on block boundaries
+                    if (compact) // runs start on block boundaries: choose the run length in whole blocks
                     {
-                        q.per_sc = (q.per_sc + q.blk_sc - 1) / q.blk_sc * q.blk_sc;
+                        const int n_blk = (q.n_sc + q.blk_sc - 1) / q.blk_sc;
+                        if (c->opt_lbs_vsplit == 0)
+                        {
+                            double best = -1.0;
+                            int    best_k = n_blk;
+                            for (int k = n_blk; k >= 1; k--) // longer runs first: ties go to fewer palette re-stagings per CTA
+                            {
+                                const int    splits = (n_blk + k - 1) / k;
+                                const double waves  = (double)(full * splits) / c->sm_count;
+                                // the last split of every tile may be shorter: count the work, not the CTAs
+                                const double eff = ((double)full * n_blk) / (std::ceil(waves) * c->sm_count * (double)k);
+                                if (eff > best + 0.02)
+                                    best = eff, best_k = k;
+                            }
+                            q.per_sc = best_k * q.blk_sc;
+                        }
+                        else
+                            q.per_sc = (q.per_sc + q.blk_sc - 1) / q.blk_sc * q.blk_sc;
                         q.vsplit = (q.n_sc + q.per_sc - 1) / q.per_sc;
                     }
                     const unsigned grid = (unsigned)(full * q.vsplit);

@@ -49,13 +49,16 @@ def config4_inputs(first: int, count: int, total: int = 1000000):
     return pick[first:first + count].reshape(count, 1), phase[first:first + count].reshape(count, 1)
 
 
-def config5_assets(coherent: bool = False):
+def config5_assets(coherent=False):
     """configs[4]: 256-joint balanced tree, 256-channel x 32-frame clip, 49 998-vertex mesh with 4 non-zero weights per
     vertex.  coherent = False: every vertex bound to random bones (no reuse between neighbouring vertices: the worst case);
     coherent = True: tubes around the bones, each vertex bound to its 4 nearest bones (what an exported character looks like)."""
     sk = A.make_synthetic_skeleton(256)
     cl, am = A.make_synthetic_clip(sk, 32)
-    mesh = A.make_coherent_mesh(sk, V=49998, seed=11) if coherent else A.make_synthetic_mesh(sk, V=49998)
+    if coherent == "chain" or coherent == 2:  # bound along the limb: bone, parent, grandparent, first child
+        mesh = A.make_chain_bound_mesh(sk, V=49998, seed=11)
+    else:
+        mesh = A.make_coherent_mesh(sk, V=49998, seed=11) if coherent else A.make_synthetic_mesh(sk, V=49998)
     return sk, cl, am, mesh
 
 

@@ -131,10 +131,11 @@ def test_config3_full_size_256_instances_over_all_ring_chunks(ctx, oracle, playe
         sb.close(), b.close()
 
 
-@pytest.mark.parametrize("coherent", [False, True])
+@pytest.mark.parametrize("coherent", [False, True, "chain"])
 def test_config5_at_its_bench_point_n512(ctx, oracle, coherent):
     """configs[4] at the bench's N = 512 (256 joints, 49 998 vertices, POS+NRM+TAN), options on auto: 32 of the 512
-    instances - first and last included - against the oracle, on the random-binding mesh and on the coherent one."""
+    instances - first and last included - against the oracle, on the random-binding mesh, on the nearest-four mesh and on
+    the limb-bound one."""
     from piccolo_b200 import capi
     sk, cl, am, mesh = W.config5_assets(coherent)
     skel = ctx.upload_skeleton(sk)

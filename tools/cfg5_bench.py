@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """configs[4] (256 joints, 49 998 vertices) LBS at one point of the sweep - short enough to sit under ncu.
-  python tools/cfg5_bench.py [--coherent 0|1] [--n 512] [--pos-only] [--compact -1|0|1] [--tile 0|8|16|32] [--reps 10]"""
+  python tools/cfg5_bench.py [--coherent 0|1|2]  (0 random bindings, 1 four nearest bones, 2 bound along the limb) [--n 512] [--pos-only] [--compact -1|0|1] [--tile 0|8|16|32] [--reps 10]"""
 import argparse, json, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -21,7 +21,7 @@ try:
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     pass
-sk, cl, am, mesh = W.config5_assets(bool(a.coherent))
+sk, cl, am, mesh = W.config5_assets({0: False, 1: True, 2: "chain"}[a.coherent])
 ctx = capi.Context(0)
 ctx.set_option("lbs_compact", a.compact), ctx.set_option("lbs_cta_tile", a.tile), ctx.set_option("lbs_vsplit", a.vsplit)
 s5 = ctx.upload_skeleton(sk)
