@@ -1531,16 +1531,20 @@ extern "C"
                 return PCL_OK;
             }
         }
-        // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM, except two-clip crowds beyond ~300 k instances
+        // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM.  (Round 1 preferred 3 blocks for two-clip crowds
+        // beyond ~300 k instances; with the packed, straight-line groups the 168-register form spills: 1.98 against 1.86 ms at 1 M.)
         int mb = c->opt_pose_min_blocks;
-        if (mb == 0)
-            mb = (b->K == 2 && b->N >= 300000) ? 3 : 2;
-        if (b->K > 2)
+        if (mb == 0 || b->K > 2)
             mb = 2;
+#define PCL_LAUNCH_POSE_SD(KK, SS, MM, DD)                                                                                  \
+    {                                                                                                                       \
+        { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, SS, MM, DD>, smem); if (rc__) return rc__; }        \
+        pose_simple_kernel<KK, SS, MM, DD><<<grid, wpb * 32, smem, c->compute>>>(p);                                        \
+    }
 #define PCL_LAUNCH_POSE_S(KK, SS, MM)                                                                                       \
     {                                                                                                                       \
-        { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, SS, MM>, smem); if (rc__) return rc__; }            \
-        pose_simple_kernel<KK, SS, MM><<<grid, wpb * 32, smem, c->compute>>>(p);                                            \
+        if (p.derived) PCL_LAUNCH_POSE_SD(KK, SS, 2, true) /* (the read-back form exists for 2 blocks per SM only) */       \
+        else PCL_LAUNCH_POSE_SD(KK, SS, MM, false)                                                                          \
     }
 #define PCL_LAUNCH_POSE_MB(KK, SS)                                                                                          \
     {                                                                                                                       \
@@ -1566,6 +1570,7 @@ extern "C"
             default: PCL_LAUNCH_POSE(4) break;
         }
 #undef PCL_LAUNCH_POSE_S
+#undef PCL_LAUNCH_POSE_SD
 #undef PCL_LAUNCH_POSE_MB
 #undef PCL_LAUNCH_POSE
         c->launches++;

@@ -10,6 +10,7 @@
 #include <cuda.h> // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
 
 #include <cstdint>
+#include <type_traits>
 
 namespace pcl
 {
@@ -442,6 +443,27 @@ namespace pcl
         f2* s2 = reinterpret_cast<f2*>(slot) + lane;
         s2[0] = t.pxy, s2[32] = t.sxy, s2[64] = t.pzsz, s2[96] = t.q.wx, s2[128] = t.q.yz;
     }
+    // the same, predicated instead of branched (the transform keeps its value when `p` is false): a uniform branch around five
+    // loads ends a basic block, and with it what ptxas can overlap
+    __device__ __forceinline__ void load_trs_if(bool p, const float* slot, int lane, TRSP& t)
+    {
+        const uint32_t a = (uint32_t)__cvta_generic_to_shared(slot) + (uint32_t)lane * 8u;
+        asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %6, 0;\n"
+                     "@q ld.shared.b64 %0, [%5];\n@q ld.shared.b64 %1, [%5+256];\n@q ld.shared.b64 %2, [%5+512];\n"
+                     "@q ld.shared.b64 %3, [%5+768];\n@q ld.shared.b64 %4, [%5+1024];\n}"
+                     : "+l"(t.pxy), "+l"(t.sxy), "+l"(t.pzsz), "+l"(t.q.wx), "+l"(t.q.yz)
+                     : "r"(a), "r"((int)p)
+                     : "memory");
+    }
+    __device__ __forceinline__ void store_trs_if(bool p, float* slot, int lane, const TRSP& t)
+    {
+        const uint32_t a = (uint32_t)__cvta_generic_to_shared(slot) + (uint32_t)lane * 8u;
+        asm volatile("{\n.reg .pred q;\nsetp.ne.b32 q, %6, 0;\n"
+                     "@q st.shared.b64 [%5], %0;\n@q st.shared.b64 [%5+256], %1;\n@q st.shared.b64 [%5+512], %2;\n"
+                     "@q st.shared.b64 [%5+768], %3;\n@q st.shared.b64 [%5+1024], %4;\n}" ::"l"(t.pxy),
+                     "l"(t.sxy), "l"(t.pzsz), "l"(t.q.wx), "l"(t.q.yz), "r"(a), "r"((int)p)
+                     : "memory");
+    }
     __device__ __forceinline__ TRSP identity_trs()
     {
         TRSP t;
@@ -483,7 +505,11 @@ namespace pcl
 #ifndef PCL_POSE_STEPS_SMEM
 #define PCL_POSE_STEPS_SMEM 0
 #endif
-    template<int K, bool SORTED, int MB>
+    // DER: the derived transforms are written out too (LevelDebugger-style read-back); a template parameter so that the common
+    // form carries no branch for it.  A group of POSE_G bones is ONE straight-line block there (no bounds checks in whole groups,
+    // parent fetch and parking predicated instead of branched): ptxas may then run bone s + 1's sampling and local pose - which do
+    // not depend on the hierarchy - inside bone s's composition chain.
+    template<int K, bool SORTED, int MB, bool DER>
     __global__ void __launch_bounds__(POSE_S_THREADS, MB) pose_simple_kernel(const PoseParams par)
     {
         extern __shared__ __align__(16) float smem[];
@@ -611,8 +637,9 @@ namespace pcl
             }
         }
 
-        for (int s0 = 0; s0 < par.n_steps_padded; s0 += POSE_G)
-        {
+        auto group = [&](const int s0, auto full_tag, auto uni_tag) {
+            constexpr bool FULL = decltype(full_tag)::value; // all POSE_G bones of the group exist
+            constexpr bool UNI  = decltype(uni_tag)::value;  // the warp's keys come from its shared-memory copy
             if (K > 1 && (s0 & 31) == 0)
             {
 #pragma unroll
@@ -624,7 +651,7 @@ namespace pcl
             for (int g = 0; g < POSE_G; g++)
             {
                 const int s = s0 + g;
-                if (s >= par.J)
+                if (!FULL && s >= par.J)
                     break;
                 const StepRec& rec  = PCL_STEP(s);
                 const int      bone = rec.joint;
@@ -633,7 +660,7 @@ namespace pcl
 #pragma unroll
                 for (int k = 0; k < K; k++)
                     ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s);
-                if (WKEYS && uni)
+                if (WKEYS && UNI)
                 {
                     const float4* wk = wkeys + s * 6; // the same address for all lanes: broadcast reads
                     const float4  t0 = wk[2], t1 = wk[5];
@@ -646,7 +673,7 @@ namespace pcl
                 for (int k = 0; k < K; k++)
                     sm[k] = sample_keys(ck[k], st[k].r);
                 // ... then the next bone's keys are requested; they land while the rest of this bone is computed
-                if (PREFETCH && !uni && s + PD < par.J)
+                if (PREFETCH && !UNI && (FULL || s + PD < par.J)) // (whole groups: the key tracks are padded by a group, §2)
                 {
 #pragma unroll
                     for (int k = 0; k < K; k++)
@@ -691,22 +718,22 @@ namespace pcl
                         qref.wx = first ? sm[k].q.wx : qref.wx, qref.yz = first ? sm[k].q.yz : qref.yz;
                         any |= ok;
                     }
-                    if (any && touched)
-                        loc = local_pose(rec, accA, accB, accC, accq);
-                    else
-                        loc = bind_pose(rec);
+                    // bones no clip animates or none contributes to keep the bind pose: the identity delta reproduces it exactly
+                    // (q_bind * (1,0,0,0), s_bind * 1, p_bind + 0), selected here instead of branched to
+                    const bool keep = !(any && touched);
+                    accA = keep ? pk(0.f, 0.f) : accA, accB = keep ? pk(1.f, 1.f) : accB, accC = keep ? pk(0.f, 1.f) : accC;
+                    accq.wx = keep ? pk(1.f, 0.f) : accq.wx, accq.yz = keep ? pk(0.f, 0.f) : accq.yz;
+                    loc = local_pose(rec, accA, accB, accC, accq);
                 }
                 // m_bones[i].update(), skeleton.cpp:110-113 -> Node::updateDerivedTransform node.cpp:32-65
                 // (one code path on purpose: a parent fetched from its slot - for a root, the identity in slot nslot - REPLACES
                 // `prev` in place, and a root goes through the same composition with the normalisation switched off; selecting
                 // between register sets cost ~30 copies per bone)
-                if (rec.psrc != -2)
-                    prev = load_trs(slots + (size_t)(rec.psrc == -1 ? par.nslot : rec.psrc) * POSE_SLOT_FLOATS, lane);
+                load_trs_if(rec.psrc != -2, slots + (size_t)(rec.psrc == -1 ? par.nslot : max(rec.psrc, 0)) * POSE_SLOT_FLOATS, lane, prev);
                 prev = composep(prev, loc, rec.psrc == -1);
                 const TRSP& der = prev;
-                if (rec.store >= 0)
-                    store_trs(slots + (size_t)rec.store * POSE_SLOT_FLOATS, lane, der);
-                if (par.derived && active)
+                store_trs_if(rec.store >= 0, slots + (size_t)max(rec.store, 0) * POSE_SLOT_FLOATS, lane, der);
+                if (DER && active)
                     store_derived(par.derived + ((size_t)inst * par.J + bone) * 10, der);
                 float4 r0, r1, r2; // outputAnimationResult, skeleton.cpp:119-156
                 palette_rowsp(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
@@ -714,7 +741,7 @@ namespace pcl
                 row[0] = r0, row[1] = r1, row[2] = r2;
             }
             __syncwarp();
-            if (contiguous && ni == 32 && s0 + POSE_G <= par.J)
+            if (contiguous && ni == 32 && FULL)
             {
                 // 32 rows x 12 units, conflict-free (see lbs_i_flush12); the group's 4 slots are 12 consecutive units
                 const size_t off = (size_t)(PCL_STEP(s0).joint + 1) * 3;
@@ -763,6 +790,21 @@ namespace pcl
                 }
             }
             __syncwarp();
+        };
+        int s0 = 0;
+        if (WKEYS && uni)
+        {
+            for (; s0 + POSE_G <= par.J; s0 += POSE_G)
+                group(s0, std::true_type {}, std::true_type {});
+            if (s0 < par.J)
+                group(s0, std::false_type {}, std::true_type {});
+        }
+        else
+        {
+            for (; s0 + POSE_G <= par.J; s0 += POSE_G)
+                group(s0, std::true_type {}, std::false_type {});
+            if (s0 < par.J)
+                group(s0, std::false_type {}, std::false_type {});
         }
     }
 
