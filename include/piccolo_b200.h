@@ -120,6 +120,15 @@ int pcl_upload_mesh(pcl_ctx* ctx, int32_t V, const float* pos /*[3V]*/, const fl
                     const float* tan /*[3V]*/, const int32_t* idx4 /*[4V]*/, const float* w4_raw /*[4V]*/,
                     int32_t max_slot, pcl_mesh* out);
 
+/* Releasing assets: what a level unload does to the caches of AnimationManager (animation_system.cpp:10-13 - the reference
+ * never drops them; a long-running host must).  A released handle is invalid from then on and is not handed out again.
+ * pcl_clip_release also gives the clip's (clip, frame) buckets back, so that reloading levels does not grow the bucket count
+ * past what the frame-coherent order supports.  A skeleton can be released once no batch, pool or clip refers to it
+ * (PCL_ERR_INVALID otherwise).  Masks live with their skeleton.  Each call waits for the context's work first. */
+int pcl_clip_release(pcl_ctx* ctx, pcl_clip clip);
+int pcl_mesh_release(pcl_ctx* ctx, pcl_mesh mesh);
+int pcl_skeleton_release(pcl_ctx* ctx, pcl_skel skel);
+
 /* ---- instances -------------------------------------------------------------------------------
  * A batch = N independent AnimationComponents sharing one skeleton, each holding K clip slots
  * (BlendState::clip_count, resource/res_type/data/blend_state.h:32-45): clip id, blend_ratio (phase),

@@ -44,6 +44,9 @@ SIGNATURES = {
     "pcl_upload_clip": (C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _ip, _fp, _fp, _fp, C.c_int32, _ip, _ip]),
     "pcl_upload_mask": (C.c_int, [_vp, C.c_int32, C.c_int32, _ip, _ip]),
     "pcl_upload_mesh": (C.c_int, [_vp, C.c_int32, _fp, _fp, _fp, _ip, _fp, C.c_int32, _ip]),
+    "pcl_clip_release": (C.c_int, [_vp, C.c_int32]),
+    "pcl_mesh_release": (C.c_int, [_vp, C.c_int32]),
+    "pcl_skeleton_release": (C.c_int, [_vp, C.c_int32]),
     "pcl_batch_create": (C.c_int, [_vp, C.c_int32, _i64, C.c_int32, C.POINTER(_vp)]),
     "pcl_batch_destroy": (C.c_int, [_vp]),
     "pcl_batch_set": (C.c_int, [_vp, _i64, _i64, _ip, _fp, _fp, _fp, _ip]),
@@ -210,6 +213,15 @@ class Context:
         out = C.c_int32()
         self._ck(self.L.pcl_upload_mesh(self.h, mesh.V, _f(a[0]), _f(a[1]), _f(a[2]), _i(a[3]), _f(a[4]), max_slot, C.byref(out)))
         return out.value
+
+    def release_clip(self, clip: int):
+        self._ck(self.L.pcl_clip_release(self.h, clip))
+
+    def release_mesh(self, mesh: int):
+        self._ck(self.L.pcl_mesh_release(self.h, mesh))
+
+    def release_skeleton(self, skel: int):
+        self._ck(self.L.pcl_skeleton_release(self.h, skel))
 
     def batch(self, skel: int, N: int, K: int = 1) -> "Batch":
         return Batch(self, skel, N, K)

@@ -29,6 +29,8 @@ namespace
         std::vector<int32_t> index, parent, order;
         std::vector<StepRec> h_steps;       // host copy: source of the __constant__ upload
         int32_t              n_clips = 0, n_simple = 0;
+        int32_t              users = 0;     // batches, pools and skin launches referring to it: a skeleton in use cannot be released
+        bool                 released = false;
         StepRec*             d_steps = nullptr;
         int32_t*             d_sched = nullptr; // [n_rounds][POSE_L_WARPS] level-parallel schedule of pose_level_kernel
         int32_t              n_rounds = 0;
@@ -40,6 +42,8 @@ namespace
         pcl_skel skel;
         void*    d_blob = nullptr;
         ClipRec  rec {};
+        int32_t  frames = 0;     // (clip, frame) buckets it occupies
+        bool     released = false;
     };
     struct MaskHost
     {
@@ -49,6 +53,7 @@ namespace
     struct MeshRec
     {
         int32_t V = 0, Vp = 0, Vt = 0, max_slot = 0;
+        bool    released = false;
         float * d_pos = nullptr, *d_nrm = nullptr, *d_tan = nullptr;
         int4*   d_idx = nullptr;
         float4* d_w   = nullptr;
@@ -448,7 +453,7 @@ namespace
         return upload(c, &m.d_vrec_blk[si], hvc);
     }
 
-    bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size(); }
+    bool valid_skel(pcl_ctx* c, pcl_skel s) { return c && s >= 0 && s < (int)c->skels.size() && !c->skels[s].released; }
 
     // 2-D tensor map over a skinned stream [capacity][row_floats], box = 32 rows x 32 floats (128 B), 128-byte swizzle.
     // The encoder lives in the driver; it is fetched through the runtime so that the library has no link-time
@@ -952,6 +957,7 @@ extern "C"
         ch.rec.keys_step      = simple ? (const float4*)d2 : nullptr;
         ch.rec.anim_step      = simple ? (const uint32_t*)(d2 + up16(skb)) : nullptr;
         ch.rec.bucket_base    = c->n_buckets;
+        ch.frames             = total_frame;
         c->n_buckets += total_frame; // lo = floor(phase * (total_frame - 1)) is one of total_frame values
         sk.n_clips++;
         sk.n_simple += simple ? 1 : 0;
@@ -1079,6 +1085,70 @@ extern "C"
     }
 
     // ------------------------------------------------------------------------------------------
+    // releasing assets (a level unload / reload must not leave its device copies behind)
+    // ------------------------------------------------------------------------------------------
+    int pcl_clip_release(pcl_ctx* c, pcl_clip clip)
+    {
+        if (!c || clip < 0 || clip >= (int)c->clips.size() || c->clips[clip].released)
+            return fail(c, PCL_ERR_INVALID, "pcl_clip_release: bad handle");
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute)); // no launch may still read it
+        ClipHost& ch = c->clips[clip];
+        SkelRec&  sk = c->skels[ch.skel];
+        cudaFree(ch.d_blob);
+        ch.d_blob = nullptr, ch.released = true;
+        sk.n_clips--, sk.n_simple -= ch.rec.simple ? 1 : 0;
+        // give its (clip, frame) buckets back: the frame-coherent order only exists while all buckets fit its counters
+        int32_t base = 0;
+        for (auto& x : c->clips)
+            if (!x.released)
+                x.rec.bucket_base = base, base += x.frames;
+        c->n_buckets = base;
+        ch.rec = ClipRec {};
+        std::vector<ClipRec> all;
+        for (auto& x : c->clips)
+            all.push_back(x.rec);
+        if (c->d_clips)
+            PCL_CK(c, copy_h2d(c, c->d_clips, all.data(), all.size() * sizeof(ClipRec)));
+        return PCL_OK;
+    }
+    int pcl_mesh_release(pcl_ctx* c, pcl_mesh mesh)
+    {
+        if (!c || mesh < 0 || mesh >= (int)c->meshes.size() || c->meshes[mesh].released)
+            return fail(c, PCL_ERR_INVALID, "pcl_mesh_release: bad handle");
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        MeshRec& m = c->meshes[mesh];
+        cudaFree(m.d_pos), cudaFree(m.d_nrm), cudaFree(m.d_tan), cudaFree(m.d_idx), cudaFree(m.d_w), cudaFree(m.d_vrec);
+        for (int i = 0; i < 3; i++)
+            cudaFree(m.d_vrec_cta[i]), cudaFree(m.d_vrec_blk[i]);
+        cudaFree(m.d_blk_slots), cudaFree(m.d_blk_cnt);
+        m = MeshRec {};
+        m.released = true;
+        return PCL_OK;
+    }
+    int pcl_skeleton_release(pcl_ctx* c, pcl_skel skel)
+    {
+        if (!valid_skel(c, skel))
+            return fail(c, PCL_ERR_INVALID, "pcl_skeleton_release: bad handle");
+        SkelRec& s = c->skels[skel];
+        if (s.users > 0 || s.n_clips > 0)
+            return fail(c, PCL_ERR_INVALID, "pcl_skeleton_release: batches, pools or clips still refer to the skeleton");
+        PCL_CK(c, cudaSetDevice(c->device));
+        PCL_CK(c, cudaStreamSynchronize(c->compute));
+        {
+            std::lock_guard<std::mutex> lk(g_const_mu);
+            if (c->device < PCL_STATIC_MAX_DEVICES && g_const_owner[c->device].ctx == c && g_const_owner[c->device].skel == skel)
+                g_const_owner[c->device] = ConstOwner();
+        }
+        cudaFree(s.d_steps), cudaFree(s.d_sched), cudaFree(s.d_masks);
+        s.d_steps = nullptr, s.d_sched = nullptr, s.d_masks = nullptr, s.n_masks = s.cap_masks = 0;
+        s.h_steps.clear(), s.h_steps.shrink_to_fit();
+        s.released = true;
+        return PCL_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------
     // instances
     // ------------------------------------------------------------------------------------------
     int pcl_batch_create(pcl_ctx* c, pcl_skel skel, int64_t N, int32_t K, pcl_batch** out)
@@ -1117,6 +1187,7 @@ extern "C"
             delete b;
             return fail(c, e == cudaErrorMemoryAllocation ? PCL_ERR_OOM : PCL_ERR_CUDA, std::string("pcl_batch_create: ") + cudaGetErrorString(e));
         }
+        c->skels[skel].users++;
         *out = b;
         return PCL_OK;
     }
@@ -1126,6 +1197,7 @@ extern "C"
         if (!b)
             return PCL_ERR_INVALID;
         cudaSetDevice(b->ctx->device);
+        b->ctx->skels[b->skel].users--;
         cudaStreamSynchronize(b->ctx->compute), cudaStreamSynchronize(b->ctx->copy);
         cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len);
         if (b->pool)
@@ -1308,7 +1380,7 @@ extern "C"
                         else
                             v = -1;
                     }
-                    else if (v < 0 || v >= (int)c->clips.size() || c->clips[v].skel != b->skel)
+                    else if (v < 0 || v >= (int)c->clips.size() || c->clips[v].skel != b->skel || c->clips[v].released)
                         return fail(c, PCL_ERR_INVALID, "pcl_batch_set: clip id does not belong to the batch's skeleton");
                     ti[(size_t)k * count + i] = v;
                 }
@@ -1638,7 +1710,7 @@ extern "C"
                 if (clip_ids)
                 {
                     const int32_t v = clip_ids[i * K + k];
-                    if (v < 0 || v >= (int)c->clips.size() || c->clips[v].skel != b->skel)
+                    if (v < 0 || v >= (int)c->clips.size() || c->clips[v].skel != b->skel || c->clips[v].released)
                         return fail(c, PCL_ERR_INVALID, "pcl_batch_frame: clip id does not belong to the batch's skeleton");
                     h_clip[(size_t)k * N + i] = v;
                 }
@@ -1723,7 +1795,8 @@ extern "C"
 
     int pcl_skinbuf_create(pcl_ctx* c, pcl_mesh mesh, int64_t capacity, int32_t flags, pcl_skinbuf** out)
     {
-        if (!c || !out || mesh < 0 || mesh >= (int)c->meshes.size() || capacity < 1 || (flags != PCL_SKIN_POS && flags != PCL_SKIN_POS_NRM_TAN))
+        if (!c || !out || mesh < 0 || mesh >= (int)c->meshes.size() || c->meshes[mesh].released || capacity < 1 ||
+            (flags != PCL_SKIN_POS && flags != PCL_SKIN_POS_NRM_TAN))
             return fail(c, PCL_ERR_INVALID, "pcl_skinbuf_create: bad argument");
         PCL_CK(c, cudaSetDevice(c->device));
         pcl_skinbuf* s = new pcl_skinbuf();
@@ -1767,7 +1840,7 @@ extern "C"
         if (!b || !out)
             return PCL_ERR_INVALID;
         pcl_ctx* c = b->ctx;
-        if (out->ctx != c || out->mesh != mesh || mesh < 0 || mesh >= (int)c->meshes.size())
+        if (out->ctx != c || out->mesh != mesh || mesh < 0 || mesh >= (int)c->meshes.size() || c->meshes[mesh].released)
             return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: skin buffer was created for another mesh / context");
         if (first < 0 || count < 1 || first + count > b->N || slot_first < 0 || slot_first + count > out->capacity)
             return fail(c, PCL_ERR_INVALID, "pcl_batch_skin: range outside the batch or the ring");

@@ -354,9 +354,26 @@ namespace Piccolo
         return h;
     }
 
+    // Drops the host caches AND the device copies behind them (a level unload): clips first, then every skeleton nothing
+    // refers to any more (a skeleton some live Skeleton / AnimationBatch still poses with stays until that object is gone).
     void AnimationManager::clearCaches()
     {
         m_skeleton_definition_cache.clear(), m_animation_data_cache.clear(), m_animation_skeleton_map_cache.clear(), m_skeleton_mask_cache.clear();
+        if (pcl_ctx* c = Runtime::context())
+        {
+            std::vector<pcl_clip> clips;
+            for (auto& kv : g_dev_clips)
+                clips.push_back(kv.second);
+            for (auto& kv : g_dev_clips_by_content)
+                clips.push_back(kv.second);
+            std::sort(clips.begin(), clips.end());
+            clips.erase(std::unique(clips.begin(), clips.end()), clips.end());
+            for (pcl_clip h : clips)
+                if (h >= 0)
+                    pcl_clip_release(c, h);
+            for (auto& kv : g_dev_skels_by_content)
+                pcl_skeleton_release(c, kv.second); // refused while in use: then it stays
+        }
         g_dev_clips.clear(), g_dev_masks.clear(), g_dev_clips_by_content.clear(), g_dev_skels_by_content.clear();
     }
 

@@ -874,6 +874,53 @@ def test_one_call_frame_refuses_large_batches(ctx, player_dev):
         b.close()
 
 
+def test_released_assets_give_memory_and_buckets_back(player):
+    """Level reloads: clips, meshes and skeletons can be released (the reference's AnimationManager caches only ever grow,
+    animation_system.cpp:10-13).  400 upload / release cycles leave the device memory where it was and the (clip, frame)
+    bucket count low enough for the frame-coherent order (each bundled clip occupies 23 buckets, the order supports 8192);
+    a released handle is refused; a skeleton in use cannot be released."""
+    import torch
+    from piccolo_b200 import capi
+    sk, cl, am, mk = player
+    mesh = A.make_player_mesh(sk, V=3000, seed=5)
+    c = capi.Context(0)
+    try:
+        skel = c.upload_skeleton(sk)
+        keep = c.upload_clip(skel, cl, am)
+        b = c.batch(skel, 5000, 1)
+        ph = np.linspace(0, 1, 5000, endpoint=False, dtype=np.float32)
+        b.set(clip_ids=np.full((5000, 1), keep, np.int32), phase=ph)
+        b.pose()
+        want = b.download_palette3x4()
+        torch.cuda.init()
+        c.sync()
+        for it in range(400):
+            if it == 20:
+                free0 = torch.cuda.mem_get_info(0)[0]  # (the allocator's pools have settled)
+            tmp = c.upload_clip(skel, cl, am)
+            m = c.upload_mesh(mesh, sk.J)
+            s2 = c.upload_skeleton(sk)
+            c.release_clip(tmp), c.release_mesh(m), c.release_skeleton(s2)
+        assert torch.cuda.mem_get_info(0)[0] >= free0 - (4 << 20)
+        with pytest.raises(capi.PclError):
+            c.release_clip(tmp)  # twice
+        with pytest.raises(capi.PclError):
+            b.set(clip_ids=np.full((5000, 1), tmp, np.int32), phase=ph)  # a released clip
+        with pytest.raises(capi.PclError):
+            c.release_skeleton(skel)  # a batch and a clip still use it
+        c.set_option("pose_sort", 1)
+        l0 = c.launch_count()
+        b.set(clip_ids=np.full((5000, 1), keep, np.int32), phase=ph)
+        b.pose()
+        assert c.launch_count() - l0 == 4, "the frame-coherent order was lost to leaked buckets"
+        assert np.array_equal(b.download_palette3x4(), want)
+        b.close()
+        c.release_clip(keep)
+        c.release_skeleton(skel)
+    finally:
+        c.close()
+
+
 def test_render_handoff_layout(ctx, player_dev):
     """joint_matrices[1024 * instance_in_draw + slot], 64 instances per draw, slot 0 = identity, only J+1 slots touched
     (main_camera_pass.cpp:2284-2298; mesh_component.cpp:72-79)."""
