@@ -77,5 +77,6 @@ def sample_ranges(n_total: int, n_ranges: int, width: int, seed: int = 3):
     while len(picks) < n_ranges:
         picks.add(int(rng.integers(0, slots)))
     starts = sorted(p * width for p in picks)
-    starts[-1] = n_total - width  # the very last instances, whatever n_total % width is
+    if len(starts) > 1:
+        starts[-1] = n_total - width  # the very last instances, whatever n_total % width is
     return [(s, width) for s in starts]
