@@ -294,6 +294,8 @@ int pcl_batch_push_to_pool(pcl_batch* b, pcl_pool* pool, int64_t first);
  * "export_mode" (0 = auto, 1, 2, 3: see pcl_batch_download_palette3x4_async); "lbs_compact" (-1 = auto: when whole palettes
  * would force variant 3 below 32 instances per CTA, 0 = never, 1 = whenever it fits: variant 3 keeps, per instance, only the
  * palette rows the current block of 1024 vertices references).
+ * "pool_bulk" (-1 / 1 = a batch attached to a pool in ANOTHER GPU's memory sends its palette rows as asynchronous bulk copies, 0 = as
+ * plain stores from the lanes).
  * PCL_ERR_INVALID for unknown keys. */
 int pcl_set_option(pcl_ctx* ctx, const char* key, int32_t value);
 

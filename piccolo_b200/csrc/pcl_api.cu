@@ -105,7 +105,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0, opt_lbs_compact = -1;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0, opt_lbs_compact = -1, opt_pool_bulk = -1;
     void*        h_small = nullptr;  // pinned staging of small synchronous palette read-backs
     bool         debug_sync = false; // PICCOLO_B200_DEBUG_SYNC=1: synchronise after every launch
     int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
@@ -673,6 +673,8 @@ extern "C"
             c->opt_export_mode = v;
         else if (k == "lbs_compact" && v >= -1 && v <= 1)
             c->opt_lbs_compact = v;
+        else if (k == "pool_bulk" && v >= -1 && v <= 1)
+            c->opt_pool_bulk = v;
         else
             return fail(c, PCL_ERR_INVALID, "pcl_set_option: unknown key or bad value: " + k);
         return PCL_OK;
@@ -1557,6 +1559,7 @@ extern "C"
         // (not when the palettes go to another GPU's pool: rows visited in random order over gigabytes of peer memory ran at
         // 69 GB/s against 350 GB/s in instance order, tools/pool_gather_check.py on two B200s)
         const bool remote = b->pool && (!b->pool->owner || b->pool->ctx->device != c->device);
+        const bool bulk_remote = remote && c->opt_pool_bulk != 0; // palettes in another GPU's memory leave as bulk copies (pose_simple_kernel, BULK)
         bool sorted = simple && !io && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
                       (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= 262144 && !remote));
         if (sorted)
@@ -1616,6 +1619,11 @@ extern "C"
 #define PCL_LAUNCH_POSE_S(KK, SS, MM)                                                                                       \
     {                                                                                                                       \
         if (p.derived) PCL_LAUNCH_POSE_SD(KK, SS, 2, true) /* (the read-back form exists for 2 blocks per SM only) */       \
+        else if (bulk_remote && KK <= 2 && !SS)                                                                             \
+        {                                                                                                                   \
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<(KK <= 2 ? KK : 1), false, 2, false, true>, smem); if (rc__) return rc__; } \
+            pose_simple_kernel<(KK <= 2 ? KK : 1), false, 2, false, true><<<grid, wpb * 32, smem, c->compute>>>(p);          \
+        }                                                                                                                   \
         else PCL_LAUNCH_POSE_SD(KK, SS, MM, false)                                                                          \
     }
 #define PCL_LAUNCH_POSE_MB(KK, SS)                                                                                          \

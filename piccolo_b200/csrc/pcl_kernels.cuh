@@ -505,11 +505,28 @@ namespace pcl
 #ifndef PCL_POSE_STEPS_SMEM
 #define PCL_POSE_STEPS_SMEM 0
 #endif
+    // BULK (palettes that live in ANOTHER GPU's memory, pcl_batch_attach_pool): the staged rows of a group leave as one bulk copy
+    // per instance (cp.async.bulk shared -> global, 192 contiguous bytes) instead of 16-byte stores from the lanes.  Stores over
+    // NVLink keep the issuing warp's store queue busy far longer than local ones, and the pose kernel - latency-bound as it is -
+    // stalled behind them (376 GB/s per producer); the bulk copies are asynchronous, the warp goes on with the next group and only
+    // has to find its staging tile read before it overwrites it.  (A plain store-side bulk copy: nothing is multicast, nothing is
+    // loaded from the peer.)
+    __device__ __forceinline__ void pose_bulk_store(void* dst_global, const void* src_smem, uint32_t bytes)
+    {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // this lane's staging stores, for the async proxy
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_global), "r"((uint32_t)__cvta_generic_to_shared(src_smem)),
+                     "r"(bytes)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    __device__ __forceinline__ void pose_bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+    __device__ __forceinline__ void pose_bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
     // DER: the derived transforms are written out too (LevelDebugger-style read-back); a template parameter so that the common
     // form carries no branch for it.  A group of POSE_G bones is ONE straight-line block there (no bounds checks in whole groups,
     // parent fetch and parking predicated instead of branched): ptxas may then run bone s + 1's sampling and local pose - which do
     // not depend on the hierarchy - inside bone s's composition chain.
-    template<int K, bool SORTED, int MB, bool DER>
+    template<int K, bool SORTED, int MB, bool DER, bool BULK = false>
     __global__ void __launch_bounds__(POSE_S_THREADS, MB) pose_simple_kernel(const PoseParams par)
     {
         extern __shared__ __align__(16) float smem[];
@@ -737,11 +754,21 @@ namespace pcl
                     store_derived(par.derived + ((size_t)inst * par.J + bone) * 10, der);
                 float4 r0, r1, r2; // outputAnimationResult, skeleton.cpp:119-156
                 palette_rowsp(der, rec.ib0, rec.ib1, rec.ib2, r0, r1, r2);
+                if (BULK && g == 0)
+                    pose_bulk_wait_read(); // the previous group's bulk copy has read this lane's staging row
                 float4* row = reinterpret_cast<float4*>(stage + (size_t)lane * SROW + g * 12);
                 row[0] = r0, row[1] = r1, row[2] = r2;
             }
             __syncwarp();
-            if (contiguous && ni == 32 && FULL)
+            if (BULK && contiguous && FULL && active)
+            {
+                // this lane's own row: 4 slots x 48 bytes, contiguous in the (remote) palette
+                pose_bulk_store(par.palette + (size_t)inst * rowsz + (size_t)(PCL_STEP(s0).joint + 1) * 3, stage + (size_t)lane * SROW, POSE_G * 48);
+            }
+            else if (BULK && contiguous && FULL)
+            {
+            }
+            else if (contiguous && ni == 32 && FULL)
             {
                 // 32 rows x 12 units, conflict-free (see lbs_i_flush12); the group's 4 slots are 12 consecutive units
                 const size_t off = (size_t)(PCL_STEP(s0).joint + 1) * 3;
@@ -806,6 +833,8 @@ namespace pcl
             if (s0 < par.J)
                 group(s0, std::false_type {}, std::false_type {});
         }
+        if (BULK)
+            pose_bulk_wait_all();
     }
 
     // -------------------------------------------------------------------------------------------
