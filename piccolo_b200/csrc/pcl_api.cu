@@ -1977,10 +1977,15 @@ extern "C"
                         q.vsplit = (q.n_sc + q.per_sc - 1) / q.per_sc;
                     }
                     const unsigned grid = (unsigned)(full * q.vsplit);
+#define PCL_LAUNCH_LBSC_C(NT_, TL_, T_, C_)                                                                                 \
+    {                                                                                                                       \
+        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<NT_, TL_, T_, C_>, smem_c); if (rc__) return rc__; }         \
+        lbs_cta_kernel<NT_, TL_, T_, C_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, tmp_pos, tmp_nt);                    \
+    }
 #define PCL_LAUNCH_LBSC(NT_, TL_, T_)                                                                                        \
     {                                                                                                                       \
-        { int rc__ = ensure_smem(c, (const void*)lbs_cta_kernel<NT_, TL_, T_>, smem_c); if (rc__) return rc__; }             \
-        lbs_cta_kernel<NT_, TL_, T_><<<grid, LBS_C_THREADS, smem_c, c->compute>>>(q, tmp_pos, tmp_nt);                         \
+        if (compact) PCL_LAUNCH_LBSC_C(NT_, TL_, T_, true)                                                                  \
+        else PCL_LAUNCH_LBSC_C(NT_, TL_, T_, false)                                                                         \
     }
 #define PCL_LAUNCH_LBSC_T(T_)                                                                                               \
     {                                                                                                                       \
@@ -1994,6 +1999,7 @@ extern "C"
                     else PCL_LAUNCH_LBSC_T(8)
 #undef PCL_LAUNCH_LBSC_T
 #undef PCL_LAUNCH_LBSC
+#undef PCL_LAUNCH_LBSC_C
                     c->launches++;
                     PCL_POST_LAUNCH(c, c->compute, "lbs_cta_kernel");
                 }

@@ -1800,7 +1800,9 @@ namespace pcl
         const int32_t*  blk_cnt;   // [n_blocks]
     };
 
-    template<bool NT, int LBS_C_TILES, int T>
+    // COMPACT (block-local palette rows, see LbsCParams::blk_sc) is a template parameter: the whole-palette form - the headline's
+    // kernel, which runs at the board's power cap where every instruction counts - carries none of its code.
+    template<bool NT, int LBS_C_TILES, int T, bool COMPACT>
     __global__ void __launch_bounds__(LBS_C_THREADS, 1)
         lbs_cta_kernel(const LbsCParams par, const __grid_constant__ CUtensorMap tm_pos, const __grid_constant__ CUtensorMap tm_nt)
     {
@@ -1828,8 +1830,8 @@ namespace pcl
         const int s_lo = split * per, s_hi = min(par.n_sc, s_lo + per);
         if (s_lo >= s_hi)
             return;
-        const int  n_steps = s_hi - s_lo;
-        const bool compact = par.blk_sc != 0;
+        const int      n_steps = s_hi - s_lo;
+        constexpr bool compact = COMPACT;
         // named barriers: 1 + b = tile b full (compute arrives, store warp syncs); 1 + TILES + b = tile b empty (store arrives, compute syncs)
 
         if (tid == 0)
