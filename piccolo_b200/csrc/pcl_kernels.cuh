@@ -1233,7 +1233,7 @@ namespace pcl
     template<bool NT, bool STORE_TMA>
     __global__ void __launch_bounds__(LBS_THREADS, 2) lbs_kernel(const LbsParams par)
     {
-        extern __shared__ __align__(128) unsigned char lsm[];
+        extern __shared__ __align__(1024) unsigned char lsm[];
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int tile  = blockIdx.x / par.vsplit;
         const int split = blockIdx.x - tile * par.vsplit;
@@ -1288,7 +1288,6 @@ namespace pcl
         {
             mbar_wait(&bars[1], vphase);
             vphase ^= 1;
-            const int    v  = vt * LBS_VT + tid;
             const float3 p  = make_float3(vpos[tid * 3], vpos[tid * 3 + 1], vpos[tid * 3 + 2]);
             float3       n  = make_float3(0, 0, 0), t = make_float3(0, 0, 0);
             if (NT)
@@ -1537,7 +1536,7 @@ namespace pcl
     {
         constexpr int LBS_I_WARPS = WARPS;
         constexpr int LBS_I_NTROW = lbs_i_ntrow(HALF);
-        extern __shared__ __align__(128) unsigned char lsm[];
+        extern __shared__ __align__(1024) unsigned char lsm[];
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         const int tile  = blockIdx.x / par.vsplit;
         const int split = blockIdx.x - tile * par.vsplit;

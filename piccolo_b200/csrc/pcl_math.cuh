@@ -152,14 +152,14 @@ namespace pcl
     }
     __device__ __forceinline__ float lo(f2 v)
     {
-        float a, b;
-        asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+        float a;
+        asm("{ .reg .b32 t; mov.b64 {%0, t}, %1; }" : "=f"(a) : "l"(v));
         return a;
     }
     __device__ __forceinline__ float hi(f2 v)
     {
-        float a, b;
-        asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+        float b;
+        asm("{ .reg .b32 t; mov.b64 {t, %0}, %1; }" : "=f"(b) : "l"(v));
         return b;
     }
     __device__ __forceinline__ f2 bc(float x) { return pk(x, x); }            // broadcast operand
