@@ -725,7 +725,7 @@ extern "C"
             return fail(c, PCL_ERR_UNSUPPORTED, "pcl_upload_skeleton: hierarchy needs more parked parents than shared memory holds");
         s.nslot = nslot;
         s.order = order;
-        s.pitch = (J + 1 + 1) & ~1; // slots per instance, even => every instance starts on a 32-byte sector
+        s.pitch = (J + 1 + 3) & ~3; // slots per instance, a multiple of 4 => every instance starts on a 64-byte boundary (the pose kernel flushes 4 slots = 192 bytes at a time)
         std::vector<int32_t> step_of(J);
         for (int st = 0; st < J; st++)
             step_of[order[st]] = st;

@@ -581,11 +581,7 @@ namespace pcl
             const int mid = (K > 1 && par.mask_ids) ? __ldg(par.mask_ids + o) : -1;
             st[k].mask_off = mid < 0 ? -1 : mid * par.J;
         }
-        if (active)
-        {
-            float4* p0 = par.palette + (size_t)inst * par.pitch * 3; // slot 0 = identity (mesh_component.cpp:72-79)
-            p0[0] = make_float4(1, 0, 0, 0), p0[1] = make_float4(0, 1, 0, 0), p0[2] = make_float4(0, 0, 1, 0);
-        }
+        // (slot 0 = identity, mesh_component.cpp:72-79: it leaves with the first group's flush, see `group` below)
         // lane-dependent parts of the flush addresses (rows = instances, 12 units = POSE_G bones x 3 rows)
         const int fa = lane >> 3, fb = lane & 7, fc4 = ((lane >> 2) & 1) * 4, fd = lane & 3;
         const int s_f0 = fa * SROW + fb * 4, s_f2 = (fa + fc4) * SROW + (8 + fd) * 4;
@@ -648,31 +644,44 @@ namespace pcl
             amask[k] = 0xffffffffu;
             if (PREFETCH && !uni)
             {
-                nk[k] = fetch_keys(st[k], 0);
+                // (step s sits at position (s + 1) & 3 of its group: step 0 uses buffer 1, step 1 buffer 0)
+                nk[PD == 2 ? K + k : k] = fetch_keys(st[k], 0);
                 if (PD == 2)
-                    nk[K + k] = fetch_keys(st[k], 1);
+                    nk[k] = fetch_keys(st[k], 1);
             }
         }
 
         auto group = [&](const int s0, auto full_tag, auto uni_tag) {
             constexpr bool FULL = decltype(full_tag)::value; // all POSE_G bones of the group exist
             constexpr bool UNI  = decltype(uni_tag)::value;  // the warp's keys come from its shared-memory copy
-            if (K > 1 && (s0 & 31) == 0)
-            {
-#pragma unroll
-                for (int k = 0; k < K; k++)
-                    amask[k] = __ldg(st[k].anim + (s0 >> 5));
-            }
+            // A group is four consecutive palette SLOTS starting at a multiple of four - 192 bytes on a 64-byte boundary of the
+            // instance's row (the row pitch is a multiple of 4 slots) - so its flush writes whole 32-byte sectors only.  Slot 0 is
+            // the identity, slot j + 1 bone j: the first group is the identity + steps 0..2 (s0 = -1), the next one steps 3..6, ...
+            // (Groups of four STEPS put every flush 48 bytes off the boundary: both end sectors of each instance's 192 bytes
+            // were written in halves by two different flushes.  1 M instances, one clip: 1.13 -> 0.95 ms, tools/pose_bench.py.)
+            const int slot0 = s0 < 0 ? 0 : PCL_STEP(s0).joint + 1;
             bool contiguous = true; // the group's palette slots are consecutive (always, unless the upload re-ordered the bones)
 #pragma unroll
             for (int g = 0; g < POSE_G; g++)
             {
                 const int s = s0 + g;
+                if (g == 0 && s0 < 0)
+                {
+                    float4* row = reinterpret_cast<float4*>(stage + (size_t)lane * SROW);
+                    row[0] = make_float4(1, 0, 0, 0), row[1] = make_float4(0, 1, 0, 0), row[2] = make_float4(0, 0, 1, 0);
+                    continue;
+                }
                 if (!FULL && s >= par.J)
                     break;
+                if (K > 1 && g == 1 && ((s0 + 1) & 31) == 0) // (step s0 itself is the last bit of the previous word)
+                {
+#pragma unroll
+                    for (int k = 0; k < K; k++)
+                        amask[k] = __ldg(st[k].anim + ((s0 + 1) >> 5));
+                }
                 const StepRec& rec  = PCL_STEP(s);
                 const int      bone = rec.joint;
-                contiguous          = contiguous && (bone == PCL_STEP(s0).joint + g);
+                contiguous          = contiguous && (bone + 1 == slot0 + g);
                 KeyPair ck[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
@@ -763,7 +772,7 @@ namespace pcl
             if (BULK && contiguous && FULL && active)
             {
                 // this lane's own row: 4 slots x 48 bytes, contiguous in the (remote) palette
-                pose_bulk_store(par.palette + (size_t)inst * rowsz + (size_t)(PCL_STEP(s0).joint + 1) * 3, stage + (size_t)lane * SROW, POSE_G * 48);
+                pose_bulk_store(par.palette + (size_t)inst * rowsz + (size_t)slot0 * 3, stage + (size_t)lane * SROW, POSE_G * 48);
             }
             else if (BULK && contiguous && FULL)
             {
@@ -771,7 +780,7 @@ namespace pcl
             else if (contiguous && ni == 32 && FULL)
             {
                 // 32 rows x 12 units, conflict-free (see lbs_i_flush12); the group's 4 slots are 12 consecutive units
-                const size_t off = (size_t)(PCL_STEP(s0).joint + 1) * 3;
+                const size_t off = (size_t)slot0 * 3;
 #pragma unroll
                 for (int gq = 0; gq < 4; gq++)
                 {
@@ -812,13 +821,13 @@ namespace pcl
                     const int s  = s0 + g;
                     const size_t irow = SORTED ? (size_t)__shfl_sync(0xffffffffu, inst32, il & 31) : (size_t)(inst0 + il);
                     if (s < par.J && il < ni)
-                        par.palette[(irow * par.pitch + PCL_STEP(s).joint + 1) * 3 + (rm - g * 3)] =
+                        par.palette[(irow * par.pitch + (s < 0 ? 0 : PCL_STEP(s).joint + 1)) * 3 + (rm - g * 3)] =
                             *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
                 }
             }
             __syncwarp();
         };
-        int s0 = 0;
+        int s0 = -1; // (the identity slot takes the first place of the first group)
         if (WKEYS && uni)
         {
             for (; s0 + POSE_G <= par.J; s0 += POSE_G)
