@@ -896,12 +896,15 @@ extern "C"
         for (int n = 0; n < NCH && simple; n++)
             if (convert[n] != -1 && next[n] >= 0)
                 simple = false;
-        const int            Jp = (J + POSE_G - 1) / POSE_G * POSE_G + POSE_G;
+        const int            Jp = pose_jp(J);
         std::vector<float4>   skeys;
         std::vector<uint32_t> sanim;
         if (simple)
         {
-            skeys.assign((size_t)Jp * F * 3, make_float4(0, 0, 0, 0));
+            skeys.assign(((size_t)Jp * F * 5 + 1) / 2, make_float4(0, 0, 0, 0)); // a | q | c tables (16, 16, 8 bytes per key)
+            float4* const ta = skeys.data();
+            float4* const tq = ta + (size_t)Jp * F;
+            float2* const tc = reinterpret_cast<float2*>(tq + (size_t)Jp * F);
             sanim.assign((Jp + 31) / 32, 0u);
             for (int st = 0; st < Jp; st++)
             {
@@ -910,7 +913,7 @@ extern "C"
                     sanim[st >> 5] |= 1u << (st & 31);
                 for (int k = 0; k < F; k++)
                 {
-                    // {p.x, p.y, s.x, s.y} {q.wxyz} {p.z, s.z, -, -}; bones without a channel get the identity track; beyond its
+                    // {p.x, p.y, s.x, s.y} | {q.wxyz} | {p.z, s.z}: one table per component (KeyPair, pcl_kernels.cuh); bones without a channel get the identity track; beyond its
                     // clamp (the carried-over prefix minimum, skeleton.cpp:75-87) a track continues with copies of the clamp key
                     float4 kp = make_float4(0, 0, 0, 0), kq = make_float4(1, 0, 0, 0), ks = make_float4(1, 1, 1, 0);
                     if (ch >= 0)
@@ -918,9 +921,9 @@ extern "C"
                         const int kk = std::min(k, hic[ch]);
                         kp = keys[((size_t)ch * F + kk) * 3], kq = keys[((size_t)ch * F + kk) * 3 + 1], ks = keys[((size_t)ch * F + kk) * 3 + 2];
                     }
-                    skeys[((size_t)st * F + k) * 3 + 0] = make_float4(kp.x, kp.y, ks.x, ks.y);
-                    skeys[((size_t)st * F + k) * 3 + 1] = kq;
-                    skeys[((size_t)st * F + k) * 3 + 2] = make_float4(kp.z, ks.z, 0.f, 0.f);
+                    ta[(size_t)st * F + k] = make_float4(kp.x, kp.y, ks.x, ks.y);
+                    tq[(size_t)st * F + k] = kq;
+                    tc[(size_t)st * F + k] = make_float2(kp.z, ks.z);
                 }
             }
         }

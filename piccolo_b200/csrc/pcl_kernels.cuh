@@ -51,7 +51,7 @@ namespace pcl
         // min(frame, F - 1) of such a track returns what the clamp of skeleton.cpp:75-87 returns (beyond the clamp lo and hi
         // name the same key, and interpolating a key with its copy gives the key back exactly), so the two key indices
         // are computed ONCE per instance and a key's address depends on (step, instance) only - no clamp table on the hot path
-        const float4*   keys_step;  // [Jp][F][3]
+        const float4*   keys_step;  // three tables, [Jp][F] each: a (16 B) | q (16 B) | c (8 B), see KeyPair
         const uint32_t* anim_step;  // [ceil(Jp / 32)] bit s: a played channel drives step s (blend path: bones no clip animates keep the bind pose)
         int32_t        bucket_base; // first (clip, frame) bucket of this clip in the context-wide numbering (order_* kernels)
         int32_t        pad_[3];
@@ -344,12 +344,16 @@ namespace pcl
     constexpr int POSE_CMAX = 320; // bones whose step records fit the constant bank (320 * 128 B = 40 KB)
     __constant__ StepRec c_steps[POSE_CMAX];
 
-    // A step-ordered key is 48 bytes: {p.x p.y s.x s.y} {q.w q.x q.y q.z} {p.z s.z - -} - the pair layout of TRSP, so that
-    // the registers of the vector loads ARE the packed operands.  Only the first 40 are ever
-    // loaded (128 + 128 + 64 bit), so no loaded register is dead: a dead lane of a vector load gets re-used by
-    // ptxas as a scratch register at once, and the write-after-write hazard then stalls the warp for the full
-    // load latency right behind the prefetch (seen as long_scoreboard on the first FMUL after the LDGs in
-    // profiles/r1_pose_v2_*).
+    // Step-ordered keys, one table per component (ClipRec::keys_step): {p.x p.y s.x s.y} [Jp][F] | {q.w q.x q.y q.z} [Jp][F] |
+    // {p.z s.z} [Jp][F] - the pair layout of TRSP, so that the registers of the vector loads ARE the packed operands, and no
+    // loaded register is dead (a dead lane of a vector load gets re-used by ptxas as a scratch register at once, and the
+    // write-after-write hazard then stalls the warp for the full load latency right behind the prefetch - seen as
+    // long_scoreboard on the first FMUL after the LDGs in profiles/r1_pose_v2_*).
+    // Why per component: the 32 lanes of a warp sit at 32 different frames of the SAME step, and a load instruction costs the
+    // L1 one pass per distinct 128-byte line.  A step's row of one component is F x 16 bytes - three or four lines for the
+    // player's 23-frame clip - where the interleaved 48-byte keys spread the same 32 lanes over ~18 lines per instruction
+    // (l1tex at 73 % of peak, warps waiting on it half of the time: profiles/r2_pose_v7_k2_summary.txt).
+    __host__ __device__ inline int pose_jp(int J) { return (J + POSE_G - 1) / POSE_G * POSE_G + POSE_G; } // rows per table
     struct KeyPair
     {
         float4 a0, q0, a1, q1;
@@ -359,7 +363,7 @@ namespace pcl
     {
         const float4*   keys;
         const uint32_t* anim;
-        uint32_t        F3, lo3, hi3; // keys per track, index of the lower / upper key of this instance: all in 16-byte units (x 3)
+        uint32_t        F, lo, hi; // keys per track, index of the lower / upper key of this instance
         int32_t         mask_off;
         float           r, w;
     };
@@ -371,7 +375,7 @@ namespace pcl
         st.r           = exact - (float)fl;
         const int h    = max(min(ce, F - 1), 0);
         const int l    = max(min(fl, h), 0);
-        st.F3 = (uint32_t)F * 3u, st.lo3 = (uint32_t)l * 3u, st.hi3 = (uint32_t)h * 3u;
+        st.F = (uint32_t)F, st.lo = (uint32_t)l, st.hi = (uint32_t)h;
     }
     // `after` is an opaque zero derived from a value the caller has just computed.  Adding it to the address
     // pins the loads BEHIND that computation, i.e. behind the consumption of the keys requested one bone ago.
@@ -381,14 +385,14 @@ namespace pcl
         asm volatile("and.b32 %0, %1, 0;" : "=r"(z) : "r"(__float_as_int(v)));
         return z;
     }
-    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int after = 0)
+    __device__ __forceinline__ KeyPair fetch_keys(const SimpleSlot& st, int s, int jp, int after = 0)
     {
-        const uint32_t base = (uint32_t)s * st.F3 + (uint32_t)after; // a clip's step-ordered copy is far below 2^32 units
-        const float4*  kl   = st.keys + (base + st.lo3);
-        const float4*  kh   = st.keys + (base + st.hi3);
+        // a clip's step-ordered copy is far below 2^32 units
+        const uint32_t ia = (uint32_t)s * st.F + (uint32_t)after, iq = (uint32_t)(s + jp) * st.F + (uint32_t)after;
+        const float2*  kc = reinterpret_cast<const float2*>(st.keys) + ((uint32_t)(s + 4 * jp) * st.F + (uint32_t)after);
         KeyPair        k;
-        k.a0 = __ldg(kl), k.q0 = __ldg(kl + 1), k.c0 = __ldg(reinterpret_cast<const float2*>(kl + 2));
-        k.a1 = __ldg(kh), k.q1 = __ldg(kh + 1), k.c1 = __ldg(reinterpret_cast<const float2*>(kh + 2));
+        k.a0 = __ldg(st.keys + (ia + st.lo)), k.q0 = __ldg(st.keys + (iq + st.lo)), k.c0 = __ldg(kc + st.lo);
+        k.a1 = __ldg(st.keys + (ia + st.hi)), k.q1 = __ldg(st.keys + (iq + st.hi)), k.c1 = __ldg(kc + st.hi);
         return k;
     }
     // (Tried and rejected: staging the keys with cp.async - LDGSTS, one 80-byte shared-memory cell per lane and clip, four bones
@@ -582,6 +586,7 @@ namespace pcl
             st[k].mask_off = mid < 0 ? -1 : mid * par.J;
         }
         // (slot 0 = identity, mesh_component.cpp:72-79: it leaves with the first group's flush, see `group` below)
+        const int jp = pose_jp(par.J); // rows per key table (fetch_keys)
         // lane-dependent parts of the flush addresses (rows = instances, 12 units = POSE_G bones x 3 rows)
         const int fa = lane >> 3, fb = lane & 7, fc4 = ((lane >> 2) & 1) * 4, fd = lane & 3;
         const int s_f0 = fa * SROW + fb * 4, s_f2 = (fa + fc4) * SROW + (8 + fd) * 4;
@@ -618,15 +623,22 @@ namespace pcl
             // (all three exchanges before any comparison: a short-circuited && would keep lanes out of a full-mask shuffle)
             const unsigned long long kp  = reinterpret_cast<unsigned long long>(st[0].keys);
             const unsigned long long kp0 = __shfl_sync(0xffffffffu, kp, 0);
-            const uint32_t           lo0 = __shfl_sync(0xffffffffu, st[0].lo3, 0), hi0 = __shfl_sync(0xffffffffu, st[0].hi3, 0);
-            const bool               same = (kp == kp0) & (st[0].lo3 == lo0) & (st[0].hi3 == hi0);
+            const uint32_t           lo0 = __shfl_sync(0xffffffffu, st[0].lo, 0), hi0 = __shfl_sync(0xffffffffu, st[0].hi, 0);
+            const bool               same = (kp == kp0) & (st[0].lo == lo0) & (st[0].hi == hi0);
             uni = __all_sync(0xffffffffu, same) != 0;
             if (uni)
             {
                 for (int i = lane; i < par.J * 6; i += 32)
                 {
                     const int sI = i / 6, u = i - sI * 6;
-                    wkeys[i]     = __ldg(st[0].keys + ((uint32_t)sI * st[0].F3 + (u < 3 ? st[0].lo3 + u : st[0].hi3 + (u - 3))));
+                    const uint32_t f = u < 3 ? st[0].lo : st[0].hi, c = u < 3 ? u : u - 3; // component: 0 a, 1 q, 2 c
+                    if (c < 2)
+                        wkeys[i] = __ldg(st[0].keys + ((uint32_t)(sI + c * jp) * st[0].F + f));
+                    else
+                    {
+                        const float2 t = __ldg(reinterpret_cast<const float2*>(st[0].keys) + ((uint32_t)(sI + 4 * jp) * st[0].F + f));
+                        wkeys[i]       = make_float4(t.x, t.y, 0.f, 0.f);
+                    }
                 }
                 __syncwarp();
             }
@@ -645,9 +657,9 @@ namespace pcl
             if (PREFETCH && !uni)
             {
                 // (step s sits at position (s + 1) & 3 of its group: step 0 uses buffer 1, step 1 buffer 0)
-                nk[PD == 2 ? K + k : k] = fetch_keys(st[k], 0);
+                nk[PD == 2 ? K + k : k] = fetch_keys(st[k], 0, jp);
                 if (PD == 2)
-                    nk[k] = fetch_keys(st[k], 1);
+                    nk[k] = fetch_keys(st[k], 1, jp);
             }
         }
 
@@ -685,7 +697,7 @@ namespace pcl
                 KeyPair ck[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
-                    ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s);
+                    ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s, jp);
                 if (WKEYS && UNI)
                 {
                     const float4* wk = wkeys + s * 6; // the same address for all lanes: broadcast reads
@@ -703,7 +715,7 @@ namespace pcl
                 {
 #pragma unroll
                     for (int k = 0; k < K; k++)
-                        nk[(PD == 2 ? (g & 1) * K : 0) + k] = fetch_keys(st[k], s + PD, opaque_zero(lo(sm[k].q.wx)));
+                        nk[(PD == 2 ? (g & 1) * K : 0) + k] = fetch_keys(st[k], s + PD, jp, opaque_zero(lo(sm[k].q.wx)));
                 }
                 TRSP loc;
                 if (K == 1)
@@ -946,14 +958,15 @@ namespace pcl
         // software pipeline over the warp's own rounds: keys one round ahead
         const int32_t* my = s_sched + warp;
         int            s_cur = my[0], s_nxt = par.n_rounds > 1 ? my[POSE_L_WARPS] : -1;
-        KeyPair        k_cur = fetch_keys(st, max(s_cur, 0));
+        const int      jp    = pose_jp(par.J);
+        KeyPair        k_cur = fetch_keys(st, max(s_cur, 0), jp);
         for (int r = 0; r <= par.n_rounds; r++)
         {
             const int     s = s_cur;
             const KeyPair k = k_cur;
             const int s_nn = r + 2 < par.n_rounds ? my[(r + 2) * POSE_L_WARPS] : -1;
             if (s_nxt >= 0)
-                k_cur = fetch_keys(st, s_nxt);
+                k_cur = fetch_keys(st, s_nxt, jp);
             s_cur = s_nxt, s_nxt = s_nn;
             if (s >= 0)
             {
