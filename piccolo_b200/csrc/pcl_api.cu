@@ -26,6 +26,7 @@ namespace
     struct SkelRec
     {
         int32_t              J = 0, pitch = 0, nslot = 0;
+        int32_t              split_base[2] = {0, 0}, split_n[2] = {0, 0}; // the two halves' step records in h_steps (pose_simple_kernel<SPLIT>); 0 = none
         std::vector<int32_t> index, parent, order;
         std::vector<StepRec> h_steps;       // host copy: source of the __constant__ upload
         int32_t              n_clips = 0, n_simple = 0;
@@ -105,7 +106,7 @@ struct pcl_ctx
     std::vector<MeshRec>  meshes;
     ClipRec*     d_clips = nullptr;
     int32_t      cap_clips = 0;
-    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0, opt_lbs_compact = -1, opt_pool_bulk = -1;
+    int32_t      opt_pose_wpb = 0, opt_pose_generic = 0, opt_lbs_variant = -1, opt_lbs_vsplit = 0, opt_lbs_inst_tile = 0, opt_lbs_warps = 0, opt_lbs_cta_tile = 0, opt_pose_sort = -1, opt_pose_min_blocks = 0, opt_pose_level = -1, opt_export_mode = 0, opt_lbs_compact = -1, opt_pool_bulk = -1, opt_pose_split = -1;
     void*        h_small = nullptr;  // pinned staging of small synchronous palette read-backs
     bool         debug_sync = false; // PICCOLO_B200_DEBUG_SYNC=1: synchronise after every launch
     int32_t      n_buckets = 0; // (clip, frame) buckets of all uploaded clips, see order_* kernels
@@ -121,6 +122,7 @@ struct pcl_batch
     int32_t   K;
     int32_t * d_clip_ids = nullptr, *d_mask_ids = nullptr;
     float *   d_phase = nullptr, *d_weight = nullptr, *d_len = nullptr;
+    float*    d_phase_alt = nullptr; // second phase array of the two-half pose form (allocated at its first advancing launch)
     float4*   d_palette = nullptr;
     float*    d_derived = nullptr;
     float4*   d_export  = nullptr;
@@ -659,6 +661,8 @@ extern "C"
             c->opt_pose_min_blocks = v;
         else if (k == "pose_level" && v >= -1 && v <= 1)
             c->opt_pose_level = v;
+        else if (k == "pose_split" && v >= -1 && v <= 1)
+            c->opt_pose_split = v;
         else if (k == "lbs_variant" && v >= -1 && v <= 3)
             c->opt_lbs_variant = v;
         else if (k == "lbs_warps" && (v == 0 || v == 8 || v == 12))
@@ -753,6 +757,59 @@ extern "C"
             r.ib0 = make_float4(m[0], m[1], m[2], m[3]);
             r.ib1 = make_float4(m[4], m[5], m[6], m[7]);
             r.ib2 = make_float4(m[8], m[9], m[10], m[11]);
+        }
+        // Two halves for small crowds (pose_simple_kernel<SPLIT>): cut at the bone that balances {its subtree + its ancestors}
+        // against {everything outside the subtree}; each half is an ancestor-closed bone list in processing order with a parking
+        // plan of its own.  Kept only when it shortens the walk by a quarter and all records fit the constant bank.
+        {
+            std::vector<int32_t> sub(J, 1), depth(J, 0);
+            for (int st = J - 1; st >= 0; st--)
+                if (s.parent[order[st]] >= 0)
+                    sub[s.parent[order[st]]] += sub[order[st]];
+            for (int st = 0; st < J; st++)
+                depth[order[st]] = s.parent[order[st]] < 0 ? 0 : depth[s.parent[order[st]]] + 1;
+            int cut = -1, cost = J;
+            for (int b = 0; b < J; b++)
+                if (s.parent[b] >= 0 && std::max(sub[b] + depth[b], J - sub[b]) < cost)
+                    cut = b, cost = std::max(sub[b] + depth[b], J - sub[b]);
+            if (cut >= 0 && J >= 16 && cost * 4 <= J * 3 && (size_t)J + (size_t)(sub[cut] + depth[cut]) + (size_t)(J - sub[cut]) + 2 * POSE_G <= (size_t)POSE_CMAX)
+            {
+                std::vector<char> in_sub(J, 0), anc(J, 0);
+                for (int b = s.parent[cut]; b >= 0; b = s.parent[b])
+                    anc[b] = 1;
+                for (int st = 0; st < J; st++)
+                {
+                    const int b = order[st];
+                    in_sub[b]   = b == cut || (s.parent[b] >= 0 && in_sub[s.parent[b]]);
+                }
+                int  nslot_h = nslot;
+                auto half    = [&](int which) {
+                    std::vector<int32_t> bones, local(J, -1), par_l, ord_l, ps, stv;
+                    for (int st = 0; st < J; st++)
+                    {
+                        const int b = order[st];
+                        if (which == 0 ? (in_sub[b] || anc[b]) : !in_sub[b])
+                            local[b] = (int32_t)bones.size(), bones.push_back(b);
+                    }
+                    for (size_t i = 0; i < bones.size(); i++)
+                        par_l.push_back(s.parent[bones[i]] < 0 ? -1 : local[s.parent[bones[i]]]), ord_l.push_back((int32_t)i);
+                    nslot_h             = std::max(nslot_h, plan_slots(par_l, ord_l, &ps, &stv));
+                    s.split_base[which] = (int32_t)steps.size(), s.split_n[which] = (int32_t)bones.size();
+                    for (size_t i = 0; i < bones.size(); i++)
+                    {
+                        StepRec r = steps[step_of[bones[i]]];
+                        r.psrc = ps[i], r.store = stv[i], r.pstep = step_of[bones[i]];
+                        steps.push_back(r);
+                    }
+                    for (int i = 0; i < POSE_G; i++) // the key prefetch runs up to two steps past the end of a whole group
+                        steps.push_back(steps.back());
+                };
+                half(0), half(1);
+                if ((size_t)pose_smem_floats_per_warp(nslot_h) * 4 > (size_t)c->max_smem_optin)
+                    steps.resize(J), s.split_n[0] = s.split_n[1] = 0;
+                else
+                    s.nslot = nslot = nslot_h;
+            }
         }
         int rc = upload(c, &s.d_steps, steps);
         if (rc != PCL_OK)
@@ -1188,7 +1245,7 @@ extern "C"
         if (e != cudaSuccess) // a crowd too big for the GPU must leave nothing behind
         {
             (void)cudaGetLastError();
-            cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len), cudaFree(b->d_palette);
+            cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_phase_alt), cudaFree(b->d_weight), cudaFree(b->d_len), cudaFree(b->d_palette);
             delete b;
             return fail(c, e == cudaErrorMemoryAllocation ? PCL_ERR_OOM : PCL_ERR_CUDA, std::string("pcl_batch_create: ") + cudaGetErrorString(e));
         }
@@ -1204,7 +1261,7 @@ extern "C"
         cudaSetDevice(b->ctx->device);
         b->ctx->skels[b->skel].users--;
         cudaStreamSynchronize(b->ctx->compute), cudaStreamSynchronize(b->ctx->copy);
-        cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_weight), cudaFree(b->d_len);
+        cudaFree(b->d_clip_ids), cudaFree(b->d_mask_ids), cudaFree(b->d_phase), cudaFree(b->d_phase_alt), cudaFree(b->d_weight), cudaFree(b->d_len);
         if (b->pool)
             b->pool->attached--;
         else
@@ -1527,6 +1584,7 @@ extern "C"
         p.palette = b->d_palette, p.derived = b->d_derived;
         p.N = b->N, p.J = s.J, p.pitch = s.pitch, p.nslot = s.nslot;
         p.n_steps_padded = (s.J + POSE_G - 1) / POSE_G * POSE_G;
+        p.split_base[0] = s.split_base[0], p.split_base[1] = s.split_base[1], p.split_n[0] = s.split_n[0], p.split_n[1] = s.split_n[1];
         p.dt = dt, p.advance = advance;
         const long long warps = (b->N + 31) / 32;
         const size_t    per_warp = pose_smem_floats_per_warp(s.nslot) * 4;
@@ -1594,7 +1652,10 @@ extern "C"
         {
             const size_t smem_l = pose_l_smem_bytes(s.J, s.n_rounds);
             const bool   fits_l = simple && b->K == 1 && !sorted && s.d_sched && smem_l <= (size_t)c->max_smem_optin;
-            const bool   small  = warps <= 2LL * c->sm_count; // measured: 20.7 us against 31-33 us up to 4 000 player instances, 29 against 32 at 8 000, level at 10 000
+            // measured (one clip, player skeleton): 14.6 us against 27-29 us (lane kernel) / 20.5 us (its two-half form) up to 4 000
+            // instances = one CTA per SM; 8 000: 24.8 against 27.0 / 21.8 - so beyond one wave only where there is no two-half form
+            const bool   has_split = s.split_n[0] > 0 && c->opt_pose_split != 0 && !p.derived && !remote;
+            const bool   small     = warps <= (has_split ? 1LL : 2LL) * c->sm_count;
             if (fits_l && (c->opt_pose_level == 1 || (c->opt_pose_level < 0 && (small || io))))
             {
                 p.sched = s.d_sched, p.n_rounds = s.n_rounds;
@@ -1611,6 +1672,25 @@ extern "C"
         }
         // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM.  (Round 1 preferred 3 blocks for two-clip crowds
         // beyond ~300 k instances; with the packed, straight-line groups the 168-register form spills: 1.98 against 1.86 ms at 1 M.)
+        // one-clip crowds too large for the level kernel, too small to give every scheduler two warps: two warps per 32 instances,
+        // half a skeleton each (pose_simple_kernel<SPLIT>); measured with tools/pose_bench.py --clips 1: 8 000 instances 27.0 -> 21.8 us
+        // (level kernel 24.8), 10 000: 28.8 -> 24.8, 16 000: 29.9 -> 25.0, 20 000 (more warps than the SMs hold at once): 33 -> 40
+        if (simple && b->K == 1 && !sorted && !io && !p.derived && !remote && s.split_n[0] > 0 &&
+            (c->opt_pose_split == 1 || (c->opt_pose_split < 0 && warps * 2 <= 8LL * c->sm_count)))
+        {
+            if (advance != 0 && !b->d_phase_alt)
+                PCL_CK(c, cudaMalloc((void**)&b->d_phase_alt, (size_t)b->N * 4));
+            p.phase_out = b->d_phase_alt;
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<1, false, 2, false, false, true>, smem); if (rc__) return rc__; }
+            pose_simple_kernel<1, false, 2, false, false, true><<<dim3(grid, 2), wpb * 32, smem, c->compute>>>(p);
+            if (advance != 0)
+                std::swap(b->d_phase, b->d_phase_alt); // both halves read the old phases; the first one wrote the new ones here
+            c->launches++;
+            PCL_POST_LAUNCH(c, c->compute, "pose_simple_kernel<split>");
+            PCL_CK(c, cudaEventRecord(c->ev_pose, c->compute));
+            b->posed = true;
+            return PCL_OK;
+        }
         int mb = c->opt_pose_min_blocks;
         if (mb == 0 || b->K > 2)
             mb = 2;

@@ -24,7 +24,8 @@ namespace pcl
         int32_t joint; // bone position in bones_map; palette slot = joint + 1
         int32_t psrc;  // parent's derived TRS: -1 root, -2 result of the previous step (still in registers), >= 0 smem slot
         int32_t store; // smem slot to keep this bone's derived TRS in for later children, or -1
-        int32_t pstep; // processing step of the parent (-1 root): pose_level_kernel's parent lookup
+        int32_t pstep; // processing step of the parent (-1 root): pose_level_kernel's parent lookup.  In the records of a
+                       // half (pose_simple_kernel<SPLIT>): this bone's step in the WHOLE skeleton = its row in the key tables
         // bind TRS (Node::m_initial_*) laid out for the packed arithmetic of pcl_math.cuh:
         float4  bA;    // (p.x, p.y, s.x, s.y)
         float4  bC;    // (1, s.z, p.z, 0): local (p.z, s.z) = sampled (p.z, s.z) * (1, s.z) + (p.z, 0) in one packed fma
@@ -75,6 +76,8 @@ namespace pcl
         const int32_t* order;    // [N] visiting order (frame-coherent, see order_* kernels) or nullptr = 0, 1, 2, ...
         long long      N;
         int32_t        J, pitch, nslot, n_steps_padded, n_rounds;
+        int32_t        split_base[2], split_n[2]; // pose_simple_kernel<SPLIT>: where each half's step records start in c_steps, how many
+        float*         phase_out;                 // pose_simple_kernel<SPLIT> with a phase advance: where the advanced phases go
         float          dt;
         int32_t        advance; // 0, PCL_ADVANCE_FIRST_ONLY, PCL_ADVANCE_ALL
     };
@@ -389,10 +392,11 @@ namespace pcl
     {
         // a clip's step-ordered copy is far below 2^32 units
         const uint32_t ia = (uint32_t)s * st.F + (uint32_t)after, iq = (uint32_t)(s + jp) * st.F + (uint32_t)after;
-        const float2*  kc = reinterpret_cast<const float2*>(st.keys) + ((uint32_t)(s + 4 * jp) * st.F + (uint32_t)after);
+        const uint32_t ic = (uint32_t)(s + 4 * jp) * st.F + (uint32_t)after; // (32-bit sums first: one IMAD.WIDE per address)
+        const float2*  kc = reinterpret_cast<const float2*>(st.keys);
         KeyPair        k;
-        k.a0 = __ldg(st.keys + (ia + st.lo)), k.q0 = __ldg(st.keys + (iq + st.lo)), k.c0 = __ldg(kc + st.lo);
-        k.a1 = __ldg(st.keys + (ia + st.hi)), k.q1 = __ldg(st.keys + (iq + st.hi)), k.c1 = __ldg(kc + st.hi);
+        k.a0 = __ldg(st.keys + (ia + st.lo)), k.q0 = __ldg(st.keys + (iq + st.lo)), k.c0 = __ldg(kc + (ic + st.lo));
+        k.a1 = __ldg(st.keys + (ia + st.hi)), k.q1 = __ldg(st.keys + (iq + st.hi)), k.c1 = __ldg(kc + (ic + st.hi));
         return k;
     }
     // (Tried and rejected: staging the keys with cp.async - LDGSTS, one 80-byte shared-memory cell per lane and clip, four bones
@@ -530,9 +534,17 @@ namespace pcl
     // form carries no branch for it.  A group of POSE_G bones is ONE straight-line block there (no bounds checks in whole groups,
     // parent fetch and parking predicated instead of branched): ptxas may then run bone s + 1's sampling and local pose - which do
     // not depend on the hierarchy - inside bone s's composition chain.
-    template<int K, bool SORTED, int MB, bool DER, bool BULK = false>
+    // SPLIT (small one-clip crowds, where a warp is alone on its scheduler and the 58-step walk IS the run time): the skeleton
+    // is cut at one bone into two halves - the cut bone's subtree plus its ancestors, and everything outside the subtree - and
+    // two warps (blockIdx.y) take one half each of the same 32 instances.  The shared ancestors are computed by both, from the
+    // same inputs with the same instructions, so the rows both write are bit-identical.  Each half has its own step records
+    // (parking plan of its own, upload time); the key tables stay those of the whole skeleton (StepRec::pstep = the row).
+    template<int K, bool SORTED, int MB, bool DER, bool BULK = false, bool SPLIT = false>
     __global__ void __launch_bounds__(POSE_S_THREADS, MB) pose_simple_kernel(const PoseParams par)
     {
+        static_assert(!SPLIT || (K == 1 && !SORTED && !DER && !BULK), "the two-half form exists for plain one-clip crowds");
+        const int sbase = SPLIT ? par.split_base[blockIdx.y] : 0;  // first step record of this warp's list
+        const int nst   = SPLIT ? par.split_n[blockIdx.y] : par.J; // steps this warp walks
         extern __shared__ __align__(16) float smem[];
         const int       lane  = threadIdx.x & 31;
         const int       wib   = threadIdx.x >> 5;
@@ -547,10 +559,11 @@ namespace pcl
                 dst[i] = __ldg(src + i);
             __syncthreads();
         }
-#define PCL_STEP(s_) s_steps[s_]
+#define PCL_STEP(s_) s_steps[sbase + (s_)]
 #else
-#define PCL_STEP(s_) c_steps[s_]
+#define PCL_STEP(s_) c_steps[sbase + (s_)]
 #endif
+#define PCL_KROW(s_) (SPLIT ? PCL_STEP(s_).pstep : (s_)) /* the step's row in the key tables */
         if (inst0 >= par.N)
             return;
         const bool      active = (inst0 + lane) < par.N;
@@ -576,8 +589,9 @@ namespace pcl
             {
                 ph += par.dt / __ldg(par.clip_len + o); // animation_component.cpp:19-21
                 ph -= floorf(ph);
-                if (active)
-                    par.phase[o] = ph;
+                // (SPLIT: both halves read the old phase, so the new one goes to a second array; the host swaps the two)
+                if (active && (!SPLIT || blockIdx.y == 0))
+                    (SPLIT ? par.phase_out : par.phase)[o] = ph;
             }
             slot_frames(st[k], ph, cr.total_frame_m1, cr.F);
             st[k].keys = cr.keys_step, st[k].anim = cr.anim_step;
@@ -657,9 +671,9 @@ namespace pcl
             if (PREFETCH && !uni)
             {
                 // (step s sits at position (s + 1) & 3 of its group: step 0 uses buffer 1, step 1 buffer 0)
-                nk[PD == 2 ? K + k : k] = fetch_keys(st[k], 0, jp);
+                nk[PD == 2 ? K + k : k] = fetch_keys(st[k], PCL_KROW(0), jp);
                 if (PD == 2)
-                    nk[k] = fetch_keys(st[k], 1, jp);
+                    nk[k] = fetch_keys(st[k], PCL_KROW(1), jp);
             }
         }
 
@@ -683,7 +697,7 @@ namespace pcl
                     row[0] = make_float4(1, 0, 0, 0), row[1] = make_float4(0, 1, 0, 0), row[2] = make_float4(0, 0, 1, 0);
                     continue;
                 }
-                if (!FULL && s >= par.J)
+                if (!FULL && s >= nst)
                     break;
                 if (K > 1 && g == 1 && ((s0 + 1) & 31) == 0) // (step s0 itself is the last bit of the previous word)
                 {
@@ -697,7 +711,7 @@ namespace pcl
                 KeyPair ck[K];
 #pragma unroll
                 for (int k = 0; k < K; k++)
-                    ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], s, jp);
+                    ck[k] = PREFETCH ? nk[(PD == 2 ? (g & 1) * K : 0) + k] : fetch_keys(st[k], PCL_KROW(s), jp);
                 if (WKEYS && UNI)
                 {
                     const float4* wk = wkeys + s * 6; // the same address for all lanes: broadcast reads
@@ -711,11 +725,11 @@ namespace pcl
                 for (int k = 0; k < K; k++)
                     sm[k] = sample_keys(ck[k], st[k].r);
                 // ... then the next bone's keys are requested; they land while the rest of this bone is computed
-                if (PREFETCH && !UNI && (FULL || s + PD < par.J)) // (whole groups: the key tracks are padded by a group, §2)
+                if (PREFETCH && !UNI && (FULL || s + PD < nst)) // (whole groups: the key tracks are padded by a group, §2)
                 {
 #pragma unroll
                     for (int k = 0; k < K; k++)
-                        nk[(PD == 2 ? (g & 1) * K : 0) + k] = fetch_keys(st[k], s + PD, jp, opaque_zero(lo(sm[k].q.wx)));
+                        nk[(PD == 2 ? (g & 1) * K : 0) + k] = fetch_keys(st[k], PCL_KROW(s + PD), jp, opaque_zero(lo(sm[k].q.wx)));
                 }
                 TRSP loc;
                 if (K == 1)
@@ -832,7 +846,7 @@ namespace pcl
                     const int g  = rm / 3;
                     const int s  = s0 + g;
                     const size_t irow = SORTED ? (size_t)__shfl_sync(0xffffffffu, inst32, il & 31) : (size_t)(inst0 + il);
-                    if (s < par.J && il < ni)
+                    if (s < nst && il < ni)
                         par.palette[(irow * par.pitch + (s < 0 ? 0 : PCL_STEP(s).joint + 1)) * 3 + (rm - g * 3)] =
                             *reinterpret_cast<const float4*>(stage + (size_t)il * SROW + rm * 4);
                 }
@@ -842,16 +856,16 @@ namespace pcl
         int s0 = -1; // (the identity slot takes the first place of the first group)
         if (WKEYS && uni)
         {
-            for (; s0 + POSE_G <= par.J; s0 += POSE_G)
+            for (; s0 + POSE_G <= nst; s0 += POSE_G)
                 group(s0, std::true_type {}, std::true_type {});
-            if (s0 < par.J)
+            if (s0 < nst)
                 group(s0, std::false_type {}, std::true_type {});
         }
         else
         {
-            for (; s0 + POSE_G <= par.J; s0 += POSE_G)
+            for (; s0 + POSE_G <= nst; s0 += POSE_G)
                 group(s0, std::true_type {}, std::false_type {});
-            if (s0 < par.J)
+            if (s0 < nst)
                 group(s0, std::false_type {}, std::false_type {});
         }
         if (BULK)

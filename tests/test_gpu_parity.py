@@ -399,6 +399,52 @@ def test_level_parallel_pose_kernel_matches_the_lane_kernels(ctx, player, oracle
         assert_mats_close(out[1][0], ref)
 
 
+@pytest.mark.parametrize("shape", ["player", "bushy200", "star", "chain"])
+def test_two_half_pose_form_is_bit_identical_to_the_whole_walk(ctx, player, oracle, shape):
+    """pose_split: two warps per 32 instances, one half of the skeleton each (the cut bone's subtree + its ancestors | the rest).
+    Same instantiation of the same device functions, same inputs per bone: every palette row - the ancestors' rows, written by
+    both halves, included - equals the whole-skeleton walk's to the bit, on whole and ragged tiles; and the oracle's within the
+    gate.  A star (all bones children of the root) and a chain have no balanced cut: the option is then ignored."""
+    if shape == "player":
+        sk, cl, am, _ = player
+    else:
+        J, br = {"chain": (40, 1), "star": (90, 89), "bushy200": (200, 3)}[shape]
+        sk = A.make_synthetic_skeleton(J, branching=br, seed=11)
+        cl, am = A.make_synthetic_clip(sk, 13, seed=12)
+    skel = ctx.upload_skeleton(sk)
+    clip = ctx.upload_clip(skel, cl, am)
+    from piccolo_b200 import capi
+    for N in (1, 33, 500, 10000):
+        ph = np.random.default_rng(N).uniform(0, 1, N).astype(np.float32)
+        ln = np.random.default_rng(N + 1).uniform(0.5, 2.0, N).astype(np.float32)
+        out = {}
+        ctx.set_option("pose_level", 0)
+        try:
+            for mode in (0, 1):
+                ctx.set_option("pose_split", mode)
+                b = ctx.batch(skel, N, 1)
+                b.set(clip_ids=np.full((N, 1), clip, np.int32), phase=ph, clip_len=ln)
+                b.pose()
+                r = [b.download_palette()]
+                # ticks: both halves read the old phases, the advanced ones land in a second array the host swaps in
+                b.tick(1.0 / 30.0, capi.PCL_ADVANCE_FIRST_ONLY)
+                b.tick(0.0421, capi.PCL_ADVANCE_ALL)
+                r += [b.download_palette(), b.phases()]
+                b.tick(0.0, capi.PCL_ADVANCE_ALL)
+                r += [b.download_palette(), b.phases()]
+                out[mode] = r
+                b.close()
+        finally:
+            ctx.set_option("pose_level", -1), ctx.set_option("pose_split", -1)
+        for x, y in zip(out[0], out[1]):
+            assert np.array_equal(x, y)
+        assert np.array_equal(out[1][2], out[1][4]) and np.array_equal(out[1][1], out[1][3])  # dt = 0 keeps phases and pose
+        ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((N, 1), np.int32), ph)
+        assert_mats_close(out[1][0], ref)
+        ref2 = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(cl, am)], np.zeros((N, 1), np.int32), out[1][2])
+        assert_mats_close(out[1][1], ref2)
+
+
 def test_two_contexts_on_one_device_share_kernel_attributes(ctx, player_dev, player):
     """The opt-in shared-memory size is a property of (device, kernel), not of a context: a second context that needs less
     must not shrink what the first one launches with (regression: 'invalid argument' on the first context's next pose)."""

@@ -15,6 +15,7 @@ ap.add_argument("--wpb", type=int, default=0)
 ap.add_argument("--pose-sort", type=int, default=-1, help="-1 auto, 0 off, 1 on: frame-coherent visiting order")
 ap.add_argument("--min-blocks", type=int, default=0)
 ap.add_argument("--level", type=int, default=-1, help="-1 auto, 0 off, 1 on: level-parallel kernel for small crowds")
+ap.add_argument("--split", type=int, default=-1, help="-1 auto, 0 off, 1 on: two warps per 32 instances, half a skeleton each")
 ap.add_argument("--sorted", type=int, default=0, help="1: instances grouped by clip id (what a crowd manager would do)")
 args = ap.parse_args()
 sk, cl, am, mk = A.load_player()
@@ -25,6 +26,7 @@ ctx.set_option("pose_warps_per_block", args.wpb)
 ctx.set_option("pose_sort", args.pose_sort)
 ctx.set_option("pose_min_blocks", args.min_blocks)
 ctx.set_option("pose_level", args.level)
+ctx.set_option("pose_split", args.split)
 skel = ctx.upload_skeleton(sk)
 ids = np.asarray([ctx.upload_clip(skel, c, am) for c in clips], np.int32)
 peak = 6540.2
