@@ -1696,8 +1696,16 @@ extern "C"
             mb = 2;
 #define PCL_LAUNCH_POSE_SD(KK, SS, MM, DD)                                                                                  \
     {                                                                                                                       \
-        { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, SS, MM, DD>, smem); if (rc__) return rc__; }        \
-        pose_simple_kernel<KK, SS, MM, DD><<<grid, wpb * 32, smem, c->compute>>>(p);                                        \
+        if (KK == 2 && MM == 2 && !DD && !p.mask_ids) /* two clips, no bone masks: blend weights hoisted out of the walk */  \
+        {                                                                                                                   \
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<2, SS, 2, false, false, false, false>, smem); if (rc__) return rc__; } \
+            pose_simple_kernel<2, SS, 2, false, false, false, false><<<grid, wpb * 32, smem, c->compute>>>(p);              \
+        }                                                                                                                   \
+        else                                                                                                                \
+        {                                                                                                                   \
+            { int rc__ = ensure_smem(c, (const void*)pose_simple_kernel<KK, SS, MM, DD>, smem); if (rc__) return rc__; }    \
+            pose_simple_kernel<KK, SS, MM, DD><<<grid, wpb * 32, smem, c->compute>>>(p);                                    \
+        }                                                                                                                   \
     }
 #define PCL_LAUNCH_POSE_S(KK, SS, MM)                                                                                       \
     {                                                                                                                       \

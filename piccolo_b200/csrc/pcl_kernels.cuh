@@ -539,7 +539,10 @@ namespace pcl
     // two warps (blockIdx.y) take one half each of the same 32 instances.  The shared ancestors are computed by both, from the
     // same inputs with the same instructions, so the rows both write are bit-identical.  Each half has its own step records
     // (parking plan of its own, upload time); the key tables stay those of the whole skeleton (StepRec::pstep = the row).
-    template<int K, bool SORTED, int MB, bool DER, bool BULK = false, bool SPLIT = false>
+    // MASKS = false (no bone mask uploaded for the skeleton: par.mask_ids == nullptr): every clip contributes to every bone, so
+    // the normalised blend weights (animation_system.cpp:117-149) are the same for all bones of an instance - computed once,
+    // before the walk, by the same expression; with masks they depend on the bone and are computed per bone.
+    template<int K, bool SORTED, int MB, bool DER, bool BULK = false, bool SPLIT = false, bool MASKS = true>
     __global__ void __launch_bounds__(POSE_S_THREADS, MB) pose_simple_kernel(const PoseParams par)
     {
         static_assert(!SPLIT || (K == 1 && !SORTED && !DER && !BULK), "the two-half form exists for plain one-clip crowds");
@@ -598,6 +601,21 @@ namespace pcl
             st[k].w = (K > 1) ? __ldg(par.weight + o) : 1.0f;
             const int mid = (K > 1 && par.mask_ids) ? __ldg(par.mask_ids + o) : -1;
             st[k].mask_off = mid < 0 ? -1 : mid * par.J;
+        }
+        float we0[K]; // MASKS = false: each clip's effective weight, for every bone
+        if (K > 1 && !MASKS)
+        {
+            float wsum = 0.f;
+#pragma unroll
+            for (int k = 0; k < K; k++)
+                wsum += st[k].w;
+            const bool live = fabsf(wsum) >= 0.0001f;
+#pragma unroll
+            for (int k = 0; k < K; k++)
+            {
+                const float wn = PCL_EXACT_NORMALISE ? st[k].w / wsum : fdiv_nobranch(st[k].w, wsum);
+                we0[k]         = (live && wn != 0.f) ? wn : 0.f;
+            }
         }
         // (slot 0 = identity, mesh_component.cpp:72-79: it leaves with the first group's flush, see `group` below)
         const int jp = pose_jp(par.J); // rows per key table (fetch_keys)
@@ -745,8 +763,8 @@ namespace pcl
 #pragma unroll
                     for (int k = 0; k < K; k++)
                     {
-                        en[k] = st[k].mask_off < 0 ? true : (__ldg(par.masks + st[k].mask_off + bone) != 0);
-                        if (en[k])
+                        en[k] = (!MASKS || st[k].mask_off < 0) ? true : (__ldg(par.masks + st[k].mask_off + bone) != 0);
+                        if (MASKS && en[k])
                             wsum += st[k].w;
                         touched |= ((amask[k] >> (s & 31)) & 1u) != 0;
                     }
@@ -759,10 +777,16 @@ namespace pcl
 #pragma unroll
                     for (int k = 0; k < K; k++)
                     {
-                        const float wn = en[k] ? (PCL_EXACT_NORMALISE ? st[k].w / wsum : fdiv_nobranch(st[k].w, wsum)) : 0.f; // animation_system.cpp:117-149
                         // (an identity track samples to the identity delta, exactly)
-                        const bool  ok = live && wn != 0.f;
-                        const float we = ok ? wn : 0.f;
+                        bool  ok;
+                        float we;
+                        if (MASKS)
+                        {
+                            const float wn = en[k] ? (PCL_EXACT_NORMALISE ? st[k].w / wsum : fdiv_nobranch(st[k].w, wsum)) : 0.f; // animation_system.cpp:117-149
+                            ok = live && wn != 0.f, we = ok ? wn : 0.f;
+                        }
+                        else
+                            we = we0[k], ok = we != 0.f;
                         const float sg = (any && qdotp(sm[k].q, qref) < 0.0f) ? -we : we;
                         accA = fma2p(sm[k].pxy, bc(we), accA), accB = fma2p(sm[k].sxy, bc(we), accB), accC = fma2p(sm[k].pzsz, bc(we), accC);
                         accq = QuatP {fma2p(sm[k].q.wx, bc(sg), accq.wx), fma2p(sm[k].q.yz, bc(sg), accq.yz)};
