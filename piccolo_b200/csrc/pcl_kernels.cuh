@@ -535,7 +535,7 @@ namespace pcl
     // parent fetch and parking predicated instead of branched): ptxas may then run bone s + 1's sampling and local pose - which do
     // not depend on the hierarchy - inside bone s's composition chain.
     // SPLIT (small one-clip crowds, where a warp is alone on its scheduler and the 58-step walk IS the run time): the skeleton
-    // is cut at one bone into two halves - the cut bone's subtree plus its ancestors, and everything outside the subtree - and
+    // is cut into two halves - a set of whole subtrees plus their ancestors, and everything outside those subtrees - and
     // two warps (blockIdx.y) take one half each of the same 32 instances.  The shared ancestors are computed by both, from the
     // same inputs with the same instructions, so the rows both write are bit-identical.  Each half has its own step records
     // (parking plan of its own, upload time); the key tables stay those of the whole skeleton (StepRec::pstep = the row).
