@@ -285,7 +285,10 @@ int pcl_batch_push_to_pool(pcl_batch* b, pcl_pool* pool, int64_t first);
  * the step-ordered kernel visit the instances grouped by the (clip, frame) bucket of their phase - same results, coherent
  * key loads; three extra small launches per pose); "pose_min_blocks" (0 = auto, 2, 3, 4: resident blocks per SM the step-ordered
  * kernel's registers are allocated for - 255 / 168 / 128 registers per thread); "pose_level" (-1 = auto: one-clip crowds small
- * enough to leave SMs idle, 0 = never, 1 = always when applicable: the level-parallel pose kernel, 8 warps per 32 instances); "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with
+ * enough to leave SMs idle, 0 = never, 1 = always when applicable: the level-parallel pose kernel, 8 warps per 32 instances);
+ * "pose_split" (-1 = auto: one-clip crowds beyond the level kernel's range that leave the SMs fewer than 8 warps each, 0 = never,
+ * 1 = always when the skeleton has a balanced cut: two warps per 32 instances walk one half of the skeleton each; same bits);
+ * "lbs_variant" (-1 = auto; 0 = lane-per-vertex kernel with
  * coalesced 128-bit stores, 1 = same with TMA bulk stores, 2 = lane-per-instance crowd kernel, 3 = crowd kernel with a
  * warp-specialised TMA store pipeline);
  * "lbs_warps" (0 = auto, 8, 12: resident warps per SM of the crowd kernel); "lbs_vsplit" (0 = auto);
