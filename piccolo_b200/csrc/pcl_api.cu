@@ -1657,8 +1657,11 @@ extern "C"
         // 69 GB/s against 350 GB/s in instance order, tools/pool_gather_check.py on two B200s)
         const bool remote = b->pool && (!b->pool->owner || b->pool->ctx->device != c->device);
         const bool bulk_remote = remote && c->opt_pool_bulk != 0; // palettes in another GPU's memory leave as bulk copies (pose_simple_kernel, BULK)
+        // (threshold re-measured on the final kernels: one clip per instance 60 k / 80 k / 100 k / 125 k / 200 k instances: +8 / -3 / -2 /
+        // -10 / -11 % with the order; two clips: +2 / +2 / -2 % at 100 k / 150 k / 200 k)
+        const long long sort_from = b->K == 1 ? 112 * 1024 : 262144;
         bool sorted = simple && !io && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
-                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= 262144 && !remote));
+                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= sort_from && !remote));
         if (sorted)
         {
             if (!b->d_order)

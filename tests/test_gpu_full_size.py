@@ -65,6 +65,30 @@ def test_config4_one_million_mixed_clips_auto_sorted_vs_oracle(ctx, oracle, play
         b.close()
 
 
+def test_config4_one_shard_of_eight_auto_sorted_vs_oracle(ctx, oracle, player):
+    """configs[3] as one of eight ranks sees it: instances [375 000, 500 000) of the 1 M crowd.  With one clip per instance the
+    launcher turns the frame-coherent order on from 114 688 instances: 4 launches, 2 048 sampled instances against the oracle."""
+    sk, cl, am, mk = player
+    clips = W.config4_clips(cl)
+    skel = ctx.upload_skeleton(sk)
+    ids = np.int32([ctx.upload_clip(skel, c, am) for c in clips])
+    first, N = 375000, 125000
+    pick, phase = W.config4_inputs(first, N)
+    b = ctx.batch(skel, N, 1)
+    try:
+        b.set(clip_ids=ids[pick], phase=phase)
+        l0 = ctx.launch_count()
+        b.pose()
+        assert ctx.launch_count() - l0 == 4, "expected the three order_* launches + pose at 125 000 one-clip instances on auto"
+        ranges = W.sample_ranges(N, 32, 64, seed=9)
+        got = _download_ranges(b, ranges)
+        sel = np.concatenate([np.arange(f, f + n) for f, n in ranges])
+        ref = oracle.pose_batch(oracle.skeleton(sk), [oracle.clip(c, am) for c in clips], pick[sel], phase[sel])
+        assert_mats_close(got, ref)
+    finally:
+        b.close()
+
+
 def test_two_clip_blend_at_320k_auto_launch_shape_vs_oracle(ctx, oracle, player):
     """K = 2 beyond 300 000 instances: the launcher sorts on the (bucket of clip 0, bucket of clip 1) pair and takes the
     3-blocks-per-SM register allocation.  config 3's inputs, 4 096 sampled instances against the oracle (A4 blend extension:
