@@ -451,10 +451,12 @@ def run_ours(args):
     for _ in range(args.steps):
         skin_all()
     lbs_ms = ctx.timer_end() / (args.steps * len(chunks))
+    lp = ctx.launch_count()
     ctx.timer_begin()
     for _ in range(args.steps):
         b.pose()
     pose_ms = ctx.timer_end() / args.steps
+    pose_launches = (ctx.launch_count() - lp) // args.steps  # 4 = the three order_* launches of the frame-coherent order + the pose kernel
     clk.__exit__()
     clocks = clk.summary()
     peak, peak_src = measured_hbm_peak()
@@ -465,7 +467,7 @@ def run_ours(args):
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(per_launch), "launch_ms": round(lbs_ms, 4),
                 "frac_of_nominal_8000": round(achieved / 8000.0, 4),
-                "pose_kernel": {"launch_ms": round(pose_ms, 4), "achieved": round(pose_bytes / (pose_ms * 1e-3) / 1e9, 1),
+                "pose_kernel": {"launch_ms": round(pose_ms, 4), "launches": int(pose_launches), "achieved": round(pose_bytes / (pose_ms * 1e-3) / 1e9, 1),
                                 "frac": round(pose_bytes / (pose_ms * 1e-3) / 1e9 / peak, 4),
                                 "joints_per_s": round(N * sk.J / (pose_ms * 1e-3), 0)}}
 

@@ -1657,9 +1657,10 @@ extern "C"
         // 69 GB/s against 350 GB/s in instance order, tools/pool_gather_check.py on two B200s)
         const bool remote = b->pool && (!b->pool->owner || b->pool->ctx->device != c->device);
         const bool bulk_remote = remote && c->opt_pool_bulk != 0; // palettes in another GPU's memory leave as bulk copies (pose_simple_kernel, BULK)
-        // (threshold re-measured on the final kernels: one clip per instance 60 k / 80 k / 100 k / 125 k / 200 k instances: +8 / -3 / -2 /
-        // -10 / -11 % with the order; two clips: +2 / +2 / -2 % at 100 k / 150 k / 200 k)
-        const long long sort_from = b->K == 1 ? 112 * 1024 : 262144;
+        // (thresholds re-measured on the final kernels, order_* launches with 2 048 items per block: one clip per instance 30 k / 40 k /
+        // 60 k / 80 k / 100 k instances: +35 / 0 / -7 / -13 / -13 % with the order; two clips, 100 k / 150 k / 200 k: -6 / -4 / -5 %
+        // with 8 mixed clips, -3.5 % at 100 k when all instances blend the same two; three and four clips: not re-measured)
+        const long long sort_from = b->K == 1 ? 48 * 1024 : b->K == 2 ? 96 * 1024 : 262144;
         bool sorted = simple && !io && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
                       (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= sort_from && !remote));
         if (sorted)

@@ -1029,7 +1029,14 @@ namespace pcl
     // -------------------------------------------------------------------------------------------
     constexpr int ORDER_MAX_BUCKETS = 8192; // 32 KB of shared-memory counters per block
     constexpr int ORDER_THREADS     = 512;
-    constexpr int ORDER_PER_THREAD  = 16;
+    // items per thread: 2 048 per block.  Measured (tools/pose_bench.py, one clip, order + pose): 16 / 8 / 4 / 2 per thread:
+    // 125 k instances 0.153 / 0.143 / 0.139 / 0.136 ms, 1 M 0.934 / 0.923 / 0.927 / 0.926 - with 16 a 1 M crowd is 123 blocks,
+    // fewer than SMs, each thread walking a chain of dependent loads per item; 4 keeps the per-block tables of the two-clip
+    // form (up to 8 192 pair buckets) a fraction of the block's work
+#ifndef PCL_ORDER_PER_THREAD
+#define PCL_ORDER_PER_THREAD 4
+#endif
+    constexpr int ORDER_PER_THREAD  = PCL_ORDER_PER_THREAD;
     struct OrderParams
     {
         const ClipRec* clips;

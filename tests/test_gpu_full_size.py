@@ -67,7 +67,7 @@ def test_config4_one_million_mixed_clips_auto_sorted_vs_oracle(ctx, oracle, play
 
 def test_config4_one_shard_of_eight_auto_sorted_vs_oracle(ctx, oracle, player):
     """configs[3] as one of eight ranks sees it: instances [375 000, 500 000) of the 1 M crowd.  With one clip per instance the
-    launcher turns the frame-coherent order on from 114 688 instances: 4 launches, 2 048 sampled instances against the oracle."""
+    launcher turns the frame-coherent order on from 49 152 instances: 4 launches, 2 048 sampled instances against the oracle."""
     sk, cl, am, mk = player
     clips = W.config4_clips(cl)
     skel = ctx.upload_skeleton(sk)
