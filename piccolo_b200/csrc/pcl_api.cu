@@ -1659,8 +1659,10 @@ extern "C"
         const bool bulk_remote = remote && c->opt_pool_bulk != 0; // palettes in another GPU's memory leave as bulk copies (pose_simple_kernel, BULK)
         // (thresholds re-measured on the final kernels, order_* launches with 2 048 items per block: one clip per instance 30 k / 40 k /
         // 60 k / 80 k / 100 k instances: +35 / 0 / -7 / -13 / -13 % with the order; two clips, 100 k / 150 k / 200 k: -6 / -4 / -5 %
-        // with 8 mixed clips, -3.5 % at 100 k when all instances blend the same two; three and four clips: not re-measured)
-        const long long sort_from = b->K == 1 ? 48 * 1024 : b->K == 2 ? 96 * 1024 : 262144;
+        // with 8 mixed clips; when all instances blend the same two clips - bench.py's crowd - the unsorted gathers already fall
+        // into three or four lines per load and the order buys -3.5 % alone, +1.5 % inside the bench's step: two clips from 128 k;
+        // three and four clips: not re-measured)
+        const long long sort_from = b->K == 1 ? 48 * 1024 : b->K == 2 ? 128 * 1024 : 262144;
         bool sorted = simple && !io && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
                       (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= sort_from && !remote));
         if (sorted)
