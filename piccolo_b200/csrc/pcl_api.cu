@@ -1663,8 +1663,15 @@ extern "C"
         // into three or four lines per load and the order buys -3.5 % alone, +1.5 % inside the bench's step: two clips from 128 k;
         // three and four clips: not re-measured)
         const long long sort_from = b->K == 1 ? 48 * 1024 : b->K == 2 ? 128 * 1024 : 262144;
+        // One wave or two?  With 2 blocks per SM the lane kernel holds 8 warps per SM; a crowd of 8 to 12 warps per SM would run a
+        // second, nearly empty wave (40 000 one-clip instances: 75 us against 48 us for 36 000).  The 168-register form holds 12:
+        // one wave, at a third more per wave.  Measured (tools/pose_bench.py --min-blocks 2 / 3, 8 mixed clips): one clip, 40 k /
+        // 48 k / 56 k instances 75 / 87 / 88 us -> 53 / 61 / 66 us (the frame-coherent order with either form: 65-93 us), 20 k /
+        // 30 k: 33 / 40 -> 30 / 36 us; two clips, 40 k / 48 k / 56 k: 115 / 117 / 117 -> 79 / 92 / 97 us, 30 k: 57 -> 63 us.
+        const bool one_wave3 = simple && b->K <= 2 && c->opt_pose_min_blocks == 0 && warps <= 12LL * c->sm_count &&
+                               (b->K == 1 || warps > 8LL * c->sm_count);
         bool sorted = simple && !io && c->n_buckets <= ORDER_MAX_BUCKETS && b->N < (1LL << 31) &&
-                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= sort_from && !remote));
+                      (c->opt_pose_sort == 1 || (c->opt_pose_sort < 0 && b->N >= sort_from && !remote && !one_wave3));
         if (sorted)
         {
             if (!b->d_order)
@@ -1712,8 +1719,9 @@ extern "C"
                 return PCL_OK;
             }
         }
-        // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM.  (Round 1 preferred 3 blocks for two-clip crowds
-        // beyond ~300 k instances; with the packed, straight-line groups the 168-register form spills: 1.98 against 1.86 ms at 1 M.)
+        // registers vs resident warps (see pose_simple_kernel): 2 blocks per SM, except where 3 save a second wave (one_wave3 above).
+        // (Round 1 preferred 3 blocks for two-clip crowds beyond ~300 k instances; with the packed, straight-line groups the
+        // 168-register form spills: 1.98 against 1.86 ms at 1 M.)
         // one-clip crowds too large for the level kernel, too small to give every scheduler two warps: two warps per 32 instances,
         // half a skeleton each (pose_simple_kernel<SPLIT>); measured with tools/pose_bench.py --clips 1: 8 000 instances 27.0 -> 21.8 us
         // (level kernel 24.8), 10 000: 28.8 -> 24.8, 16 000: 29.9 -> 25.0, 20 000 (more warps than the SMs hold at once): 33 -> 40
@@ -1734,7 +1742,9 @@ extern "C"
             return PCL_OK;
         }
         int mb = c->opt_pose_min_blocks;
-        if (mb == 0 || b->K > 2)
+        if (mb == 0)
+            mb = (one_wave3 && !sorted) ? 3 : 2;
+        if (b->K > 2)
             mb = 2;
 #define PCL_LAUNCH_POSE_SD(KK, SS, MM, DD)                                                                                  \
     {                                                                                                                       \
